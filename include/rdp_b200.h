@@ -1,0 +1,132 @@
+/*
+ * rdp_b200.h - C ABI of the B200-native vision hot path (U-Net forward + curvature profile).
+ *
+ * The reference (xuanjiangliu/robotic-discovery-platform) has no FFI of its own: the hot path sits behind two
+ * Python symbols imported by its gRPC server (services/vision_analysis/server.py:47-48).  This header is the
+ * boundary underneath our drop-in `pkg.segmentation_model.UNet` / `pkg.geometry_utils.compute_curvature_profile`:
+ * plain pointers and sizes, no torch types, callable from ctypes or any C caller.
+ *
+ * Conventions
+ *  - every data pointer is a DEVICE pointer owned by the caller unless a comment says "host";
+ *  - calls are asynchronous on `stream` (a cudaStream_t passed as void*; NULL = legacy default stream);
+ *  - return value: 0 on success, a negative RDP_ERR_* otherwise; rdp_last_error() gives the text for the
+ *    calling thread.  No exceptions cross this boundary;
+ *  - per-frame *data* conditions (too few points, degenerate bins, ...) are not errors: they are reported in
+ *    the per-frame `status` output (RDP_FRAME_*), mirroring the reference's "return an empty CurvatureResult";
+ *  - handles are immutable after creation; workspaces are per call, so concurrent callers (the reference server
+ *    runs 10 worker threads, server.py:172) only need distinct workspaces and streams.
+ */
+#ifndef RDP_B200_H
+#define RDP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RDP_OK 0
+#define RDP_ERR_BAD_ARGUMENT (-1)
+#define RDP_ERR_UNSUPPORTED (-2)
+#define RDP_ERR_CUDA (-3)
+#define RDP_ERR_WORKSPACE_TOO_SMALL (-4)
+
+/* per-frame status written by rdp_geom_curvature (same numbering as oracle/geometry_port.py) */
+#define RDP_FRAME_OK 0
+#define RDP_FRAME_TOO_FEW_POINTS 1  /* < 100 valid points             geometry_utils.py:64  */
+#define RDP_FRAME_DEGENERATE_BINS 2 /* < 50 points or bin width <= 0  geometry_utils.py:121,127 */
+#define RDP_FRAME_TOO_FEW_EDGE 3    /* < 20 edge points               geometry_utils.py:69  */
+#define RDP_FRAME_FIT_INVALID 4     /* splprep would raise (parameter not strictly increasing) :95-97 */
+#define RDP_FRAME_NEEDS_KNOTS 5     /* cubic on 8 knots leaves fp > s: FITPACK would insert knots (not run here) */
+
+/* depth element formats */
+#define RDP_DEPTH_U16 0 /* z = (double)d * scale                     (uint16 image * Python float) */
+#define RDP_DEPTH_F32 1 /* z = (double)(float)(d * (float)scale)     (float32 image * Python float) */
+#define RDP_DEPTH_F32_WIDE 2 /* z = (double)d * scale                (float32 image * numpy float64 scalar) */
+
+/* U-Net input formats */
+#define RDP_IN_RGB_U8_NHWC 0 /* (B,H,W,C) uint8, scaled by 1/255 on load (ToTensor, server.py:108) */
+#define RDP_IN_F32_NCHW 1    /* (B,C,H,W) float32, the tensor the reference module receives (server.py:121) */
+
+int rdp_abi_version(void);
+const char* rdp_last_error(void);
+
+/* ------------------------------------------------------------------------------------------------------ */
+/* U-Net: replaces UNet.forward (pkg/segmentation_model.py:109-120) and, optionally, the server's          */
+/* `sigmoid(out) > 0.5` mask rule (services/vision_analysis/server.py:124).                                 */
+/* ------------------------------------------------------------------------------------------------------ */
+
+typedef struct RdpUnet RdpUnet;
+
+/* One 3x3 conv + eval-mode BatchNorm + ReLU (DoubleConv halves, segmentation_model.py:31-36), already folded:
+ * weight = bf16 [cout][9][cin_pad] with gamma/sqrt(var+eps) multiplied in, tap index = 3*ky+kx, channels padded
+ * with zeros to a multiple of 64 (the first layer is stored im2col-style as [cout][64], k = (3*ky+kx)*cin + c);
+ * shift = fp32 [cout] = beta - mean*gamma/sqrt(var+eps). */
+typedef struct {
+  const void* weight; /* device, bf16 */
+  const float* shift; /* device, fp32 */
+  int32_t cin;        /* logical input channels (before padding) */
+  int32_t cout;
+} RdpConvLayer;
+
+typedef struct {
+  int32_t n_channels;      /* UNet(n_channels, ...) ; 9*n_channels must be <= 64 */
+  int32_t n_classes;       /* UNet(..., n_classes)  ; 1..8 */
+  RdpConvLayer conv[18];   /* inc.0, inc.3, down1.0, down1.3, ... down4.3, up1.0, ... up4.3 in forward order */
+  const float* outc_weight; /* device fp32 [n_classes][64]   OutConv, segmentation_model.py:81 */
+  const float* outc_bias;   /* device fp32 [n_classes] */
+} RdpUnetWeights;
+
+/* Builds an immutable handle (copies the small descriptor, keeps the caller's device pointers). */
+int rdp_unet_create(const RdpUnetWeights* weights, RdpUnet** out);
+void rdp_unet_destroy(RdpUnet* net);
+
+/* Scratch for activations of one forward call of shape (B,H,W). */
+int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W, size_t* bytes);
+
+/* logits: fp32 (B, n_classes, H, W) or NULL.  mask: uint8 (B, n_classes, H, W) in {0,1} or NULL; it is
+ * [sigmoidf(logit) > 0.5f] evaluated in fp32 like the server does.  At least one of them must be non-NULL. */
+int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
+                     uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Number of kernel launches one rdp_unet_forward call issues (for bench.py's gpu_launches). */
+int rdp_unet_launch_count(const RdpUnet* net);
+
+/* Debug / parity hook: copy of an intermediate activation as fp32 NCHW.  `index` = 0..17 (conv outputs in the
+ * order of RdpUnetWeights.conv).  Must be called after rdp_unet_forward on the same workspace and stream. */
+int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,
+                             float* out_nchw, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------ */
+/* Geometry: replaces compute_curvature_profile (pkg/geometry_utils.py:42-97) for a batch of frames.        */
+/* ------------------------------------------------------------------------------------------------------ */
+
+typedef struct {
+  double* mean_curvature;  /* [B]          geometry_utils.py:160 */
+  double* max_curvature;   /* [B] */
+  double* spline_points;   /* [B][100][3]  geometry_utils.py:83-87 */
+  int32_t* status;         /* [B] RDP_FRAME_* */
+  int32_t* n_points;       /* [B] valid masked points N                      (NULL allowed) */
+  int32_t* n_edge;         /* [B] edge points E                              (NULL allowed) */
+  double* fit_residual;    /* [B] fp of the 8-knot least-squares cubic        (NULL allowed) */
+  float* points_xyz;       /* [B][H*W][3] fp32 point cloud, row-major order   (NULL allowed) _get_pcd_from_mask */
+  uint32_t* edge_pixels;   /* [B][H*W/20+64] pixel index v*W+u of the edge points, ordered by x (NULL allowed) */
+  int32_t* bin_counts;     /* [B][50] points per x-bin                        (NULL allowed) */
+} RdpCurvatureOut;
+
+int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes);
+
+/* mask: uint8 (B,H,W), pixel selected when > 0.  depth: (B,H,W) of `depth_fmt`.  intrinsics: HOST pointer to
+ * 4 doubles fx, fy, cx, cy = K[0,0], K[1,1], K[0,2], K[1,2] (geometry_utils.py:111-112), shared by the batch. */
+int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                       const double* intrinsics, double depth_scale, const RdpCurvatureOut* out, void* workspace,
+                       size_t workspace_bytes, void* stream);
+
+/* Number of kernel launches (incl. the workspace memset) one rdp_geom_curvature call issues. */
+int rdp_geom_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RDP_B200_H */

@@ -1,0 +1,638 @@
+// U-Net forward on sm_100a: replaces UNet.forward of the reference (pkg/segmentation_model.py:109-120) plus the
+// server's mask rule (services/vision_analysis/server.py:124).
+//
+// Activations live in HBM as NHWC bf16.  Every 3x3 convolution (+ folded eval-BatchNorm + ReLU) is one launch of
+// `k_conv3x3`, an implicit GEMM on the 5th-generation tensor cores:
+//   * M = a 128-pixel spatial patch (tile_h x tile_w) of one frame, N = 64..256 output channels, K = 9 taps x Cin;
+//   * per K-step (one tap, 64 input channels) TMA loads the patch shifted by the tap offset from a 4-D NHWC tensor
+//     map - out-of-bounds pixels are zero-filled by the TMA unit, which *is* the convolution padding - and the
+//     matching 64-wide slice of the packed weights, both with 128-byte swizzle, into a ring of shared-memory stages;
+//   * one thread issues tcgen05.mma (bf16 x bf16 -> fp32) into a TMEM accumulator; two accumulator stages let the
+//     epilogue of tile i overlap the MMAs of tile i+1 (persistent CTAs, static round-robin over tiles);
+//   * four epilogue warps read TMEM (tcgen05.ld), add the BN shift, apply ReLU and store bf16 NHWC; for the last
+//     layer they also apply the 1x1 OutConv, and write fp32 logits and/or the thresholded mask;
+//   * skip connections are read in place: the K loop takes its first channel blocks from the skip tensor and the
+//     rest from the upsampled tensor (two tensor maps), so `torch.cat` never materialises.
+// Pooling, bilinear upsampling (align_corners=True, position-dependent weights) and the first layer's im2col are
+// separate bandwidth-bound kernels in this round.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+
+#include "rdp_common.cuh"
+#include "sm100_ptx.cuh"
+
+namespace rdp {
+namespace unet {
+
+using namespace ptx;
+
+constexpr int TILE_M = 128;   // pixels per tile = UMMA M
+constexpr int BLOCK_K = 64;   // bf16 elements per K-step = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int CONV_THREADS = 192;  // warp 0: TMA producer, warp 1: MMA issuer, warps 2-5: epilogue
+constexpr int A_STAGE_BYTES = TILE_M * BLOCK_K * 2;
+constexpr int SMEM_BUDGET = 200 * 1024;
+
+struct ConvParams {
+  int B, H, W;
+  int tile_w, tile_h, tiles_x, tiles_y;
+  int n_tiles;     // Cout / BN
+  int kb0, kb1;    // 64-channel blocks taken from source 0 (skip / plain input) and source 1 (upsampled)
+  int taps;        // 9, or 1 for the im2col'ed first layer
+  int cin_pad;     // (kb0 + kb1) * 64: K stride between taps in the packed weights
+  int cout;
+  int total_work;  // B * tiles_y * tiles_x * n_tiles
+  const float* shift;
+  __nv_bfloat16* out;  // NHWC, may be null when only the head output is wanted
+  // fused OutConv head (only with BN == cout == 64)
+  const float* head_w;
+  const float* head_b;
+  int n_classes;
+  float* logits;
+  uint8_t* mask;
+};
+
+template <int BN>
+struct ConvCfg {
+  static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int STAGES = SMEM_BUDGET / STAGE_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// sigmoid(x) > 0.5 evaluated in fp32 as torch does: true from x = 1.5 * 2^-24 upwards (probed on torch 2.11 CPU)
+__device__ __forceinline__ bool mask_rule(float logit) { return logit > 8.940697e-8f; }
+
+template <int BN>
+__global__ void __launch_bounds__(CONV_THREADS, 1)
+k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
+          const __grid_constant__ CUtensorMap map_w, const ConvParams p) {
+  using Cfg = ConvCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + Cfg::STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* full = bars;                       // [STAGES] TMA -> MMA
+  uint64_t* empty = bars + Cfg::STAGES;        // [STAGES] MMA -> TMA
+  uint64_t* acc_full = bars + 2 * Cfg::STAGES; // [2] MMA -> epilogue
+  uint64_t* acc_empty = acc_full + 2;          // [2] epilogue -> MMA
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_steps = (p.kb0 + p.kb1) * p.taps;
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_src0);
+    prefetch_tensormap(&map_src1);
+    prefetch_tensormap(&map_w);
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      uint32_t stage = 0, phase = 0;
+      for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+        const int nt = work % p.n_tiles;
+        int m = work / p.n_tiles;
+        const int tx = m % p.tiles_x; m /= p.tiles_x;
+        const int ty = m % p.tiles_y;
+        const int n = m / p.tiles_y;
+        const int x0 = tx * p.tile_w, y0 = ty * p.tile_h;
+        for (int cb = 0; cb < p.kb0 + p.kb1; ++cb) {
+          const CUtensorMap* src = cb < p.kb0 ? &map_src0 : &map_src1;
+          const int c0 = (cb < p.kb0 ? cb : cb - p.kb0) * BLOCK_K;
+          for (int tap = 0; tap < p.taps; ++tap) {
+            const int dy = p.taps == 9 ? tap / 3 - 1 : 0, dx = p.taps == 9 ? tap % 3 - 1 : 0;
+            mbar_wait(&empty[stage], phase ^ 1);
+            mbar_arrive_expect_tx(&full[stage], Cfg::STAGE_BYTES);
+            tma_load_4d(smem_a + stage * A_STAGE_BYTES, src, c0, x0 + dx, y0 + dy, n, &full[stage]);
+            tma_load_2d(smem_b + stage * Cfg::B_STAGE_BYTES, &map_w, tap * p.cin_pad + cb * BLOCK_K, nt * BN, &full[stage]);
+            if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ================= MMA issuer =================
+      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_acc = tmem_base + as * BN;
+        for (int ks = 0; ks < k_steps; ++ks) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * A_STAGE_BYTES));
+          const uint64_t db = make_sw128_desc(smem_u32(smem_b + stage * Cfg::B_STAGE_BYTES));
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            // advancing 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in 16-byte descriptor units
+            mma_bf16_ss(tmem_acc, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+          }
+          tc_commit(&empty[stage]);  // frees the smem stage once these MMAs have read it
+          if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(&acc_full[as]);    // accumulator complete
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int quarter = warp & 3;  // TMEM lanes this warp may read: 32*quarter .. +31
+    const int row = quarter * 32 + lane;
+    uint32_t as = 0, aphase = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+      const int nt = work % p.n_tiles;
+      int m = work / p.n_tiles;
+      const int tx = m % p.tiles_x; m /= p.tiles_x;
+      const int ty = m % p.tiles_y;
+      const int n = m / p.tiles_y;
+      const int y = ty * p.tile_h + row / p.tile_w, x = tx * p.tile_w + row % p.tile_w;
+      const bool inside = y < p.H && x < p.W;
+      const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
+      float head[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) head[c] = 0.f;
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + c0, r);
+        tmem_ld_wait();
+        const float* sh = p.shift + nt * BN + c0;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = fmaxf(__uint_as_float(r[j]) + __ldg(sh + j), 0.f);
+        if (BN == 64 && p.head_w != nullptr) {
+#pragma unroll
+          for (int cls = 0; cls < 8; ++cls) {
+            if (cls < p.n_classes) {
+              const float* hw = p.head_w + cls * 64 + c0;
+              float a = head[cls];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) a = fmaf(v[j], __ldg(hw + j), a);
+              head[cls] = a;
+            }
+          }
+        }
+        if (inside && p.out != nullptr) {
+          uint4* dst = reinterpret_cast<uint4*>(p.out + pixel * p.cout + nt * BN + c0);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            uint4 o;
+            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[8 * q + 0], v[8 * q + 1]);
+            __nv_bfloat162 t1 = __floats2bfloat162_rn(v[8 * q + 2], v[8 * q + 3]);
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[8 * q + 4], v[8 * q + 5]);
+            __nv_bfloat162 t3 = __floats2bfloat162_rn(v[8 * q + 6], v[8 * q + 7]);
+            o.x = *reinterpret_cast<uint32_t*>(&t0);
+            o.y = *reinterpret_cast<uint32_t*>(&t1);
+            o.z = *reinterpret_cast<uint32_t*>(&t2);
+            o.w = *reinterpret_cast<uint32_t*>(&t3);
+            dst[q] = o;
+          }
+        }
+      }
+      // accumulator stage drained: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      if (BN == 64 && p.head_w != nullptr && inside) {
+        const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
+#pragma unroll
+        for (int cls = 0; cls < 8; ++cls) {
+          if (cls < p.n_classes) {
+            const float logit = head[cls] + __ldg(p.head_b + cls);
+            const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
+            if (p.logits) p.logits[o] = logit;
+            if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
+          }
+        }
+      }
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// bandwidth-bound helpers
+// ---------------------------------------------------------------------------------------------------------
+// First layer: gather the 3x3xC neighbourhood of every pixel into 64 bf16 (k = (3*ky+kx)*C + c, zero padded),
+// so that inc.0 runs through the same tensor-core kernel as a 1x1 convolution with K = 64.
+__global__ void __launch_bounds__(256) k_im2col_first(const void* in, int in_fmt, int B, int H, int W, int C,
+                                                      __nv_bfloat16* out) {
+  const size_t total = (size_t)B * H * W * 8;  // 8 chunks of 8 values per pixel
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int chunk = (int)(i & 7);
+    size_t px = i >> 3;
+    const int x = (int)(px % W);
+    const int y = (int)((px / W) % H);
+    const int n = (int)(px / ((size_t)W * H));
+    __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = chunk * 8 + j;
+      float val = 0.f;
+      if (k < 9 * C) {
+        const int tap = k / C, c = k - tap * C;
+        const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+          if (in_fmt == RDP_IN_RGB_U8_NHWC)
+            val = (float)((const uint8_t*)in)[(((size_t)n * H + yy) * W + xx) * C + c] / 255.0f;  // ToTensor
+          else
+            val = ((const float*)in)[(((size_t)n * C + c) * H + yy) * W + xx];
+        }
+      }
+      v[j] = __float2bfloat16_rn(val);
+    }
+    *reinterpret_cast<uint4*>(out + px * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
+  }
+}
+
+__device__ __forceinline__ uint4 bf16x8_max(uint4 a, uint4 b) {
+  uint4 r;
+  const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
+  __nv_bfloat162* pr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pr[i] = __hmax2(pa[i], pb[i]);
+  return r;
+}
+
+// MaxPool2d(2) (segmentation_model.py:47) on NHWC bf16, 8 channels per thread.
+__global__ void __launch_bounds__(256) k_maxpool2(const __nv_bfloat16* in, int B, int H, int W, int C, __nv_bfloat16* out) {
+  const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
+  const size_t total = (size_t)B * Ho * Wo * C8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    size_t r = i / C8;
+    const int xo = (int)(r % Wo); r /= Wo;
+    const int yo = (int)(r % Ho);
+    const int n = (int)(r / Ho);
+    const uint4* src = reinterpret_cast<const uint4*>(in + (((size_t)n * H + 2 * yo) * W + 2 * xo) * C) + c8;
+    const size_t rowstride = (size_t)W * C8;
+    const uint4 a = __ldg(src), b = __ldg(src + C8), c = __ldg(src + rowstride), d = __ldg(src + rowstride + C8);
+    reinterpret_cast<uint4*>(out)[i] = bf16x8_max(bf16x8_max(a, b), bf16x8_max(c, d));
+  }
+}
+
+// nn.Upsample(scale_factor=2, bilinear, align_corners=True) followed by the zero pad of Up.forward
+// (segmentation_model.py:61,68-74): (B,h,w,C) -> (B,Hs,Ws,C), interpolated values placed at offset (py, px).
+__global__ void __launch_bounds__(256) k_upsample2x(const __nv_bfloat16* in, int B, int h, int w, int C, int Hs, int Ws,
+                                                    int py, int px, __nv_bfloat16* out) {
+  const int Ho = 2 * h, Wo = 2 * w, C8 = C / 8;
+  const float ry = Ho > 1 ? (float)(h - 1) / (float)(Ho - 1) : 0.f;
+  const float rx = Wo > 1 ? (float)(w - 1) / (float)(Wo - 1) : 0.f;
+  const size_t total = (size_t)B * Hs * Ws * C8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    size_t r = i / C8;
+    const int xs = (int)(r % Ws); r /= Ws;
+    const int ys = (int)(r % Hs);
+    const int n = (int)(r / Hs);
+    const int yo = ys - py, xo = xs - px;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (yo >= 0 && yo < Ho && xo >= 0 && xo < Wo) {
+      const float fy = ry * (float)yo, fx = rx * (float)xo;
+      const int y0 = (int)fy, x0 = (int)fx;
+      const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+      const float ly1 = fy - (float)y0, ly0 = 1.f - ly1, lx1 = fx - (float)x0, lx0 = 1.f - lx1;
+      const uint4* base = reinterpret_cast<const uint4*>(in + (size_t)n * h * w * C) + c8;
+      const uint4 v00 = __ldg(base + ((size_t)y0 * w + x0) * C8), v01 = __ldg(base + ((size_t)y0 * w + x1) * C8);
+      const uint4 v10 = __ldg(base + ((size_t)y1 * w + x0) * C8), v11 = __ldg(base + ((size_t)y1 * w + x1) * C8);
+      const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
+      const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&v01);
+      const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
+      const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
+      __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 fa = __bfloat1622float2(a[j]), fb = __bfloat1622float2(b[j]);
+        const float2 fc = __bfloat1622float2(c[j]), fd = __bfloat1622float2(d[j]);
+        const float r0 = ly0 * (lx0 * fa.x + lx1 * fb.x) + ly1 * (lx0 * fc.x + lx1 * fd.x);
+        const float r1 = ly0 * (lx0 * fa.y + lx1 * fb.y) + ly1 * (lx0 * fc.y + lx1 * fd.y);
+        po[j] = __floats2bfloat162_rn(r0, r1);
+      }
+    }
+    reinterpret_cast<uint4*>(out)[i] = o;
+  }
+}
+
+// NHWC bf16 -> NCHW fp32 (parity hook, not on the hot path)
+__global__ void k_nhwc_to_nchw_f32(const __nv_bfloat16* in, int B, int H, int W, int C, float* out) {
+  const size_t total = (size_t)B * C * H * W;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    size_t r = i / W;
+    const int y = (int)(r % H); r /= H;
+    const int c = (int)(r % C);
+    const int n = (int)(r / C);
+    out[i] = __bfloat162float(in[(((size_t)n * H + y) * W + x) * C + c]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// 4-D map over an NHWC bf16 activation: dims (C, W, H, B), box (64, tile_w, tile_h, 1), 128-byte swizzle.
+static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int tile_w, int tile_h) {
+  EncodeTiledFn fn = encode_fn();
+  RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)tile_w, (cuuint32_t)tile_h, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(activation %dx%dx%dx%d) failed: %d", B, H, W, C, (int)r);
+  return RDP_OK;
+}
+
+// 2-D map over packed weights [cout][K]: dims (K, cout), box (64, bn).
+static int make_weight_map(CUtensorMap* m, const void* ptr, int K, int cout, int bn) {
+  EncodeTiledFn fn = encode_fn();
+  RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)cout};
+  cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  cuuint32_t box[2] = {BLOCK_K, (cuuint32_t)bn};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(weights %dx%d) failed: %d", cout, K, (int)r);
+  return RDP_OK;
+}
+
+static void pick_tile(int H, int W, int& tw, int& th) {
+  const int cand[5][2] = {{16, 8}, {8, 16}, {32, 4}, {64, 2}, {128, 1}};
+  long best = -1;
+  for (auto& c : cand) {
+    const long cover = (long)((W + c[0] - 1) / c[0]) * ((H + c[1] - 1) / c[1]);
+    if (best < 0 || cover < best) {
+      best = cover;
+      tw = c[0];
+      th = c[1];
+    }
+  }
+}
+
+struct Level { int H, W; };
+
+}  // namespace unet
+}  // namespace rdp
+
+using namespace rdp;
+using namespace rdp::unet;
+
+struct RdpUnet {
+  RdpUnetWeights w;
+  CUtensorMap wmap[18];
+  int bn[18];
+  int cin_pad[18];
+  int num_sms;
+};
+
+namespace {
+
+// Activation buffers of one forward call, all NHWC bf16, carved from the caller's workspace.
+struct Buffers {
+  Level lv[5];
+  __nv_bfloat16* col;      // im2col of the input, 64 ch @ level 0
+  __nv_bfloat16* act[18];  // output of conv i
+  __nv_bfloat16* pool[4];  // pooled x1..x4
+  __nv_bfloat16* up[4];    // upsampled + padded low-resolution branch for up1..up4
+  size_t bytes;
+};
+
+const int kConvLevel[18] = {0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
+
+Buffers carve_unet(const RdpUnet* net, void* ws, int B, int H, int W) {
+  Buffers b;
+  b.lv[0] = {H, W};
+  for (int i = 1; i < 5; ++i) b.lv[i] = {b.lv[i - 1].H / 2, b.lv[i - 1].W / 2};
+  Carver c(ws);
+  auto px = [&](int l) { return (size_t)B * b.lv[l].H * b.lv[l].W; };
+  b.col = c.take<__nv_bfloat16>(px(0) * 64);
+  for (int i = 0; i < 18; ++i) b.act[i] = c.take<__nv_bfloat16>(px(kConvLevel[i]) * net->w.conv[i].cout);
+  for (int i = 0; i < 4; ++i) b.pool[i] = c.take<__nv_bfloat16>(px(i + 1) * net->w.conv[2 * i + 1].cout);
+  // up[j] feeds conv 10+2j: channels = cout of the layer below (conv 9+2j), spatial = skip level 3-j
+  for (int j = 0; j < 4; ++j) b.up[j] = c.take<__nv_bfloat16>(px(3 - j) * net->w.conv[9 + 2 * j].cout);
+  b.bytes = c.total();
+  return b;
+}
+
+template <int BN>
+int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms,
+                   cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ConvCfg<BN>::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int grid = p.total_work < num_sms ? p.total_work : num_sms;
+  k_conv3x3<BN><<<grid, CONV_THREADS, ConvCfg<BN>::SMEM_BYTES, stream>>>(s0, s1, wm, p);
+  return RDP_OK;
+}
+
+}  // namespace
+
+extern "C" int rdp_unet_create(const RdpUnetWeights* w, RdpUnet** out) {
+  RDP_REQUIRE(w && out, RDP_ERR_BAD_ARGUMENT, "rdp_unet_create: null argument");
+  RDP_REQUIRE(w->n_channels >= 1 && 9 * w->n_channels <= 64, RDP_ERR_UNSUPPORTED, "rdp_unet_create: n_channels %d unsupported (9*C must be <= 64)", w->n_channels);
+  RDP_REQUIRE(w->n_classes >= 1 && w->n_classes <= 8, RDP_ERR_UNSUPPORTED, "rdp_unet_create: n_classes %d unsupported (1..8)", w->n_classes);
+  RDP_REQUIRE(w->outc_weight && w->outc_bias, RDP_ERR_BAD_ARGUMENT, "rdp_unet_create: missing OutConv parameters");
+  static const int cin[18] = {0, 64, 64, 128, 128, 256, 256, 512, 512, 512, 1024, 512, 512, 256, 256, 128, 128, 64};
+  static const int cout[18] = {64, 64, 128, 128, 256, 256, 512, 512, 512, 512, 512, 256, 256, 128, 128, 64, 64, 64};
+  RdpUnet* net = new (std::nothrow) RdpUnet;
+  RDP_REQUIRE(net, RDP_ERR_CUDA, "rdp_unet_create: out of host memory");
+  net->w = *w;
+  int dev = 0;
+  cudaDeviceProp prop;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    delete net;
+    set_error("rdp_unet_create: no CUDA device");
+    return RDP_ERR_CUDA;
+  }
+  if (prop.major != 10) {
+    delete net;
+    set_error("rdp_unet_create: this library is built for sm_100a only (device is sm_%d%d)", prop.major, prop.minor);
+    return RDP_ERR_UNSUPPORTED;
+  }
+  net->num_sms = prop.multiProcessorCount;
+  for (int i = 0; i < 18; ++i) {
+    const RdpConvLayer& L = w->conv[i];
+    const int want_cin = i == 0 ? w->n_channels : cin[i];
+    if (!L.weight || !L.shift || L.cin != want_cin || L.cout != cout[i]) {
+      delete net;
+      set_error("rdp_unet_create: layer %d expects cin=%d cout=%d with non-null weight/shift (got %d, %d)", i, want_cin, cout[i], L.cin, L.cout);
+      return RDP_ERR_BAD_ARGUMENT;
+    }
+    net->cin_pad[i] = i == 0 ? 64 : cin[i];
+    net->bn[i] = cout[i] >= 256 ? 256 : cout[i];
+    const int K = i == 0 ? 64 : 9 * cin[i];
+    const int rc = make_weight_map(&net->wmap[i], L.weight, K, cout[i], net->bn[i]);
+    if (rc != RDP_OK) {
+      delete net;
+      return rc;
+    }
+  }
+  *out = net;
+  return RDP_OK;
+}
+
+extern "C" void rdp_unet_destroy(RdpUnet* net) { delete net; }
+
+extern "C" int rdp_unet_launch_count(const RdpUnet*) { return 1 + 18 + 4 + 4; }
+
+extern "C" int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W, size_t* bytes) {
+  RDP_REQUIRE(net && bytes, RDP_ERR_BAD_ARGUMENT, "rdp_unet_workspace_bytes: null argument");
+  RDP_REQUIRE(B > 0 && H >= 16 && W >= 16, RDP_ERR_BAD_ARGUMENT, "rdp_unet_workspace_bytes: bad shape %dx%dx%d (H, W >= 16)", B, H, W);
+  *bytes = carve_unet(net, nullptr, B, H, W).bytes;
+  return RDP_OK;
+}
+
+extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
+                                uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream_) {
+  RDP_REQUIRE(net && input && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: null argument");
+  RDP_REQUIRE(logits || mask, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: neither logits nor mask requested");
+  RDP_REQUIRE(in_fmt == RDP_IN_RGB_U8_NHWC || in_fmt == RDP_IN_F32_NCHW, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: unknown input format %d", in_fmt);
+  RDP_REQUIRE(B > 0 && H >= 16 && W >= 16, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: bad shape %dx%dx%d (H, W >= 16)", B, H, W);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const Buffers buf = carve_unet(net, workspace, B, H, W);
+  RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_forward: workspace %zu < required %zu bytes", workspace_bytes, buf.bytes);
+  RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
+
+  auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
+
+  {
+    const size_t items = (size_t)B * H * W * 8;
+    k_im2col_first<<<ew_grid(items), 256, 0, stream>>>(input, in_fmt, B, H, W, net->w.n_channels, buf.col);
+  }
+
+  // one conv launch: sources (src0 with c0 channels [+ src1 with c1 channels]) at level `lvl` -> act[i]
+  auto conv = [&](int i, const __nv_bfloat16* src0, int c0, const __nv_bfloat16* src1, int c1, int taps) -> int {
+    const Level L = buf.lv[kConvLevel[i]];
+    ConvParams p{};
+    p.B = B; p.H = L.H; p.W = L.W;
+    pick_tile(L.H, L.W, p.tile_w, p.tile_h);
+    p.tiles_x = (L.W + p.tile_w - 1) / p.tile_w;
+    p.tiles_y = (L.H + p.tile_h - 1) / p.tile_h;
+    p.cout = net->w.conv[i].cout;
+    p.n_tiles = p.cout / net->bn[i];
+    p.kb0 = c0 / 64; p.kb1 = c1 / 64;
+    p.taps = taps;
+    p.cin_pad = net->cin_pad[i];
+    p.total_work = B * p.tiles_y * p.tiles_x * p.n_tiles;
+    p.shift = net->w.conv[i].shift;
+    p.out = buf.act[i];
+    if (i == 17) {
+      p.head_w = net->w.outc_weight;
+      p.head_b = net->w.outc_bias;
+      p.n_classes = net->w.n_classes;
+      p.logits = logits;
+      p.mask = mask;
+    }
+    CUtensorMap m0, m1;
+    int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, p.tile_w, p.tile_h);
+    if (rc != RDP_OK) return rc;
+    rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, p.tile_w, p.tile_h);
+    if (rc != RDP_OK) return rc;
+    switch (net->bn[i]) {
+      case 64: return launch_conv_bn<64>(m0, m1, net->wmap[i], p, net->num_sms, stream);
+      case 128: return launch_conv_bn<128>(m0, m1, net->wmap[i], p, net->num_sms, stream);
+      default: return launch_conv_bn<256>(m0, m1, net->wmap[i], p, net->num_sms, stream);
+    }
+  };
+#define RDP_TRY(expr)          \
+  do {                         \
+    const int _rc = (expr);    \
+    if (_rc != RDP_OK) return _rc; \
+  } while (0)
+
+  // encoder: inc, down1..down4 (segmentation_model.py:110-114)
+  RDP_TRY(conv(0, buf.col, 64, nullptr, 0, 1));
+  RDP_TRY(conv(1, buf.act[0], 64, nullptr, 0, 9));
+  for (int d = 0; d < 4; ++d) {
+    const Level L = buf.lv[d];
+    const int C = net->w.conv[2 * d + 1].cout;
+    const size_t items = (size_t)B * (L.H / 2) * (L.W / 2) * (C / 8);
+    k_maxpool2<<<ew_grid(items), 256, 0, stream>>>(buf.act[2 * d + 1], B, L.H, L.W, C, buf.pool[d]);
+    RDP_TRY(conv(2 * d + 2, buf.pool[d], C, nullptr, 0, 9));
+    RDP_TRY(conv(2 * d + 3, buf.act[2 * d + 2], net->w.conv[2 * d + 2].cout, nullptr, 0, 9));
+  }
+  // decoder: up1..up4 (segmentation_model.py:115-118); skip channels first, then the upsampled branch
+  for (int j = 0; j < 4; ++j) {
+    const int low_i = 9 + 2 * j;                 // conv whose output is upsampled
+    const int skip_i = 7 - 2 * j;                // x4, x3, x2, x1
+    const Level Ls = buf.lv[3 - j], Ll = buf.lv[4 - j];
+    const int Cl = net->w.conv[low_i].cout, Cs = net->w.conv[skip_i].cout;
+    const int dy = Ls.H - 2 * Ll.H, dx = Ls.W - 2 * Ll.W;
+    const size_t items = (size_t)B * Ls.H * Ls.W * (Cl / 8);
+    k_upsample2x<<<ew_grid(items), 256, 0, stream>>>(buf.act[low_i], B, Ll.H, Ll.W, Cl, Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
+    RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, buf.up[j], Cl, 9));
+    RDP_TRY(conv(11 + 2 * j, buf.act[10 + 2 * j], net->w.conv[10 + 2 * j].cout, nullptr, 0, 9));
+  }
+#undef RDP_TRY
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
+
+extern "C" int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,
+                                        float* out_nchw, void* stream_) {
+  RDP_REQUIRE(net && workspace && out_nchw && index >= 0 && index < 18, RDP_ERR_BAD_ARGUMENT, "rdp_unet_read_activation: bad argument");
+  const Buffers buf = carve_unet(net, const_cast<void*>(workspace), B, H, W);
+  const Level L = buf.lv[kConvLevel[index]];
+  const int C = net->w.conv[index].cout;
+  const size_t total = (size_t)B * C * L.H * L.W;
+  k_nhwc_to_nchw_f32<<<(int)std::min<size_t>((total + 255) / 256, 65535), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      buf.act[index], B, L.H, L.W, C, out_nchw);
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}

@@ -1,0 +1,97 @@
+"""Batched curvature profile on the GPU through the C ABI (`rdp_geom_curvature`).
+
+Replaces `compute_curvature_profile` and its helpers (reference `pkg/geometry_utils.py:42-162`) for device tensors:
+masks (B,H,W) uint8, depth (B,H,W) uint16 | float32.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+
+NUM_SAMPLES = 100
+NUM_BINS = 50
+
+
+@dataclass
+class CurvatureBatch:
+    mean_curvature: torch.Tensor   # (B,) f64
+    max_curvature: torch.Tensor    # (B,) f64
+    spline_points: torch.Tensor    # (B,100,3) f64
+    status: torch.Tensor           # (B,) i32, rdp_b200._lib.FRAME_*
+    n_points: torch.Tensor         # (B,) i32
+    n_edge: torch.Tensor           # (B,) i32
+    fit_residual: torch.Tensor     # (B,) f64
+    points_xyz: torch.Tensor | None = None    # (B,H*W,3) f32, first n_points rows valid
+    edge_pixels: torch.Tensor | None = None   # (B,ecap) u32 as int32 view, first n_edge valid
+    bin_counts: torch.Tensor | None = None    # (B,50) i32
+    workspace: torch.Tensor | None = None
+
+
+def depth_format(depth_dtype, depth_scale) -> int:
+    """NumPy promotion of `depth_image[v, u] * depth_scale` (reference `geometry_utils.py:105`)."""
+    if depth_dtype in (torch.uint16, np.dtype(np.uint16)):
+        return _lib.DEPTH_U16
+    if depth_dtype in (torch.float32, np.dtype(np.float32)):
+        # Python float (weak scalar) keeps float32; a NumPy float64 scalar promotes the product to float64
+        return _lib.DEPTH_F32_WIDE if isinstance(depth_scale, np.floating) and not isinstance(depth_scale, np.float32) else _lib.DEPTH_F32
+    raise _lib.RdpError(f"unsupported depth dtype {depth_dtype}")
+
+
+def workspace_bytes(B: int, H: int, W: int) -> int:
+    n = C.c_size_t()
+    _lib.check(_lib.load().rdp_geom_workspace_bytes(B, H, W, C.byref(n)), "rdp_geom_workspace_bytes")
+    return n.value
+
+
+def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_scale, *, want_points=False,
+                    want_edge=False, want_bins=False, workspace=None, depth_fmt=None) -> CurvatureBatch:
+    lib = _lib.load()
+    if masks.device.type != "cuda" or depth.device != masks.device:
+        raise _lib.RdpError("curvature_batch needs CUDA tensors on one device; there is no CPU path")
+    if masks.dtype != torch.uint8 or masks.dim() != 3 or depth.shape != masks.shape:
+        raise _lib.RdpError(f"masks must be (B,H,W) uint8 and depth the same shape (got {tuple(masks.shape)} {masks.dtype}, "
+                            f"{tuple(depth.shape)} {depth.dtype})")
+    B, H, W = masks.shape
+    dev = masks.device
+    fmt = depth_format(depth.dtype, depth_scale) if depth_fmt is None else depth_fmt
+    masks, depth = masks.contiguous(), depth.contiguous()
+    K = np.asarray(intrinsics, dtype=np.float64)
+    k4 = (C.c_double * 4)(K[0, 0], K[1, 1], K[0, 2], K[1, 2]) if K.shape == (3, 3) else (C.c_double * 4)(*K.reshape(4))
+    with torch.cuda.device(dev):
+        need = workspace_bytes(B, H, W)
+        if workspace is None or workspace.numel() < need:
+            workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+        res = CurvatureBatch(
+            mean_curvature=torch.empty(B, dtype=torch.float64, device=dev),
+            max_curvature=torch.empty(B, dtype=torch.float64, device=dev),
+            spline_points=torch.empty((B, NUM_SAMPLES, 3), dtype=torch.float64, device=dev),
+            status=torch.empty(B, dtype=torch.int32, device=dev),
+            n_points=torch.empty(B, dtype=torch.int32, device=dev),
+            n_edge=torch.empty(B, dtype=torch.int32, device=dev),
+            fit_residual=torch.empty(B, dtype=torch.float64, device=dev),
+            workspace=workspace,
+        )
+        out = _lib.CurvatureOut()
+        out.mean_curvature, out.max_curvature = res.mean_curvature.data_ptr(), res.max_curvature.data_ptr()
+        out.spline_points, out.status = res.spline_points.data_ptr(), res.status.data_ptr()
+        out.n_points, out.n_edge = res.n_points.data_ptr(), res.n_edge.data_ptr()
+        out.fit_residual = res.fit_residual.data_ptr()
+        if want_points:
+            res.points_xyz = torch.empty((B, H * W, 3), dtype=torch.float32, device=dev)
+            out.points_xyz = res.points_xyz.data_ptr()
+        if want_edge:
+            res.edge_pixels = torch.empty((B, H * W // 20 + 64), dtype=torch.int32, device=dev)
+            out.edge_pixels = res.edge_pixels.data_ptr()
+        if want_bins:
+            res.bin_counts = torch.empty((B, NUM_BINS), dtype=torch.int32, device=dev)
+            out.bin_counts = res.bin_counts.data_ptr()
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(lib.rdp_geom_curvature(masks.data_ptr(), depth.data_ptr(), fmt, B, H, W, k4, float(depth_scale),
+                                          C.byref(out), workspace.data_ptr(), workspace.numel(), stream),
+                   "rdp_geom_curvature")
+    return res

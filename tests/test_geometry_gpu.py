@@ -1,0 +1,158 @@
+"""GPU parity of the geometry kernels (through the C ABI) against the oracle and the reference's golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import geometry_port as gp
+from rdp_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _run(frames, **kw):
+    from rdp_b200 import geometry
+    masks = torch.from_numpy(np.stack([f["mask_gt"] for f in frames])).cuda()
+    depth = torch.from_numpy(np.stack([f["depth"] for f in frames])).cuda()
+    r = geometry.curvature_batch(masks, depth, frames[0]["K"], frames[0]["depth_scale"], want_points=True,
+                                 want_edge=True, want_bins=True, **kw)
+    torch.cuda.synchronize()
+    return r
+
+
+def _check_frame(r, i, f, curv_rtol=1e-9):
+    o = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
+    n = int(r.n_points[i])
+    assert n == o.n_points
+    pcd, pix = gp.deproject(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
+    got = r.points_xyz[i, :n].cpu().numpy().astype(np.float64)
+    # fp32 output: within 1e-5 relative of the fp64 reference points (north_star), in the same row-major order
+    np.testing.assert_allclose(got, pcd, rtol=1e-5, atol=1e-7)
+    if o.n_points >= gp.MIN_POINTS and o.status != gp.DEGENERATE_BINS:
+        assert np.array_equal(r.bin_counts[i].cpu().numpy(), o.bin_counts)        # bit-exact bin indices
+    st = int(r.status[i])
+    if o.status == gp.OK and o.n_knots > 8:
+        assert st == 5                                                             # RDP_FRAME_NEEDS_KNOTS
+        return o
+    assert st == o.status, (st, o.status)
+    if o.status != gp.OK:
+        assert float(r.mean_curvature[i]) == 0.0 and float(r.max_curvature[i]) == 0.0
+        return o
+    E = int(r.n_edge[i])
+    assert E == o.n_edge
+    edge = r.edge_pixels[i, :E].cpu().numpy().astype(np.int64)
+    assert np.array_equal(edge, o.edge_pix)                                        # bit-exact selection and order
+    assert abs(float(r.fit_residual[i]) - o.fp) <= 1e-9 * max(o.fp, 1e-12)
+    assert abs(float(r.mean_curvature[i]) - o.mean_curvature) <= curv_rtol * abs(o.mean_curvature)
+    assert abs(float(r.max_curvature[i]) - o.max_curvature) <= curv_rtol * abs(o.max_curvature)
+    np.testing.assert_allclose(r.spline_points[i].cpu().numpy(), o.spline_points, rtol=0, atol=1e-10)
+    return o
+
+
+@pytest.mark.parametrize("flavour", ["f32", "u16"])
+def test_batch_matches_oracle(flavour):
+    frames = [synth.make_frame(30 + s, 240, 320, fill, flavour) for s, fill in enumerate([0.05, 0.15, 0.30, 0.45])]
+    r = _run(frames)
+    for i, f in enumerate(frames):
+        o = _check_frame(r, i, f)
+        assert o.status == gp.OK
+
+
+def test_matches_reference_golden_vectors(manifest, golden):
+    """Curvature within 1e-3 relative of what the unmodified reference returned (north_star bar); tie-free frames."""
+    for name, meta in manifest["cases"].items():
+        if meta["kind"] != "geometry" or meta["depth"] != "f32" or meta["n_knots"] != 8:
+            continue
+        g = golden(name)
+        f = synth.make_frame(meta["seed"], meta["H"], meta["W"], meta["fill"], meta["depth"])
+        r = _run([f])
+        assert int(r.status[0]) == 0 and int(r.n_points[0]) == meta["n_points"] and int(r.n_edge[0]) == meta["n_edge"]
+        assert abs(float(r.mean_curvature[0]) - meta["mean_curvature"]) <= 1e-3 * meta["mean_curvature"]
+        assert abs(float(r.max_curvature[0]) - meta["max_curvature"]) <= 1e-3 * meta["max_curvature"]
+        # in fact the agreement is far tighter than the bar
+        assert abs(float(r.mean_curvature[0]) - meta["mean_curvature"]) <= 1e-8 * meta["mean_curvature"]
+        np.testing.assert_allclose(r.spline_points[0].cpu().numpy(), g["spline_points"], rtol=0, atol=1e-9)
+        W = meta["W"]
+        edge = r.edge_pixels[0, : meta["n_edge"]].cpu().numpy().astype(np.int64)
+        pcd, pix = gp.deproject(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
+        lut = {int(p): j for j, p in enumerate(pix)}
+        pts = pcd[[lut[int(e)] for e in edge]]
+        assert np.array_equal(pts[np.lexsort((pts[:, 1], pts[:, 0]))], g["edge_sorted"]), name
+
+
+def test_degenerate_and_mixed_batch():
+    H, W = 120, 160
+    base = synth.make_frame(20, H, W, 0.3, "f32")
+    K = base["K"]
+
+    def fr(mask, depth):
+        return {"mask_gt": mask, "depth": depth, "K": K, "depth_scale": 1.0}
+
+    m99 = np.zeros((H, W), np.uint8); m99.reshape(-1)[np.flatnonzero(base["depth"].reshape(-1) > 0)[:99]] = 1
+    mcol = np.zeros((H, W), np.uint8); mcol[:, 80] = 1
+    dcol = base["depth"].copy(); dcol[:, 80] = 0.5
+    mrow = np.zeros((H, W), np.uint8); mrow[60, 10:150] = 1
+    frames = [
+        fr(np.zeros((H, W), np.uint8), base["depth"]),          # empty mask
+        fr(base["mask_gt"], np.zeros((H, W), np.float32)),      # all-zero depth
+        fr(m99, base["depth"]),                                 # 99 points
+        fr(mcol, dcol),                                         # single column, constant depth: bin width 0
+        fr(mrow, np.abs(base["depth"]) + 0.1),                  # 140 points -> tiny but valid fit
+        fr(base["mask_gt"], base["depth"]),                     # a normal frame in the same batch
+        fr(base["mask_gt"], np.where(base["depth"] > 0, np.float32(np.nan), base["depth"]).astype(np.float32)),  # NaN depth
+    ]
+    r = _run(frames)
+    want = [gp.TOO_FEW_POINTS, gp.TOO_FEW_POINTS, gp.TOO_FEW_POINTS, gp.DEGENERATE_BINS, gp.OK, gp.OK, gp.TOO_FEW_POINTS]
+    assert r.status.cpu().tolist() == want
+    for i, f in enumerate(frames[:6]):
+        _check_frame(r, i, f)
+
+
+def test_ragged_shape_and_scalar_path():
+    """H*W not a multiple of 16 takes the scalar load path; odd sizes must still be exact."""
+    f = synth.make_frame(41, 123, 187, 0.3, "u16")
+    r = _run([f, synth.make_frame(42, 123, 187, 0.2, "u16")])
+    _check_frame(r, 0, f)
+
+
+def test_numpy_promotion_modes():
+    f = synth.make_frame(43, 120, 160, 0.3, "f32")
+    f["depth_scale"] = 0.5
+    f["depth"] = (f["depth"] * 2).astype(np.float32)
+    _check_frame(_run([f]), 0, f)                       # float32 * python float -> float32 product
+    f2 = dict(f); f2["depth_scale"] = np.float64(0.5)
+    _check_frame(_run([f2]), 0, f2)                     # float32 * numpy float64 -> float64 product
+
+
+def test_large_bin_uses_global_paths():
+    """All points but one fall into a single x-bin: exercises the unstaged select and the global-memory sort."""
+    H, W = 480, 640
+    f = synth.make_frame(44, H, W, 0.5, "f32")
+    m = np.zeros((H, W), np.uint8); m[:, 200:420] = f["mask_gt"][:, 200:420]; m[240, 0] = 1
+    d = f["depth"].copy(); d[240, 0] = 0.4
+    f2 = {"mask_gt": m, "depth": d, "K": f["K"], "depth_scale": 1.0}
+    r = _run([f2])
+    o = gp.curvature_profile(m, d, f["K"], 1.0)
+    assert o.bin_counts.max() > 6144 and o.bin_k.max() > 2048
+    assert np.array_equal(r.bin_counts[0].cpu().numpy(), o.bin_counts)
+    E = int(r.n_edge[0])
+    assert E == o.n_edge and np.array_equal(r.edge_pixels[0, :E].cpu().numpy().astype(np.int64), o.edge_pix)
+
+
+def test_full_size_batch_properties():
+    """BASELINE config C2/C4 size (640x480, B=64): properties that need no oracle at this size."""
+    B, H, W = 64, 480, 640
+    frames = [synth.make_frame(100 + i, H, W, 0.15, "u16") for i in range(4)]
+    masks = torch.from_numpy(np.stack([f["mask_gt"] for f in frames])).cuda().repeat(B // 4, 1, 1)
+    depth = torch.from_numpy(np.stack([f["depth"] for f in frames])).cuda().repeat(B // 4, 1, 1)
+    from rdp_b200 import geometry
+    r = geometry.curvature_batch(masks, depth, frames[0]["K"], 0.001, want_points=True, want_edge=True, want_bins=True)
+    torch.cuda.synchronize()
+    assert (r.status == 0).all()
+    # identical frames give identical results wherever they sit in the batch (no cross-frame leakage)
+    for t in (r.mean_curvature, r.max_curvature, r.n_points, r.n_edge):
+        assert torch.equal(t.view(B // 4, 4), t[:4].expand(B // 4, 4))
+    assert torch.equal(r.bin_counts.sum(dim=1), r.n_points)
+    valid = ((masks > 0) & (depth.to(torch.int32) > 0)).flatten(1).sum(dim=1).to(torch.int32)
+    assert torch.equal(valid, r.n_points)
+    for i in range(4):
+        _check_frame(r, i, frames[i])
