@@ -93,6 +93,12 @@ int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fmt, int B, i
 /* Number of kernel launches one rdp_unet_forward call issues (for bench.py's gpu_launches). */
 int rdp_unet_launch_count(const RdpUnet* net);
 
+/* Measurement aid (no counterpart in the reference): the same forward with a CUDA event recorded on `stream` between
+ * launches; blocks until the call has finished and fills launch_ms (HOST, rdp_unet_launch_count entries) in launch
+ * order: im2col, inc.0, inc.3, then (maxpool, conv, conv) x4, then (upsample, conv, conv) x4. */
+int rdp_unet_forward_profiled(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
+                              uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);
+
 /* Debug / parity hook: copy of an intermediate activation as fp32 NCHW.  `index` = 0..17 (conv outputs in the
  * order of RdpUnetWeights.conv).  Must be called after rdp_unet_forward on the same workspace and stream. */
 int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,
@@ -125,6 +131,13 @@ int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, in
 
 /* Number of kernel launches (incl. the workspace memset) one rdp_geom_curvature call issues. */
 int rdp_geom_launch_count(void);
+
+/* Measurement aid (no counterpart in the reference): as rdp_geom_curvature, with a CUDA event between launches;
+ * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, bin_hist, bin_offsets,
+ * scatter, select_sort, fit. */
+int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                                const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
+                                void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);
 
 #ifdef __cplusplus
 }

@@ -95,15 +95,35 @@ def order_along_x(pcd, pix, rows):
     return rows[np.lexsort((pix[rows], pcd[rows, 0]))]
 
 
-def fit_spline(points, s=SMOOTH_S):
-    """(E,3) ordered points -> (t, c[3][n-4], fp, ier).  Raises ValueError like `splprep` on bad input."""
+def fit_spline(points, s=SMOOTH_S, fit="port"):
+    """(E,3) ordered points -> (t, c[3][n-4], fp, ier).  Raises ValueError like `splprep` on bad input.
+
+    fit="port" runs the FITPACK restatement in this directory; fit="scipy" makes the very call the reference makes
+    (`geometry_utils.py:78`) - used where the reference's *speed* is wanted (bench.py's CPU baseline).
+    """
+    if fit == "scipy":
+        import warnings
+        from scipy.interpolate import splprep
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            (tck, _u), fp, ier, _msg = splprep([points[:, 0], points[:, 1], points[:, 2]], s=s, k=3, full_output=1)
+        if ier > 3:
+            raise ValueError("Error on input data")
+        return np.asarray(tck[0]), np.asarray(tck[1]), fp, ier
     return fitpack_port.parcur(points, s=s)
 
 
-def curvature_of_spline(t, c, num=NUM_SAMPLES):
+def _splev(u, t, c, der, fit):
+    if fit == "scipy":
+        from scipy.interpolate import splev
+        return np.asarray(splev(u, (t, list(c), 3), der=der))
+    return fitpack_port.splev(u, t, c, der)
+
+
+def curvature_of_spline(t, c, num=NUM_SAMPLES, fit="port"):
     u = np.linspace(0.0, 1.0, num)
-    d1 = fitpack_port.splev(u, t, c, der=1)      # (3, num)
-    d2 = fitpack_port.splev(u, t, c, der=2)
+    d1 = _splev(u, t, c, 1, fit)      # (3, num)
+    d2 = _splev(u, t, c, 2, fit)
     cr = np.cross(d1.T, d2.T)
     n_cr = np.sqrt((cr * cr).sum(axis=1))
     n_d1 = np.sqrt((d1 * d1).sum(axis=0))
@@ -131,7 +151,7 @@ class Profile:
     tck: tuple | None = None
 
 
-def curvature_profile(mask, depth, K, depth_scale) -> Profile:
+def curvature_profile(mask, depth, K, depth_scale, fit="port") -> Profile:
     pcd, pix = deproject(mask, depth, K, depth_scale)
     out = Profile(n_points=int(pcd.shape[0]))
     if pcd.shape[0] < MIN_POINTS:
@@ -148,11 +168,11 @@ def curvature_profile(mask, depth, K, depth_scale) -> Profile:
     rows = order_along_x(pcd, pix, rows)
     out.edge_pix = pix[rows]
     try:
-        t, c, fp, ier = fit_spline(pcd[rows])
+        t, c, fp, ier = fit_spline(pcd[rows], fit=fit)
     except (TypeError, ValueError):
         out.status = FIT_INVALID
         return out
     out.tck, out.n_knots, out.fp, out.ier = (t, c, 3), int(t.shape[0]), float(fp), int(ier)
-    out.mean_curvature, out.max_curvature = curvature_of_spline(t, c)
-    out.spline_points = fitpack_port.splev(np.linspace(0.0, 1.0, NUM_SAMPLES), t, c).T.copy()
+    out.mean_curvature, out.max_curvature = curvature_of_spline(t, c, fit=fit)
+    out.spline_points = _splev(np.linspace(0.0, 1.0, NUM_SAMPLES), t, c, 0, fit).T.copy()
     return out

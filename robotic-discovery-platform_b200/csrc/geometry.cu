@@ -790,9 +790,9 @@ extern "C" int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes) {
 
 extern "C" int rdp_geom_launch_count(void) { return 7; }
 
-extern "C" int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
-                                  const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
-                                  void* workspace, size_t workspace_bytes, void* stream_) {
+static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                          const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
+                          void* workspace, size_t workspace_bytes, void* stream_, cudaEvent_t* marks) {
   RDP_REQUIRE(mask && depth && intrinsics && out && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_geom_curvature: null pointer");
   RDP_REQUIRE(B > 0 && H > 0 && W > 0, RDP_ERR_BAD_ARGUMENT, "rdp_geom_curvature: bad shape %dx%dx%d", B, H, W);
   RDP_REQUIRE((size_t)H * W < (1ull << 31) / 4, RDP_ERR_UNSUPPORTED, "rdp_geom_curvature: frame too large");
@@ -819,17 +819,52 @@ extern "C" int rdp_geom_curvature(const uint8_t* mask, const void* depth, int de
     RDP_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SELECT_SMEM));
     smem_opt_in = true;
   }
+  int n_marks = 0;
+  auto mark = [&]() {
+    if (marks) cudaEventRecord(marks[n_marks++], stream);
+  };
+  mark();
   RDP_CUDA_TRY(cudaMemsetAsync(workspace, 0, pl.header_bytes, stream));
+  mark();
   const bool vec = (p.P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
   const int tiles_total = B * pl.tiles;
   if (vec) k_deproject<true><<<tiles_total, DP_THREADS, 0, stream>>>(p);
   else k_deproject<false><<<tiles_total, DP_THREADS, 0, stream>>>(p);
+  mark();
   const dim3 pgrid((p.P + PT_PER_BLOCK - 1) / PT_PER_BLOCK, B);
   k_bin_hist<<<pgrid, PT_THREADS, 0, stream>>>(p);
+  mark();
   k_bin_offsets<<<(B + 63) / 64, 64, 0, stream>>>(p);
+  mark();
   k_scatter<<<pgrid, PT_THREADS, 0, stream>>>(p);
+  mark();
   k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, SELECT_SMEM, stream>>>(p);
+  mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
+  mark();
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
+}
+
+extern "C" int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                                  const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
+                                  void* workspace, size_t workspace_bytes, void* stream) {
+  return curvature_impl(mask, depth, depth_fmt, B, H, W, intrinsics, depth_scale, out, workspace, workspace_bytes, stream, nullptr);
+}
+
+extern "C" int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                                           const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
+                                           void* workspace, size_t workspace_bytes, void* stream, float* launch_ms) {
+  RDP_REQUIRE(launch_ms, RDP_ERR_BAD_ARGUMENT, "rdp_geom_curvature_profiled: launch_ms is null");
+  const int n = rdp_geom_launch_count();
+  cudaEvent_t ev[16];
+  for (int i = 0; i <= n; ++i) RDP_CUDA_TRY(cudaEventCreate(&ev[i]));
+  int rc = curvature_impl(mask, depth, depth_fmt, B, H, W, intrinsics, depth_scale, out, workspace, workspace_bytes, stream, ev);
+  if (rc == RDP_OK && cudaEventSynchronize(ev[n]) != cudaSuccess) {
+    set_error("rdp_geom_curvature_profiled: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = RDP_ERR_CUDA;
+  }
+  for (int i = 0; i < n && rc == RDP_OK; ++i) cudaEventElapsedTime(&launch_ms[i], ev[i], ev[i + 1]);
+  for (int i = 0; i <= n; ++i) cudaEventDestroy(ev[i]);
+  return rc;
 }

@@ -538,8 +538,8 @@ extern "C" int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W,
   return RDP_OK;
 }
 
-extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
-                                uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream_) {
+static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
+                        uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream_, cudaEvent_t* marks) {
   RDP_REQUIRE(net && input && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: null argument");
   RDP_REQUIRE(logits || mask, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: neither logits nor mask requested");
   RDP_REQUIRE(in_fmt == RDP_IN_RGB_U8_NHWC || in_fmt == RDP_IN_F32_NCHW, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: unknown input format %d", in_fmt);
@@ -550,10 +550,16 @@ extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fm
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
   auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
+  int n_marks = 0;
+  auto mark = [&]() {
+    if (marks) cudaEventRecord(marks[n_marks++], stream);
+  };
+  mark();
 
   {
     const size_t items = (size_t)B * H * W * 8;
     k_im2col_first<<<ew_grid(items), 256, 0, stream>>>(input, in_fmt, B, H, W, net->w.n_channels, buf.col);
+    mark();
   }
 
   // one conv launch: sources (src0 with c0 channels [+ src1 with c1 channels]) at level `lvl` -> act[i]
@@ -585,10 +591,12 @@ extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fm
     rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, p.tile_w, p.tile_h);
     if (rc != RDP_OK) return rc;
     switch (net->bn[i]) {
-      case 64: return launch_conv_bn<64>(m0, m1, net->wmap[i], p, net->num_sms, stream);
-      case 128: return launch_conv_bn<128>(m0, m1, net->wmap[i], p, net->num_sms, stream);
-      default: return launch_conv_bn<256>(m0, m1, net->wmap[i], p, net->num_sms, stream);
+      case 64: rc = launch_conv_bn<64>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+      case 128: rc = launch_conv_bn<128>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+      default: rc = launch_conv_bn<256>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
     }
+    mark();
+    return rc;
   };
 #define RDP_TRY(expr)          \
   do {                         \
@@ -604,6 +612,7 @@ extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fm
     const int C = net->w.conv[2 * d + 1].cout;
     const size_t items = (size_t)B * (L.H / 2) * (L.W / 2) * (C / 8);
     k_maxpool2<<<ew_grid(items), 256, 0, stream>>>(buf.act[2 * d + 1], B, L.H, L.W, C, buf.pool[d]);
+    mark();
     RDP_TRY(conv(2 * d + 2, buf.pool[d], C, nullptr, 0, 9));
     RDP_TRY(conv(2 * d + 3, buf.act[2 * d + 2], net->w.conv[2 * d + 2].cout, nullptr, 0, 9));
   }
@@ -616,12 +625,35 @@ extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fm
     const int dy = Ls.H - 2 * Ll.H, dx = Ls.W - 2 * Ll.W;
     const size_t items = (size_t)B * Ls.H * Ls.W * (Cl / 8);
     k_upsample2x<<<ew_grid(items), 256, 0, stream>>>(buf.act[low_i], B, Ll.H, Ll.W, Cl, Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
+    mark();
     RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, buf.up[j], Cl, 9));
     RDP_TRY(conv(11 + 2 * j, buf.act[10 + 2 * j], net->w.conv[10 + 2 * j].cout, nullptr, 0, 9));
   }
 #undef RDP_TRY
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
+}
+
+extern "C" int rdp_unet_forward(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
+                                uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream) {
+  return forward_impl(net, input, in_fmt, B, H, W, logits, mask, workspace, workspace_bytes, stream, nullptr);
+}
+
+extern "C" int rdp_unet_forward_profiled(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W,
+                                         float* logits, uint8_t* mask, void* workspace, size_t workspace_bytes,
+                                         void* stream, float* launch_ms) {
+  RDP_REQUIRE(launch_ms, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward_profiled: launch_ms is null");
+  const int n = rdp_unet_launch_count(net);
+  cudaEvent_t ev[64];
+  for (int i = 0; i <= n; ++i) RDP_CUDA_TRY(cudaEventCreate(&ev[i]));
+  int rc = forward_impl(net, input, in_fmt, B, H, W, logits, mask, workspace, workspace_bytes, stream, ev);
+  if (rc == RDP_OK && cudaEventSynchronize(ev[n]) != cudaSuccess) {
+    set_error("rdp_unet_forward_profiled: %s", cudaGetErrorString(cudaGetLastError()));
+    rc = RDP_ERR_CUDA;
+  }
+  for (int i = 0; i < n && rc == RDP_OK; ++i) cudaEventElapsedTime(&launch_ms[i], ev[i], ev[i + 1]);
+  for (int i = 0; i <= n; ++i) cudaEventDestroy(ev[i]);
+  return rc;
 }
 
 extern "C" int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,

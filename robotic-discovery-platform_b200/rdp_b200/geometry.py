@@ -15,6 +15,7 @@ from . import _lib
 
 NUM_SAMPLES = 100
 NUM_BINS = 50
+LAUNCH_NAMES = ["memset", "deproject", "bin_hist", "bin_offsets", "scatter", "select_sort", "fit"]
 
 
 @dataclass
@@ -49,7 +50,8 @@ def workspace_bytes(B: int, H: int, W: int) -> int:
 
 
 def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_scale, *, want_points=False,
-                    want_edge=False, want_bins=False, workspace=None, depth_fmt=None) -> CurvatureBatch:
+                    want_edge=False, want_bins=False, workspace=None, depth_fmt=None,
+                    launch_ms: list | None = None) -> CurvatureBatch:
     lib = _lib.load()
     if masks.device.type != "cuda" or depth.device != masks.device:
         raise _lib.RdpError("curvature_batch needs CUDA tensors on one device; there is no CPU path")
@@ -91,7 +93,12 @@ def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_
             res.bin_counts = torch.empty((B, NUM_BINS), dtype=torch.int32, device=dev)
             out.bin_counts = res.bin_counts.data_ptr()
         stream = torch.cuda.current_stream(dev).cuda_stream
-        _lib.check(lib.rdp_geom_curvature(masks.data_ptr(), depth.data_ptr(), fmt, B, H, W, k4, float(depth_scale),
-                                          C.byref(out), workspace.data_ptr(), workspace.numel(), stream),
-                   "rdp_geom_curvature")
+        args = (masks.data_ptr(), depth.data_ptr(), fmt, B, H, W, k4, float(depth_scale), C.byref(out),
+                workspace.data_ptr(), workspace.numel(), stream)
+        if launch_ms is None:
+            _lib.check(lib.rdp_geom_curvature(*args), "rdp_geom_curvature")
+        else:       # measurement aid: CUDA events between launches, blocks until done
+            buf = (C.c_float * lib.rdp_geom_launch_count())()
+            _lib.check(lib.rdp_geom_curvature_profiled(*args, buf), "rdp_geom_curvature_profiled")
+            launch_ms[:] = list(buf)
     return res

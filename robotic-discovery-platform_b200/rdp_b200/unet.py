@@ -79,7 +79,12 @@ class UnetEngine:
     def new_workspace(self, B: int, H: int, W: int) -> torch.Tensor:
         return torch.empty(self.workspace_bytes(B, H, W), dtype=torch.uint8, device=self.device)
 
-    def forward(self, x: torch.Tensor, *, want_logits: bool = True, want_mask: bool = False, workspace=None):
+    LAUNCH_NAMES = (["im2col", "conv inc.0", "conv inc.3"]
+                    + [f"{k} down{d}{s}" for d in range(1, 5) for k, s in (("maxpool", ""), ("conv", ".0"), ("conv", ".3"))]
+                    + [f"{k} up{u}{s}" for u in range(1, 5) for k, s in (("upsample", ""), ("conv", ".0"), ("conv", ".3"))])
+
+    def forward(self, x: torch.Tensor, *, want_logits: bool = True, want_mask: bool = False, workspace=None,
+                launch_ms: list | None = None):
         """x: (B,H,W,C) uint8 RGB or (B,C,H,W) float32, on the engine's device.
 
         Returns (logits fp32 (B,n_classes,H,W) or None, mask uint8 (B,n_classes,H,W) or None, workspace).
@@ -100,11 +105,16 @@ class UnetEngine:
             logits = torch.empty((B, self.n_classes, H, W), dtype=torch.float32, device=self.device) if want_logits else None
             mask = torch.empty((B, self.n_classes, H, W), dtype=torch.uint8, device=self.device) if want_mask else None
             stream = torch.cuda.current_stream(self.device).cuda_stream
-            _lib.check(self.lib.rdp_unet_forward(
-                self._handle, x.data_ptr(), fmt, B, H, W,
-                logits.data_ptr() if logits is not None else None,
-                mask.data_ptr() if mask is not None else None,
-                workspace.data_ptr(), workspace.numel(), stream), "rdp_unet_forward")
+            args = (self._handle, x.data_ptr(), fmt, B, H, W,
+                    logits.data_ptr() if logits is not None else None,
+                    mask.data_ptr() if mask is not None else None,
+                    workspace.data_ptr(), workspace.numel(), stream)
+            if launch_ms is None:
+                _lib.check(self.lib.rdp_unet_forward(*args), "rdp_unet_forward")
+            else:   # measurement aid: CUDA events between launches, blocks until done
+                buf = (C.c_float * self.launches_per_forward)()
+                _lib.check(self.lib.rdp_unet_forward_profiled(*args, buf), "rdp_unet_forward_profiled")
+                launch_ms[:] = list(buf)
         return logits, mask, workspace
 
     def read_activation(self, index: int, B: int, H: int, W: int, workspace: torch.Tensor) -> torch.Tensor:

@@ -128,7 +128,7 @@ def test_large_bin_uses_global_paths():
     H, W = 480, 640
     f = synth.make_frame(44, H, W, 0.5, "f32")
     m = np.zeros((H, W), np.uint8); m[:, 200:420] = f["mask_gt"][:, 200:420]; m[240, 0] = 1
-    d = f["depth"].copy(); d[240, 0] = 0.4
+    d = f["depth"].copy(); d[240, 0] = 30.0      # far outlier stretches the x range: the band collapses into bin 49
     f2 = {"mask_gt": m, "depth": d, "K": f["K"], "depth_scale": 1.0}
     r = _run([f2])
     o = gp.curvature_profile(m, d, f["K"], 1.0)
