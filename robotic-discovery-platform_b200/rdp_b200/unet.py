@@ -45,6 +45,8 @@ class UnetEngine:
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise _lib.RdpError("UnetEngine needs a CUDA device; there is no CPU path")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.n_channels, self.n_classes = n_channels, n_classes
         with torch.cuda.device(self.device):
             self._w, self._shift = fold_and_pack(state_dict, n_channels, self.device)
