@@ -18,6 +18,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -57,17 +58,118 @@ struct ConvParams {
   uint8_t* mask;
 };
 
+constexpr int AUX_SHIFT_FLOATS = 512;   // BN shift of every output channel of the layer
+constexpr int AUX_HEAD_FLOATS = 8 * 64;  // OutConv weights
+constexpr int AUX_BYTES = (AUX_SHIFT_FLOATS + AUX_HEAD_FLOATS + 8) * 4;
+
 template <int BN>
 struct ConvCfg {
   static constexpr int B_STAGE_BYTES = BN * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   static constexpr int STAGES = SMEM_BUDGET / STAGE_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
-  static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + AUX_BYTES;
 };
 
 // sigmoid(x) > 0.5 evaluated in fp32 as torch does: true from x = 1.5 * 2^-24 upwards (probed on torch 2.11 CPU)
 __device__ __forceinline__ bool mask_rule(float logit) { return logit > 8.940697e-8f; }
+
+
+// All threads: stage the per-channel shift (and the OutConv weights / bias) in shared memory once per CTA.
+__device__ __forceinline__ void stage_aux(const ConvParams& p, float* s_aux) {
+  for (int i = threadIdx.x; i < p.cout; i += blockDim.x) s_aux[i] = __ldg(p.shift + i);
+  if (p.head_w != nullptr) {
+    for (int i = threadIdx.x; i < p.n_classes * 64; i += blockDim.x) s_aux[AUX_SHIFT_FLOATS + i] = __ldg(p.head_w + i);
+    if (threadIdx.x < p.n_classes) s_aux[AUX_SHIFT_FLOATS + AUX_HEAD_FLOATS + threadIdx.x] = __ldg(p.head_b + threadIdx.x);
+  }
+}
+
+// two fp32 -> packed bf16x2 (lo = first element), optionally clamped at zero by the conversion itself
+template <bool RELU>
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  uint32_t d;
+  if (RELU) asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
+// Drains one 128 x BN fp32 accumulator tile: BN shift + ReLU -> bf16 NHWC store; for the last layer also the 1x1
+// OutConv (+ mask rule).  Thread = one pixel (TMEM lane); 32-column chunks, the next chunk's tcgen05.ld is in
+// flight while the current one is processed.
+template <int BN>
+__device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* s_aux, uint32_t taddr, int nt, int n, int y,
+                                              int x, bool inside, uint64_t* acc_empty_bar, int lane) {
+  const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
+  const bool head_on = BN == 64 && p.head_w != nullptr;
+  float head[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) head[c] = 0.f;
+  uint32_t r[2][32];
+  tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+  for (int c = 0; c < BN / 32; ++c) {
+    tmem_ld_wait();
+    if (c + 1 < BN / 32) tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+    const float4* sh4 = reinterpret_cast<const float4*>(s_aux + nt * BN + c * 32);
+    float v[32];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const float4 sh = sh4[q];
+      v[4 * q + 0] = __uint_as_float(r[c & 1][4 * q + 0]) + sh.x;
+      v[4 * q + 1] = __uint_as_float(r[c & 1][4 * q + 1]) + sh.y;
+      v[4 * q + 2] = __uint_as_float(r[c & 1][4 * q + 2]) + sh.z;
+      v[4 * q + 3] = __uint_as_float(r[c & 1][4 * q + 3]) + sh.w;
+    }
+    if (BN == 64 && head_on) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+#pragma unroll
+      for (int cls = 0; cls < 8; ++cls) {
+        if (cls < p.n_classes) {
+          const float4* hw4 = reinterpret_cast<const float4*>(s_aux + AUX_SHIFT_FLOATS + cls * 64 + c * 32);
+          float a = head[cls];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 w = hw4[q];
+            a = fmaf(v[4 * q + 0], w.x, a);
+            a = fmaf(v[4 * q + 1], w.y, a);
+            a = fmaf(v[4 * q + 2], w.z, a);
+            a = fmaf(v[4 * q + 3], w.w, a);
+          }
+          head[cls] = a;
+        }
+      }
+    }
+    if (inside && p.out != nullptr) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + pixel * p.cout + nt * BN + c * 32);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint4 o;
+        o.x = pack_bf16x2<true>(v[8 * q + 0], v[8 * q + 1]);
+        o.y = pack_bf16x2<true>(v[8 * q + 2], v[8 * q + 3]);
+        o.z = pack_bf16x2<true>(v[8 * q + 4], v[8 * q + 5]);
+        o.w = pack_bf16x2<true>(v[8 * q + 6], v[8 * q + 7]);
+        dst[q] = o;
+      }
+    }
+  }
+  // accumulator stage drained: hand it back to the MMA warp
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(acc_empty_bar);
+  if (BN == 64 && head_on && inside) {
+    const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
+#pragma unroll
+    for (int cls = 0; cls < 8; ++cls) {
+      if (cls < p.n_classes) {
+        const float logit = head[cls] + s_aux[AUX_SHIFT_FLOATS + AUX_HEAD_FLOATS + cls];
+        const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
+        if (p.logits) p.logits[o] = logit;
+        if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
+      }
+    }
+  }
+}
 
 template <int BN>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
@@ -84,9 +186,11 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
   uint64_t* acc_full = bars + 2 * Cfg::STAGES; // [2] MMA -> epilogue
   uint64_t* acc_empty = acc_full + 2;          // [2] epilogue -> MMA
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_steps = (p.kb0 + p.kb1) * p.taps;
+  stage_aux(p, s_aux);
 
   if (threadIdx.x == 0) {
     prefetch_tensormap(&map_src0);
@@ -172,67 +276,10 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
       const int n = m / p.tiles_y;
       const int y = ty * p.tile_h + row / p.tile_w, x = tx * p.tile_w + row % p.tile_w;
       const bool inside = y < p.H && x < p.W;
-      const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
-      float head[8];
-#pragma unroll
-      for (int c = 0; c < 8; ++c) head[c] = 0.f;
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c0, r);
-        tmem_ld_wait();
-        const float* sh = p.shift + nt * BN + c0;
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = fmaxf(__uint_as_float(r[j]) + __ldg(sh + j), 0.f);
-        if (BN == 64 && p.head_w != nullptr) {
-#pragma unroll
-          for (int cls = 0; cls < 8; ++cls) {
-            if (cls < p.n_classes) {
-              const float* hw = p.head_w + cls * 64 + c0;
-              float a = head[cls];
-#pragma unroll
-              for (int j = 0; j < 32; ++j) a = fmaf(v[j], __ldg(hw + j), a);
-              head[cls] = a;
-            }
-          }
-        }
-        if (inside && p.out != nullptr) {
-          uint4* dst = reinterpret_cast<uint4*>(p.out + pixel * p.cout + nt * BN + c0);
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            uint4 o;
-            __nv_bfloat162 t0 = __floats2bfloat162_rn(v[8 * q + 0], v[8 * q + 1]);
-            __nv_bfloat162 t1 = __floats2bfloat162_rn(v[8 * q + 2], v[8 * q + 3]);
-            __nv_bfloat162 t2 = __floats2bfloat162_rn(v[8 * q + 4], v[8 * q + 5]);
-            __nv_bfloat162 t3 = __floats2bfloat162_rn(v[8 * q + 6], v[8 * q + 7]);
-            o.x = *reinterpret_cast<uint32_t*>(&t0);
-            o.y = *reinterpret_cast<uint32_t*>(&t1);
-            o.z = *reinterpret_cast<uint32_t*>(&t2);
-            o.w = *reinterpret_cast<uint32_t*>(&t3);
-            dst[q] = o;
-          }
-        }
-      }
-      // accumulator stage drained: hand it back to the MMA warp
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&acc_empty[as]);
-      if (BN == 64 && p.head_w != nullptr && inside) {
-        const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
-#pragma unroll
-        for (int cls = 0; cls < 8; ++cls) {
-          if (cls < p.n_classes) {
-            const float logit = head[cls] + __ldg(p.head_b + cls);
-            const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
-            if (p.logits) p.logits[o] = logit;
-            if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
-          }
-        }
-      }
+      epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, &acc_empty[as], lane);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
@@ -242,6 +289,221 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// k_conv3x3_halo: the 3x3 convolution with the activation patch loaded ONCE per 64-channel block
+// ---------------------------------------------------------------------------------------------------------
+// The 9 taps of a 3x3 convolution read the same (tile_h+2) x (tile_w+2) halo patch shifted by one pixel.  With an
+// 8-wide tile the halo is 18 x 10 pixels x 128 bytes, laid out by one TMA box as 180 swizzled 128-byte rows
+// (row = hy*10 + hx).  For tap (dy,dx) the MMA's 8-row core groups are the 8 pixels of tile row ty, which sit at
+// byte offset ((ty+dy)*10 + dx) * 128: a descriptor with start = stage + (dy*10+dx)*128 and a stride of
+// 10 rows = 1280 bytes between groups addresses them in place.  The 128-byte swizzle is a function of the shared
+// memory address bits, so a start address that is not 1024-byte aligned needs no other adjustment.
+// L2 -> shared-memory traffic for A drops from 9 x 16 KB to 22.5 KB per channel block (6.4x).
+// Weights stay resident in shared memory for the whole kernel when all 9*Cin/64 slices fit (the 64-wide
+// full-resolution layers), otherwise they stream through their own ring, one 64-wide slice per tap.
+constexpr int HALO_W = 10, HALO_H = 18;
+constexpr int HALO_BYTES = HALO_W * HALO_H * 128;  // 23040
+constexpr int HALO_STRIDE = 23 * 1024;             // stage stride, keeps every stage 1024-byte aligned
+constexpr int HALO_SMEM_TOTAL = 227 * 1024;
+constexpr int HALO_MAX_STAGES = 12;
+constexpr int HALO_BAR_BYTES = 512 + AUX_BYTES;
+
+struct HaloCfg {
+  int sa, sb;  // A (halo) stages, B (weight slice) stages
+};
+
+// High word of a SWIZZLE_128B K-major descriptor: stride between 8-row groups, version 1, layout type 2.
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) { return (sbo_bytes >> 4) | (1u << 14) | (2u << 29); }
+// Low word: start address in 16-byte units (smem < 256 KB, so it fits 14 bits) and LBO = 1.
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr) { return (smem_addr >> 4) | (1u << 16); }
+__device__ __forceinline__ uint64_t desc_pack(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+
+
+// MMA issue loop of the halo kernel (one thread).  The issue loop is the critical path of the 64-wide layers (a
+// 128x64x16 MMA occupies the tensor pipe for only ~32-48 cycles), so descriptors are a constant high word plus
+// (base + immediate) low words, taps are unrolled, and when the TMEM allocation starts at column 0 (BASE0, the
+// usual case with one CTA per SM) the accumulator address is an immediate as well: the tile loop is unrolled
+// over the two accumulator stages.
+template <int BN, bool RESIDENT, bool BASE0>
+__device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg& cfg, uint8_t* smem_a, uint8_t* smem_b,
+                                              uint64_t* full_a, uint64_t* empty_a, uint64_t* full_b, uint64_t* empty_b,
+                                              uint64_t* w_full, uint64_t* acc_full, uint64_t* acc_empty, uint32_t tmem_base) {
+  constexpr int B_BLOCK = BN * BLOCK_K * 2;
+  constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
+  constexpr uint32_t hi_a = desc_hi(HALO_W * 128), hi_b = desc_hi(1024);
+  const int ncb = p.kb0 + p.kb1;
+  uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
+  const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
+  if (RESIDENT) {
+    mbar_wait(w_full, 0);
+    tc_fence_after();
+  }
+  int work = blockIdx.x;
+  while (work < p.total_work) {
+#pragma unroll
+    for (int as = 0; as < 2; ++as) {
+      if (work < p.total_work) {
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_acc = BASE0 ? (uint32_t)(as * BN) : tmem_base + as * BN;
+        for (int cb = 0; cb < ncb; ++cb) {
+          mbar_wait(&full_a[sa], pa);
+          tc_fence_after();
+          const uint32_t a_lo = a_lo0 + sa * (HALO_STRIDE >> 4);
+          const uint32_t bres_lo = b_lo0 + cb * (9 * B_BLOCK >> 4);
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            uint32_t b_lo;
+            if (RESIDENT) {
+              b_lo = bres_lo + tap * (B_BLOCK >> 4);
+            } else {
+              mbar_wait(&full_b[sb], pb);
+              tc_fence_after();
+              b_lo = b_lo0 + sb * (B_BLOCK >> 4);
+            }
+            const uint32_t at_lo = a_lo + ((tap / 3) * HALO_W + tap % 3) * 8;  // 128 bytes per halo row
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              mma_bf16_ss(tmem_acc, desc_pack(at_lo + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc,
+                          (cb | tap | k) != 0);
+            if (!RESIDENT) {
+              tc_commit(&empty_b[sb]);
+              if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
+            }
+          }
+          tc_commit(&empty_a[sa]);
+          if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+        }
+        tc_commit(&acc_full[as]);
+        work += gridDim.x;
+      }
+    }
+    aphase ^= 1;
+  }
+}
+
+template <int BN, bool RESIDENT>
+__global__ void __launch_bounds__(CONV_THREADS, 1)
+k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
+               const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
+  constexpr int B_BLOCK = BN * BLOCK_K * 2;  // one 64-wide weight slice
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int ncb = p.kb0 + p.kb1;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
+  const int b_bytes = RESIDENT ? 9 * ncb * B_BLOCK : cfg.sb * B_BLOCK;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + b_bytes);
+  uint64_t* full_a = bars;                          // [HALO_MAX_STAGES]
+  uint64_t* empty_a = bars + HALO_MAX_STAGES;       // [HALO_MAX_STAGES]
+  uint64_t* full_b = bars + 2 * HALO_MAX_STAGES;    // [HALO_MAX_STAGES]
+  uint64_t* empty_b = bars + 3 * HALO_MAX_STAGES;   // [HALO_MAX_STAGES]
+  uint64_t* w_full = bars + 4 * HALO_MAX_STAGES;    // [1]
+  uint64_t* acc_full = w_full + 1;                  // [2]
+  uint64_t* acc_empty = w_full + 3;                 // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 5);
+  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  stage_aux(p, s_aux);
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_src0);
+    prefetch_tensormap(&map_src1);
+    prefetch_tensormap(&map_w);
+    for (int s = 0; s < HALO_MAX_STAGES; ++s) {
+      mbar_init(&full_a[s], 1);
+      mbar_init(&empty_a[s], 1);
+      mbar_init(&full_b[s], 1);
+      mbar_init(&empty_b[s], 1);
+    }
+    mbar_init(w_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer =================
+      if (RESIDENT) {
+        mbar_arrive_expect_tx(w_full, 9 * ncb * B_BLOCK);
+        for (int cb = 0; cb < ncb; ++cb)
+          for (int tap = 0; tap < 9; ++tap)
+            tma_load_2d(smem_b + (cb * 9 + tap) * B_BLOCK, &map_w, tap * p.cin_pad + cb * BLOCK_K, 0, w_full);
+      }
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
+      for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+        const int nt = work % p.n_tiles;
+        int m = work / p.n_tiles;
+        const int tx = m % p.tiles_x; m /= p.tiles_x;
+        const int ty = m % p.tiles_y;
+        const int n = m / p.tiles_y;
+        const int x0 = tx * 8, y0 = ty * 16;
+        for (int cb = 0; cb < ncb; ++cb) {
+          const CUtensorMap* src = cb < p.kb0 ? &map_src0 : &map_src1;
+          const int c0 = (cb < p.kb0 ? cb : cb - p.kb0) * BLOCK_K;
+          mbar_wait(&empty_a[sa], pa ^ 1);
+          mbar_arrive_expect_tx(&full_a[sa], HALO_BYTES);
+          tma_load_4d(smem_a + sa * HALO_STRIDE, src, c0, x0 - 1, y0 - 1, n, &full_a[sa]);
+          if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+          if (!RESIDENT) {
+#pragma unroll 1
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(&empty_b[sb], pb ^ 1);
+              mbar_arrive_expect_tx(&full_b[sb], B_BLOCK);
+              tma_load_2d(smem_b + sb * B_BLOCK, &map_w, tap * p.cin_pad + cb * BLOCK_K, nt * BN, &full_b[sb]);
+              if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ================= MMA issuer =================
+      if (tmem_base == 0)
+        halo_mma_loop<BN, RESIDENT, true>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
+      else
+        halo_mma_loop<BN, RESIDENT, false>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
+    }
+  } else {
+    // ================= epilogue (warps 2..5) =================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    uint32_t as = 0, aphase = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+      const int nt = work % p.n_tiles;
+      int m = work / p.n_tiles;
+      const int tx = m % p.tiles_x; m /= p.tiles_x;
+      const int ty = m % p.tiles_y;
+      const int n = m / p.tiles_y;
+      const int y = ty * 16 + (row >> 3), x = tx * 8 + (row & 7);
+      const bool inside = y < p.H && x < p.W;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
+      epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, &acc_empty[as], lane);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
   }
 }
 
@@ -381,12 +643,12 @@ static EncodeTiledFn encode_fn() {
 }
 
 // 4-D map over an NHWC bf16 activation: dims (C, W, H, B), box (64, tile_w, tile_h, 1), 128-byte swizzle.
-static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int tile_w, int tile_h) {
+static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w, int box_h) {
   EncodeTiledFn fn = encode_fn();
   RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)tile_w, (cuuint32_t)tile_h, 1};
+  cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -481,6 +743,39 @@ int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorM
   return RDP_OK;
 }
 
+template <int BN, bool RESIDENT>
+int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p,
+                       const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
+    attr_set = true;
+  }
+  const int grid = p.total_work < num_sms ? p.total_work : num_sms;
+  k_conv3x3_halo<BN, RESIDENT><<<grid, CONV_THREADS, HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
+  return RDP_OK;
+}
+
+template <int BN>
+int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms,
+                     cudaStream_t stream) {
+  const int ncb = p.kb0 + p.kb1, b_block = BN * BLOCK_K * 2;
+  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES;
+  static const int env_sa = getenv("RDP_HALO_SA") ? atoi(getenv("RDP_HALO_SA")) : 0;
+  HaloCfg cfg{};
+  const int w_bytes = 9 * ncb * b_block;
+  if (p.n_tiles == 1 && w_bytes + 3 * HALO_STRIDE <= budget) {
+    cfg.sb = 0;
+    cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / HALO_STRIDE);
+    return launch_conv_halo_t<BN, true>(s0, s1, wm, p, cfg, num_sms, stream);
+  }
+  // streamed weights: a halo block lasts 9 taps, so few A stages suffice; the weight ring must cover the
+  // bandwidth-latency product of one 64-wide slice per tap
+  cfg.sa = env_sa ? env_sa : (BN == 256 ? 2 : 3);
+  cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * HALO_STRIDE) / b_block);
+  return launch_conv_halo_t<BN, false>(s0, s1, wm, p, cfg, num_sms, stream);
+}
+
 }  // namespace
 
 extern "C" int rdp_unet_create(const RdpUnetWeights* w, RdpUnet** out) {
@@ -549,6 +844,10 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_forward: workspace %zu < required %zu bytes", workspace_bytes, buf.bytes);
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
+  static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
+  // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
+  static const char* sel_env = getenv("RDP_CONV_SEL");
+  const char* sel = (sel_env && strlen(sel_env) == 18) ? sel_env : "1hhhhhhhhhhhhhhhhh";
   auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
   int n_marks = 0;
   auto mark = [&]() {
@@ -567,7 +866,9 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const Level L = buf.lv[kConvLevel[i]];
     ConvParams p{};
     p.B = B; p.H = L.H; p.W = L.W;
-    pick_tile(L.H, L.W, p.tile_w, p.tile_h);
+    const bool halo = taps == 9 && !force_v1 && sel[i] == 'h';
+    if (halo) { p.tile_w = 8; p.tile_h = 16; }
+    else pick_tile(L.H, L.W, p.tile_w, p.tile_h);
     p.tiles_x = (L.W + p.tile_w - 1) / p.tile_w;
     p.tiles_y = (L.H + p.tile_h - 1) / p.tile_h;
     p.cout = net->w.conv[i].cout;
@@ -586,10 +887,20 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       p.mask = mask;
     }
     CUtensorMap m0, m1;
-    int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, p.tile_w, p.tile_h);
+    const int box_w = halo ? HALO_W : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
+    int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
-    rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, p.tile_w, p.tile_h);
+    rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
+    if (halo) {
+      switch (net->bn[i]) {
+        case 64: rc = launch_conv_halo<64>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+        case 128: rc = launch_conv_halo<128>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+        default: rc = launch_conv_halo<256>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+      }
+      mark();
+      return rc;
+    }
     switch (net->bn[i]) {
       case 64: rc = launch_conv_bn<64>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
       case 128: rc = launch_conv_bn<128>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
