@@ -48,6 +48,8 @@ extern "C" {
 /* U-Net input formats */
 #define RDP_IN_RGB_U8_NHWC 0 /* (B,H,W,C) uint8, scaled by 1/255 on load (ToTensor, server.py:108) */
 #define RDP_IN_F32_NCHW 1    /* (B,C,H,W) float32, the tensor the reference module receives (server.py:121) */
+/* OR into in_fmt: also keep the last conv's activation in the workspace (only rdp_unet_read_activation(17) needs it) */
+#define RDP_IN_FLAG_KEEP_ACTIVATIONS 0x100
 
 int rdp_abi_version(void);
 const char* rdp_last_error(void);

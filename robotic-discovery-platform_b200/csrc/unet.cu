@@ -141,15 +141,16 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
       }
     }
     if (inside && p.out != nullptr) {
-      uint4* dst = reinterpret_cast<uint4*>(p.out + pixel * p.cout + nt * BN + c * 32);
+      // 32 bytes (one full DRAM sector) per store instruction
+      __nv_bfloat16* dst = p.out + pixel * p.cout + nt * BN + c * 32;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        uint4 o;
-        o.x = pack_bf16x2<true>(v[8 * q + 0], v[8 * q + 1]);
-        o.y = pack_bf16x2<true>(v[8 * q + 2], v[8 * q + 3]);
-        o.z = pack_bf16x2<true>(v[8 * q + 4], v[8 * q + 5]);
-        o.w = pack_bf16x2<true>(v[8 * q + 6], v[8 * q + 7]);
-        dst[q] = o;
+      for (int q = 0; q < 2; ++q) {
+        uint32_t o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = pack_bf16x2<true>(v[16 * q + 2 * e], v[16 * q + 2 * e + 1]);
+        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * q), "r"(o[0]), "r"(o[1]),
+                     "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
+                     : "memory");
       }
     }
   }
@@ -507,6 +508,166 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// k_conv_first: inc.0 (Cin = n_channels, K = 9*Cin <= 64) straight from the camera image
+// ---------------------------------------------------------------------------------------------------------
+// With 3 input channels the layer is bandwidth-bound (it reads 3 bytes and writes 128 bytes per pixel), so the
+// point is to never materialise an im2col matrix in HBM: twelve producer warps gather each pixel's 3x3xC
+// neighbourhood (uint8 -> x/255 -> bf16 through a 256-entry table, exactly ToTensor's division) and write it as one
+// 128-byte row of the swizzled A tile in shared memory; the tensor core multiplies by the resident 64x64 weight
+// block; the usual epilogue adds the BN shift, applies ReLU and stores bf16 NHWC.
+constexpr int FIRST_STAGES = 4;
+constexpr int FIRST_PRODUCER_WARPS = 12;  // three groups of 128 threads
+constexpr int FIRST_MMA_WARP = FIRST_PRODUCER_WARPS;
+constexpr int FIRST_THREADS = (FIRST_PRODUCER_WARPS + 1 + 4) * 32;
+constexpr int FIRST_SMEM = FIRST_STAGES * A_STAGE_BYTES + 64 * BLOCK_K * 2 + 1024 + 256 + AUX_BYTES + 512;
+
+template <int C, bool U8>
+__global__ void __launch_bounds__(FIRST_THREADS, 1)
+k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, const void* __restrict__ in) {
+  constexpr int BN = 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + FIRST_STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + BN * BLOCK_K * 2);
+  uint64_t* a_full = bars;                   // [FIRST_STAGES], 128 producer arrivals each
+  uint64_t* a_empty = bars + FIRST_STAGES;   // [FIRST_STAGES]
+  uint64_t* w_full = bars + 2 * FIRST_STAGES;
+  uint64_t* acc_full = w_full + 1;           // [2]
+  uint64_t* acc_empty = w_full + 3;          // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 5);
+  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
+  uint16_t* s_lut = reinterpret_cast<uint16_t*>(reinterpret_cast<uint8_t*>(s_aux) + AUX_BYTES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_w);
+    for (int s = 0; s < FIRST_STAGES; ++s) {
+      mbar_init(&a_full[s], 128);
+      mbar_init(&a_empty[s], 1);
+    }
+    mbar_init(w_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 4);
+    }
+    fence_mbar_init();
+  }
+  if (threadIdx.x < 256) {
+    const __nv_bfloat16 v = __float2bfloat16_rn(__fdiv_rn((float)threadIdx.x, 255.0f));  // ToTensor: uint8 / 255
+    s_lut[threadIdx.x] = *reinterpret_cast<const uint16_t*>(&v);
+  }
+  stage_aux(p, s_aux);
+  if (warp == FIRST_MMA_WARP) tmem_alloc(tmem_slot, 2 * BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp < FIRST_PRODUCER_WARPS) {
+    // ================= im2col producers: thread = one pixel row of the A tile =================
+    const int group = warp >> 2;                 // three groups of 128 threads take every third tile
+    const int r = (warp & 3) * 32 + lane;
+    const int ry = r / p.tile_w, rx = r % p.tile_w;
+    int it = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
+      if (it % 3 != group) continue;
+      const int stage = it % FIRST_STAGES;
+      const uint32_t phase = (uint32_t)(it / FIRST_STAGES) & 1u;
+      int m = work;
+      const int tx = m % p.tiles_x; m /= p.tiles_x;
+      const int ty = m % p.tiles_y;
+      const int n = m / p.tiles_y;
+      const int y = ty * p.tile_h + ry, x = tx * p.tile_w + rx;
+      uint16_t v[64];
+#pragma unroll
+      for (int k = 0; k < 64; ++k) v[k] = 0;
+      if (y < p.H && x < p.W) {
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+          if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+              if (U8) {
+                v[tap * C + c] = s_lut[__ldg((const uint8_t*)in + (((size_t)n * p.H + yy) * p.W + xx) * C + c)];
+              } else {
+                const __nv_bfloat16 b = __float2bfloat16_rn(__ldg((const float*)in + (((size_t)n * C + c) * p.H + yy) * p.W + xx));
+                v[tap * C + c] = *reinterpret_cast<const uint16_t*>(&b);
+              }
+            }
+          }
+        }
+      }
+      mbar_wait(&a_empty[stage], phase ^ 1);
+      uint8_t* rowp = smem_a + stage * A_STAGE_BYTES + r * 128;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        uint4 o;
+        o.x = (uint32_t)v[8 * j + 0] | ((uint32_t)v[8 * j + 1] << 16);
+        o.y = (uint32_t)v[8 * j + 2] | ((uint32_t)v[8 * j + 3] << 16);
+        o.z = (uint32_t)v[8 * j + 4] | ((uint32_t)v[8 * j + 5] << 16);
+        o.w = (uint32_t)v[8 * j + 6] | ((uint32_t)v[8 * j + 7] << 16);
+        *reinterpret_cast<uint4*>(rowp + ((j ^ (r & 7)) << 4)) = o;  // the 128-byte swizzle TMA would have applied
+      }
+      fence_proxy_async();  // generic-proxy writes -> visible to the tensor core's async proxy
+      mbar_arrive(&a_full[stage]);
+    }
+  } else if (warp == FIRST_MMA_WARP) {
+    if (lane == 0) {
+      // ================= weights + MMA issuer =================
+      mbar_arrive_expect_tx(w_full, BN * BLOCK_K * 2);
+      tma_load_2d(smem_b, &map_w, 0, 0, w_full);
+      mbar_wait(w_full, 0);
+      tc_fence_after();
+      constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
+      const uint64_t db = make_sw128_desc(smem_u32(smem_b));
+      uint32_t as = 0, aphase = 0;
+      int it = 0;
+      for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
+        const int stage = it % FIRST_STAGES;
+        const uint32_t phase = (uint32_t)(it / FIRST_STAGES) & 1u;
+        mbar_wait(&acc_empty[as], aphase ^ 1);
+        mbar_wait(&a_full[stage], phase);
+        tc_fence_after();
+        const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * A_STAGE_BYTES));
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) mma_bf16_ss(tmem_base + as * BN, da + 2 * k, db + 2 * k, idesc, k != 0);
+        tc_commit(&a_empty[stage]);
+        tc_commit(&acc_full[as]);
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue =================
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    uint32_t as = 0, aphase = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+      int m = work;
+      const int tx = m % p.tiles_x; m /= p.tiles_x;
+      const int ty = m % p.tiles_y;
+      const int n = m / p.tiles_y;
+      const int y = ty * p.tile_h + row / p.tile_w, x = tx * p.tile_w + row % p.tile_w;
+      const bool inside = y < p.H && x < p.W;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
+      epilogue_tile<BN>(p, s_aux, taddr, 0, n, y, x, inside, &acc_empty[as], lane);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == FIRST_MMA_WARP) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 2 * BN);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // bandwidth-bound helpers
 // ---------------------------------------------------------------------------------------------------------
@@ -552,63 +713,58 @@ __device__ __forceinline__ uint4 bf16x8_max(uint4 a, uint4 b) {
   return r;
 }
 
-// MaxPool2d(2) (segmentation_model.py:47) on NHWC bf16, 8 channels per thread.
-__global__ void __launch_bounds__(256) k_maxpool2(const __nv_bfloat16* in, int B, int H, int W, int C, __nv_bfloat16* out) {
-  const int Ho = H / 2, Wo = W / 2, C8 = C / 8;
-  const size_t total = (size_t)B * Ho * Wo * C8;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    size_t r = i / C8;
-    const int xo = (int)(r % Wo); r /= Wo;
-    const int yo = (int)(r % Ho);
-    const int n = (int)(r / Ho);
-    const uint4* src = reinterpret_cast<const uint4*>(in + (((size_t)n * H + 2 * yo) * W + 2 * xo) * C) + c8;
-    const size_t rowstride = (size_t)W * C8;
-    const uint4 a = __ldg(src), b = __ldg(src + C8), c = __ldg(src + rowstride), d = __ldg(src + rowstride + C8);
-    reinterpret_cast<uint4*>(out)[i] = bf16x8_max(bf16x8_max(a, b), bf16x8_max(c, d));
-  }
+// MaxPool2d(2) (segmentation_model.py:47) on NHWC bf16, 8 channels (16 bytes) per thread.
+// grid = (ceil(Wo*C8 / 256), Ho, B): no 64-bit divisions on the streaming path.
+__global__ void __launch_bounds__(256) k_maxpool2(const __nv_bfloat16* in, int H, int W, int C8, int c8_shift,
+                                                  __nv_bfloat16* out) {
+  const int Ho = H >> 1, Wo = W >> 1;
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= Wo * C8) return;
+  const int xo = c8_shift >= 0 ? t >> c8_shift : t / C8, c8 = t - xo * C8;
+  const int yo = blockIdx.y, n = blockIdx.z;
+  const uint4* src = reinterpret_cast<const uint4*>(in) + (((size_t)n * H + 2 * yo) * W + 2 * xo) * C8 + c8;
+  const size_t rowstride = (size_t)W * C8;
+  const uint4 a = __ldg(src), b = __ldg(src + C8), c = __ldg(src + rowstride), d = __ldg(src + rowstride + C8);
+  reinterpret_cast<uint4*>(out)[(((size_t)n * Ho + yo) * Wo + xo) * C8 + c8] = bf16x8_max(bf16x8_max(a, b), bf16x8_max(c, d));
 }
 
 // nn.Upsample(scale_factor=2, bilinear, align_corners=True) followed by the zero pad of Up.forward
 // (segmentation_model.py:61,68-74): (B,h,w,C) -> (B,Hs,Ws,C), interpolated values placed at offset (py, px).
-__global__ void __launch_bounds__(256) k_upsample2x(const __nv_bfloat16* in, int B, int h, int w, int C, int Hs, int Ws,
-                                                    int py, int px, __nv_bfloat16* out) {
-  const int Ho = 2 * h, Wo = 2 * w, C8 = C / 8;
+// grid = (ceil(Ws*C8 / 256), Hs, B).
+__global__ void __launch_bounds__(256) k_upsample2x(const __nv_bfloat16* in, int h, int w, int C8, int c8_shift, int Hs,
+                                                    int Ws, int py, int px, __nv_bfloat16* out) {
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= Ws * C8) return;
+  const int xs = c8_shift >= 0 ? t >> c8_shift : t / C8, c8 = t - xs * C8;
+  const int ys = blockIdx.y, n = blockIdx.z;
+  const int Ho = 2 * h, Wo = 2 * w;
   const float ry = Ho > 1 ? (float)(h - 1) / (float)(Ho - 1) : 0.f;
   const float rx = Wo > 1 ? (float)(w - 1) / (float)(Wo - 1) : 0.f;
-  const size_t total = (size_t)B * Hs * Ws * C8;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    size_t r = i / C8;
-    const int xs = (int)(r % Ws); r /= Ws;
-    const int ys = (int)(r % Hs);
-    const int n = (int)(r / Hs);
-    const int yo = ys - py, xo = xs - px;
-    uint4 o = make_uint4(0, 0, 0, 0);
-    if (yo >= 0 && yo < Ho && xo >= 0 && xo < Wo) {
-      const float fy = ry * (float)yo, fx = rx * (float)xo;
-      const int y0 = (int)fy, x0 = (int)fx;
-      const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
-      const float ly1 = fy - (float)y0, ly0 = 1.f - ly1, lx1 = fx - (float)x0, lx0 = 1.f - lx1;
-      const uint4* base = reinterpret_cast<const uint4*>(in + (size_t)n * h * w * C) + c8;
-      const uint4 v00 = __ldg(base + ((size_t)y0 * w + x0) * C8), v01 = __ldg(base + ((size_t)y0 * w + x1) * C8);
-      const uint4 v10 = __ldg(base + ((size_t)y1 * w + x0) * C8), v11 = __ldg(base + ((size_t)y1 * w + x1) * C8);
-      const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
-      const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&v01);
-      const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
-      const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
-      __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
+  const int yo = ys - py, xo = xs - px;
+  uint4 o = make_uint4(0, 0, 0, 0);
+  if (yo >= 0 && yo < Ho && xo >= 0 && xo < Wo) {
+    const float fy = ry * (float)yo, fx = rx * (float)xo;
+    const int y0 = (int)fy, x0 = (int)fx;
+    const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+    const float ly1 = fy - (float)y0, ly0 = 1.f - ly1, lx1 = fx - (float)x0, lx0 = 1.f - lx1;
+    const uint4* base = reinterpret_cast<const uint4*>(in) + (size_t)n * h * w * C8 + c8;
+    const uint4 v00 = __ldg(base + (y0 * w + x0) * C8), v01 = __ldg(base + (y0 * w + x1) * C8);
+    const uint4 v10 = __ldg(base + (y1 * w + x0) * C8), v11 = __ldg(base + (y1 * w + x1) * C8);
+    const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
+    const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&v01);
+    const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
+    const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
+    __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float2 fa = __bfloat1622float2(a[j]), fb = __bfloat1622float2(b[j]);
-        const float2 fc = __bfloat1622float2(c[j]), fd = __bfloat1622float2(d[j]);
-        const float r0 = ly0 * (lx0 * fa.x + lx1 * fb.x) + ly1 * (lx0 * fc.x + lx1 * fd.x);
-        const float r1 = ly0 * (lx0 * fa.y + lx1 * fb.y) + ly1 * (lx0 * fc.y + lx1 * fd.y);
-        po[j] = __floats2bfloat162_rn(r0, r1);
-      }
+    for (int j = 0; j < 4; ++j) {
+      const float2 fa = __bfloat1622float2(a[j]), fb = __bfloat1622float2(b[j]);
+      const float2 fc = __bfloat1622float2(c[j]), fd = __bfloat1622float2(d[j]);
+      const float r0 = ly0 * (lx0 * fa.x + lx1 * fb.x) + ly1 * (lx0 * fc.x + lx1 * fd.x);
+      const float r1 = ly0 * (lx0 * fa.y + lx1 * fb.y) + ly1 * (lx0 * fc.y + lx1 * fd.y);
+      po[j] = __floats2bfloat162_rn(r0, r1);
     }
-    reinterpret_cast<uint4*>(out)[i] = o;
   }
+  reinterpret_cast<uint4*>(out)[(((size_t)n * Hs + ys) * Ws + xs) * C8 + c8] = o;
 }
 
 // NHWC bf16 -> NCHW fp32 (parity hook, not on the hot path)
@@ -687,6 +843,12 @@ static void pick_tile(int H, int W, int& tw, int& th) {
 
 struct Level { int H, W; };
 
+static int log2_exact(int v) {  // shift for a power of two, -1 otherwise
+  int s = 0;
+  while ((1 << s) < v) ++s;
+  return (1 << s) == v ? s : -1;
+}
+
 }  // namespace unet
 }  // namespace rdp
 
@@ -741,6 +903,32 @@ int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorM
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
   k_conv3x3<BN><<<grid, CONV_THREADS, ConvCfg<BN>::SMEM_BYTES, stream>>>(s0, s1, wm, p);
   return RDP_OK;
+}
+
+template <int C, bool U8>
+int launch_conv_first_t(const CUtensorMap& wm, const ConvParams& p, const void* in, int num_sms, cudaStream_t stream) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv_first<C, U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FIRST_SMEM));
+    attr_set = true;
+  }
+  const int grid = p.total_work < num_sms ? p.total_work : num_sms;
+  k_conv_first<C, U8><<<grid, FIRST_THREADS, FIRST_SMEM, stream>>>(wm, p, in);
+  return RDP_OK;
+}
+
+// returns 1 when a specialised kernel exists for this channel count (else the im2col path is used)
+int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const ConvParams& p, const void* in, int num_sms,
+                      cudaStream_t stream, int* rc) {
+  switch (C * 2 + (u8 ? 1 : 0)) {
+    case 3: *rc = launch_conv_first_t<1, true>(wm, p, in, num_sms, stream); return 1;
+    case 2: *rc = launch_conv_first_t<1, false>(wm, p, in, num_sms, stream); return 1;
+    case 7: *rc = launch_conv_first_t<3, true>(wm, p, in, num_sms, stream); return 1;
+    case 6: *rc = launch_conv_first_t<3, false>(wm, p, in, num_sms, stream); return 1;
+    case 9: *rc = launch_conv_first_t<4, true>(wm, p, in, num_sms, stream); return 1;
+    case 8: *rc = launch_conv_first_t<4, false>(wm, p, in, num_sms, stream); return 1;
+    default: return 0;
+  }
 }
 
 template <int BN, bool RESIDENT>
@@ -837,6 +1025,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
                         uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream_, cudaEvent_t* marks) {
   RDP_REQUIRE(net && input && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: null argument");
   RDP_REQUIRE(logits || mask, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: neither logits nor mask requested");
+  const bool keep_all = (in_fmt & RDP_IN_FLAG_KEEP_ACTIVATIONS) != 0;
+  in_fmt &= ~RDP_IN_FLAG_KEEP_ACTIVATIONS;
   RDP_REQUIRE(in_fmt == RDP_IN_RGB_U8_NHWC || in_fmt == RDP_IN_F32_NCHW, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: unknown input format %d", in_fmt);
   RDP_REQUIRE(B > 0 && H >= 16 && W >= 16, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: bad shape %dx%dx%d (H, W >= 16)", B, H, W);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -844,6 +1034,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_forward: workspace %zu < required %zu bytes", workspace_bytes, buf.bytes);
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
+  static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
   static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
   static const char* sel_env = getenv("RDP_CONV_SEL");
@@ -855,7 +1046,30 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   };
   mark();
 
-  {
+  // first layer: fused gather + tensor-core kernel when the channel count has a specialisation (1, 3, 4);
+  // otherwise an explicit im2col buffer feeds the generic kernel.  Both occupy two launch slots.
+  bool first_fused = false;
+  if (!force_v1) {
+    ConvParams p{};
+    p.B = B; p.H = H; p.W = W;
+    pick_tile(H, W, p.tile_w, p.tile_h);
+    p.tiles_x = (W + p.tile_w - 1) / p.tile_w;
+    p.tiles_y = (H + p.tile_h - 1) / p.tile_h;
+    p.cout = 64; p.n_tiles = 1; p.kb0 = 1; p.taps = 1; p.cin_pad = 64;
+    p.total_work = B * p.tiles_y * p.tiles_x;
+    p.shift = net->w.conv[0].shift;
+    p.out = debug_nostore ? nullptr : buf.act[0];
+    int rc = RDP_OK;
+    mark();  // (slot of the im2col launch)
+    if (launch_conv_first(net->w.n_channels, in_fmt == RDP_IN_RGB_U8_NHWC, net->wmap[0], p, input, net->num_sms, stream, &rc)) {
+      if (rc != RDP_OK) return rc;
+      first_fused = true;
+      mark();
+    } else if (marks) {
+      --n_marks;
+    }
+  }
+  if (!first_fused) {
     const size_t items = (size_t)B * H * W * 8;
     k_im2col_first<<<ew_grid(items), 256, 0, stream>>>(input, in_fmt, B, H, W, net->w.n_channels, buf.col);
     mark();
@@ -878,8 +1092,9 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.cin_pad = net->cin_pad[i];
     p.total_work = B * p.tiles_y * p.tiles_x * p.n_tiles;
     p.shift = net->w.conv[i].shift;
-    p.out = buf.act[i];
+    p.out = debug_nostore ? nullptr : buf.act[i];
     if (i == 17) {
+      if (!keep_all) p.out = nullptr;  // nobody reads up4.3's activation: the head consumes it in registers
       p.head_w = net->w.outc_weight;
       p.head_b = net->w.outc_bias;
       p.n_classes = net->w.n_classes;
@@ -916,13 +1131,13 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   } while (0)
 
   // encoder: inc, down1..down4 (segmentation_model.py:110-114)
-  RDP_TRY(conv(0, buf.col, 64, nullptr, 0, 1));
+  if (!first_fused) RDP_TRY(conv(0, buf.col, 64, nullptr, 0, 1));
   RDP_TRY(conv(1, buf.act[0], 64, nullptr, 0, 9));
   for (int d = 0; d < 4; ++d) {
     const Level L = buf.lv[d];
     const int C = net->w.conv[2 * d + 1].cout;
-    const size_t items = (size_t)B * (L.H / 2) * (L.W / 2) * (C / 8);
-    k_maxpool2<<<ew_grid(items), 256, 0, stream>>>(buf.act[2 * d + 1], B, L.H, L.W, C, buf.pool[d]);
+    const int C8 = C / 8;
+    k_maxpool2<<<dim3(((L.W / 2) * C8 + 255) / 256, L.H / 2, B), 256, 0, stream>>>(buf.act[2 * d + 1], L.H, L.W, C8, log2_exact(C8), buf.pool[d]);
     mark();
     RDP_TRY(conv(2 * d + 2, buf.pool[d], C, nullptr, 0, 9));
     RDP_TRY(conv(2 * d + 3, buf.act[2 * d + 2], net->w.conv[2 * d + 2].cout, nullptr, 0, 9));
@@ -934,8 +1149,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const Level Ls = buf.lv[3 - j], Ll = buf.lv[4 - j];
     const int Cl = net->w.conv[low_i].cout, Cs = net->w.conv[skip_i].cout;
     const int dy = Ls.H - 2 * Ll.H, dx = Ls.W - 2 * Ll.W;
-    const size_t items = (size_t)B * Ls.H * Ls.W * (Cl / 8);
-    k_upsample2x<<<ew_grid(items), 256, 0, stream>>>(buf.act[low_i], B, Ll.H, Ll.W, Cl, Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
+    const int C8 = Cl / 8;
+    k_upsample2x<<<dim3((Ls.W * C8 + 255) / 256, Ls.H, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, log2_exact(C8), Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
     mark();
     RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, buf.up[j], Cl, 9));
     RDP_TRY(conv(11 + 2 * j, buf.act[10 + 2 * j], net->w.conv[10 + 2 * j].cout, nullptr, 0, 9));

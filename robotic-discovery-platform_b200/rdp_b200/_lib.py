@@ -12,6 +12,7 @@ OK = 0
 FRAME_OK, FRAME_TOO_FEW_POINTS, FRAME_DEGENERATE_BINS, FRAME_TOO_FEW_EDGE, FRAME_FIT_INVALID, FRAME_NEEDS_KNOTS = range(6)
 DEPTH_U16, DEPTH_F32, DEPTH_F32_WIDE = 0, 1, 2
 IN_RGB_U8_NHWC, IN_F32_NCHW = 0, 1
+IN_FLAG_KEEP_ACTIVATIONS = 0x100
 
 EXPORTS = [
     "rdp_abi_version", "rdp_last_error",

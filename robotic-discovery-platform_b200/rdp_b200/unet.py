@@ -86,7 +86,7 @@ class UnetEngine:
                     + [f"{k} up{u}{s}" for u in range(1, 5) for k, s in (("upsample", ""), ("conv", ".0"), ("conv", ".3"))])
 
     def forward(self, x: torch.Tensor, *, want_logits: bool = True, want_mask: bool = False, workspace=None,
-                launch_ms: list | None = None):
+                launch_ms: list | None = None, keep_activations: bool = False):
         """x: (B,H,W,C) uint8 RGB or (B,C,H,W) float32, on the engine's device.
 
         Returns (logits fp32 (B,n_classes,H,W) or None, mask uint8 (B,n_classes,H,W) or None, workspace).
@@ -100,6 +100,8 @@ class UnetEngine:
         else:
             raise _lib.RdpError(f"unsupported input {tuple(x.shape)} {x.dtype}")
         x = x.contiguous()
+        if keep_activations:        # parity hook: read_activation(17) needs the last layer's output stored
+            fmt |= _lib.IN_FLAG_KEEP_ACTIVATIONS
         with torch.cuda.device(self.device):
             need = self.workspace_bytes(B, H, W)
             if workspace is None or workspace.numel() < need:

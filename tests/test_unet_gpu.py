@@ -33,7 +33,7 @@ def test_layer_activations_random_weights():
     from rdp_b200.unet import UnetEngine
     eng = UnetEngine(sd, 3, 1, "cuda")
     rgb = torch.from_numpy(batch["rgb"]).cuda()
-    logits, mask, ws = eng.forward(rgb, want_logits=True, want_mask=True)
+    logits, mask, ws = eng.forward(rgb, want_logits=True, want_mask=True, keep_activations=True)
     taps = {}
     ref = unet_port.unet_forward(sd, unet_port.rgb_u8_to_input(batch["rgb"]), taps)
     for i, (conv, _, _, _) in enumerate(synth.unet_layer_table(3)):

@@ -27,7 +27,7 @@ def main():
     batch = synth.make_batch(range(B), H, W, 0.3, "u16")
     eng = UnetEngine(sd, 3, 1, dev)
     rgb = torch.from_numpy(batch["rgb"]).to(dev)
-    logits, mask, ws = eng.forward(rgb, want_logits=True, want_mask=True)
+    logits, mask, ws = eng.forward(rgb, want_logits=True, want_mask=True, keep_activations=True)
     torch.cuda.synchronize()
     print("forward done; logits range", float(logits.min()), float(logits.max()), "coverage", float(mask.float().mean()))
     acts = [eng.read_activation(i, B, H, W, ws) for i in range(18)]
