@@ -141,6 +141,32 @@ int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int dept
                                 const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
                                 void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);
 
+/* ------------------------------------------------------------------------------------------------------ */
+/* Deprojection without a workspace.  (No counterpart in the reference: it exists for hosts that cannot      */
+/* allocate device memory, not to mirror one of its functions; the arithmetic is _get_pcd_from_mask's.)      */
+/* ------------------------------------------------------------------------------------------------------ */
+
+/* For callers that may not call cudaMalloc - a server that reserved the whole GPU for its own pool and bans
+ * allocation on the request path, a control loop that cannot wait for (or survive the failure of) an allocation.
+ * The scratch the deprojection kernel needs lives in a fixed array inside the library instead of a workspace.
+ *
+ *   mask, depth, depth_fmt, intrinsics (host, 4 doubles), depth_scale: as for rdp_geom_curvature
+ *   points_xyz  [B][H*W][3] fp32   the point cloud, row-major pixel order        (output, device)
+ *   pixel_ids   [B][H*W]    uint32 flat pixel index v*W+u of every point         (output, device)
+ *   n_points    [B]         int32  number of valid points per frame              (output, device)
+ *
+ * Limits: at most 64 frames and at most 16384 tiles of 4096 pixels per call (B * ceil(H*W/4096)); larger batches
+ * are refused with RDP_ERR_UNSUPPORTED.  The array (about 200 KB) is held by every GPU that loads the library
+ * until the process exits.  The call itself performs no allocation of any kind.
+ *
+ * The first call on each device looks up the array's device address; make that first call with the device
+ * current and before any stream capture begins.  All calls share the array and each clears what it uses
+ * before running, so calls whose GPU work could overlap (different streams, different threads) race: keep them
+ * on one stream or wait for one to finish before issuing the next. */
+int rdp_geom_deproject_static(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                              const double* intrinsics, double depth_scale, float* points_xyz, uint32_t* pixel_ids,
+                              int32_t* n_points, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

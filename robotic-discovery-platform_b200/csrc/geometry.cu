@@ -17,6 +17,8 @@
 //   k_fit          latency     one CTA per frame: chord-length scan, 4x4 normal equations in fp64, curvature
 #include <stdarg.h>
 
+#include <mutex>
+
 #include "rdp_common.cuh"
 
 namespace rdp {
@@ -867,4 +869,101 @@ extern "C" int rdp_geom_curvature_profiled(const uint8_t* mask, const void* dept
   for (int i = 0; i < n && rc == RDP_OK; ++i) cudaEventElapsedTime(&launch_ms[i], ev[i], ev[i + 1]);
   for (int i = 0; i <= n; ++i) cudaEventDestroy(ev[i]);
   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// rdp_geom_deproject_static: the deprojection stage for callers that must not allocate device memory
+// ---------------------------------------------------------------------------------------------------------
+// Some hosts cannot hand this library a workspace: a serving process that gave every byte of device memory to
+// its own pool at start-up and forbids cudaMalloc on the request path, or a control loop that cannot absorb the
+// latency (or the failure) of an allocation.  For them the bookkeeping k_deproject needs - per-frame counters and
+// min/max, the look-back descriptors of the ordered compaction, the tile ticket - lives in the fixed array below
+// instead of a caller-provided workspace.  The caller passes only inputs and outputs.
+//
+// The array is part of the library image: every GPU that loads the library carries it until the process exits.
+// All calls share it and it keeps what the last call left behind, so each call clears the part it uses first
+// (stream-ordered), and two calls that overlap on the GPU would race: issue them on one stream, or otherwise make
+// sure one has finished before the next starts.
+constexpr int STATIC_MAX_FRAMES = 64;
+constexpr int STATIC_MAX_TILES = 16384;  // sum over the batch of ceil(H*W / 4096)
+constexpr size_t STATIC_SCRATCH_BYTES =
+    ((sizeof(rdp::geom::FrameState) * STATIC_MAX_FRAMES + 255) / 256) * 256 + sizeof(unsigned long long) * STATIC_MAX_TILES + 256;
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+namespace {
+
+__global__ void k_export_counts(const rdp::geom::FrameState* fs, int B, int32_t* n_points) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) n_points[b] = fs[b].n_points;
+}
+
+constexpr int STATIC_MAX_DEVICES = 64;
+
+// In host code `g_static_scratch` is only a handle for the runtime, not an address a kernel can use: the device
+// address has to be asked for, once per device, with that device current.
+int static_scratch_address(void** out) {
+  static void* cache[STATIC_MAX_DEVICES] = {};
+  static bool known[STATIC_MAX_DEVICES] = {};
+  static std::mutex lock;
+  int dev = 0;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  RDP_REQUIRE(dev >= 0 && dev < STATIC_MAX_DEVICES, RDP_ERR_UNSUPPORTED, "rdp_geom_deproject_static: device index %d out of range", dev);
+  std::lock_guard<std::mutex> guard(lock);
+  if (!known[dev]) {
+    void* ptr = nullptr;
+    RDP_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    cache[dev] = ptr;
+    known[dev] = true;
+  }
+  *out = cache[dev];
+  return RDP_OK;
+}
+
+}  // namespace
+
+extern "C" int rdp_geom_deproject_static(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
+                                         const double* intrinsics, double depth_scale, float* points_xyz,
+                                         uint32_t* pixel_ids, int32_t* n_points, void* stream_) {
+  RDP_REQUIRE(mask && depth && intrinsics && points_xyz && pixel_ids && n_points, RDP_ERR_BAD_ARGUMENT,
+              "rdp_geom_deproject_static: null pointer");
+  RDP_REQUIRE(B > 0 && H > 0 && W > 0, RDP_ERR_BAD_ARGUMENT, "rdp_geom_deproject_static: bad shape %dx%dx%d", B, H, W);
+  RDP_REQUIRE((size_t)H * W < (1ull << 31) / 4, RDP_ERR_UNSUPPORTED, "rdp_geom_deproject_static: frame too large");
+  RDP_REQUIRE(depth_fmt >= RDP_DEPTH_U16 && depth_fmt <= RDP_DEPTH_F32_WIDE, RDP_ERR_BAD_ARGUMENT,
+              "rdp_geom_deproject_static: unknown depth format %d", depth_fmt);
+  const int P = H * W;
+  const int tiles = (P + TILE_PX - 1) / TILE_PX;
+  RDP_REQUIRE(B <= STATIC_MAX_FRAMES && (long long)B * tiles <= STATIC_MAX_TILES, RDP_ERR_UNSUPPORTED,
+              "rdp_geom_deproject_static: batch of %d frames x %d tiles exceeds the built-in scratch (at most %d frames and "
+              "%d tiles of 4096 pixels per call); use rdp_geom_curvature with a workspace for larger batches",
+              B, tiles, STATIC_MAX_FRAMES, STATIC_MAX_TILES);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  void* scratch = nullptr;
+  const int rc = static_scratch_address(&scratch);
+  if (rc != RDP_OK) return rc;
+
+  Params p{};
+  Carver c(scratch);
+  p.fs = c.take<FrameState>(STATIC_MAX_FRAMES);
+  p.tile_state = c.take<unsigned long long>(STATIC_MAX_TILES);
+  p.ticket = c.take<unsigned int>(64);
+  // counters, look-back descriptors and the ticket must start at zero; the rest of the array is not read
+  RDP_CUDA_TRY(cudaMemsetAsync(p.fs, 0, sizeof(FrameState) * B, stream));
+  RDP_CUDA_TRY(cudaMemsetAsync(p.tile_state, 0, sizeof(unsigned long long) * (size_t)B * tiles, stream));
+  RDP_CUDA_TRY(cudaMemsetAsync(p.ticket, 0, sizeof(unsigned int), stream));
+  p.mask = mask;
+  p.depth = depth;
+  p.depth_fmt = depth_fmt;
+  p.B = B; p.H = H; p.W = W; p.P = P;
+  p.tiles = tiles;
+  p.fx = intrinsics[0]; p.fy = intrinsics[1]; p.cx = intrinsics[2]; p.cy = intrinsics[3];
+  p.scale = depth_scale;
+  p.scale_f32 = (float)depth_scale;
+  p.pix = pixel_ids;
+  p.out.points_xyz = points_xyz;
+  const bool vec = (P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
+  if (vec) k_deproject<true><<<B * tiles, DP_THREADS, 0, stream>>>(p);
+  else k_deproject<false><<<B * tiles, DP_THREADS, 0, stream>>>(p);
+  k_export_counts<<<(B + 63) / 64, 64, 0, stream>>>(p.fs, B, n_points);
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
 }
