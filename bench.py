@@ -279,27 +279,21 @@ def run_b200(args):
     value = world * B * args.steps / (ms * 1e-3)
 
     # ---- timed region 2: end to end from pinned host buffers through the public API ----
-    out_host = {k: torch.empty(s, dtype=d).pin_memory() for k, s, d in
-                (("mean", (B,), torch.float64), ("max", (B,), torch.float64), ("status", (B,), torch.int32),
-                 ("pts", (B, 100, 3), torch.float64))}
-    rgb_d, depth_d = torch.empty_like(dev_rgb[0]), torch.empty_like(dev_depth[0])
-
-    def e2e_step(i):
-        s = i % RING
-        rgb_d.copy_(host_rgb[s], non_blocking=True)
-        depth_d.copy_(host_depth[s], non_blocking=True)
-        r = step(i, rgb_d, depth_d)
-        out_host["mean"].copy_(r.mean_curvature, non_blocking=True)
-        out_host["max"].copy_(r.max_curvature, non_blocking=True)
-        out_host["status"].copy_(r.status, non_blocking=True)
-        out_host["pts"].copy_(r.spline_points, non_blocking=True)
-
-    e2e_step(0)
+    # FramePipeline = the per-GPU stream pipeline a user runs: H2D of micro-batch i+1 and D2H of i-1 overlap compute of i
+    from rdp_b200.pipeline import FramePipeline
+    pipe = FramePipeline(model, K, scale, B, H, W, depth_dtype=dev_depth[0].dtype, slots=2, device=dev)
+    pipe.submit(host_rgb[0], host_depth[0])
+    pipe.collect()
     barrier()
-    e0.record()
+    s_in, _, s_out = pipe.events()
+    e0.record(s_in)
     for i in range(args.steps):
-        e2e_step(i)
-    e1.record()
+        if pipe.in_flight == 2:
+            pipe.collect(copy=False)
+        pipe.submit(host_rgb[i % RING], host_depth[i % RING])
+    while pipe.in_flight:
+        last = pipe.collect(copy=False)
+    e1.record(s_out)
     barrier()
     ms_e2e = e0.elapsed_time(e1)
     if world > 1:
@@ -307,8 +301,8 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_e2e = float(t.item())
     e2e_value = world * B * args.steps / (ms_e2e * 1e-3)
-    h2d = int(host_rgb[0].numel() * 1 + host_depth[0].numel() * 2)
-    d2h = int(sum(t.numel() * t.element_size() for t in out_host.values()))
+    h2d, d2h = int(pipe.h2d_bytes), int(pipe.d2h_bytes)
+    e2e_ok = int((last["status"] == 0).sum())
 
     # ---- per-launch timing (CUDA events between launches on the launching stream), same inputs ----
     eng = model._engine_for(dev)
@@ -343,13 +337,15 @@ def run_b200(args):
                    "batch_per_gpu": B, "height": H, "width": W, "fill": FILL, "depth": "u16",
                    "weights": f"seeded random init (seed {WEIGHT_SEED}) with a planted colour path so that masks follow the object",
                    "parallelism": f"frames sharded over {world} GPU(s), no collective",
-                   "l2": f"ring of {RING} input batches ({RING * h2d / 1e6:.0f} MB) and {unet_ws.numel() / 1e9:.1f} GB of "
+                   "l2": f"ring of {RING} input batches ({RING * B * P * 5 / 1e6:.0f} MB) and {unet_ws.numel() / 1e9:.1f} GB of "
                          "activations per step, both larger than the 126 MB L2",
                    "frames_ok": int((status == 0).sum()), "mean_points_per_frame": n_points},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps,
-                "how": "pinned host rgb u8 + depth u16 -> H2D -> UNet.forward_mask -> curvature_batch -> D2H of mean/max/status/points"},
+                "frames_ok_last_batch": e2e_ok,
+                "how": "rdp_b200.pipeline.FramePipeline: pinned host rgb u8 + depth u16 -> H2D -> UNet.forward_mask -> "
+                       "curvature_batch -> D2H of mean/max/status/points, three streams, two slots"},
         "gpu_launches": int((eng.launches_per_forward + len(geometry.LAUNCH_NAMES) - 1) * args.steps),
         "roofline": {"bound": "tensor", "kernel": "k_conv3x3 (18 launches per step)", "achieved": conv_tflops,
                      "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": conv_tflops / peaks["tflops"], "traffic": None,
