@@ -132,6 +132,19 @@ class ClockSampler(threading.Thread):
 # --------------------------------------------------------------------------------------------------------------
 # CPU port of the reference (oracle) - only used by the cpu_baseline leg and --impl reference
 # --------------------------------------------------------------------------------------------------------------
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1; the reference arm is meant to use every host core, as the reference would."""
+    import torch
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        pass
+    if torch.get_num_threads() < n:
+        torch.set_num_threads(n)
+    return torch.get_num_threads()
+
+
 def cpu_reference_frames(sd, frames, K, scale):
     """Reference path as shipped: fp32 U-Net on all host threads, server mask rule, then per-frame geometry."""
     import torch
@@ -148,6 +161,7 @@ def cpu_reference_frames(sd, frames, K, scale):
 def time_cpu_reference(H, W, budget_s=15.0, max_frames=64):
     import torch
     from rdp_b200 import synth
+    use_all_host_threads()
     sd = synth.make_state_dict(WEIGHT_SEED, planted=True)
     frames = [synth.make_frame(1000 + i, H, W, FILL, "u16") for i in range(2)]
     K, scale = frames[0]["K"], frames[0]["depth_scale"]
@@ -173,6 +187,7 @@ def run_reference(args):
         return 0
     import torch
     from rdp_b200 import synth
+    use_all_host_threads()
     H, W = args.height, args.width
     sd = synth.make_state_dict(WEIGHT_SEED, planted=True)
     per_step = args.ref_frames
