@@ -56,6 +56,11 @@ struct ConvParams {
   int n_classes;
   float* logits;
   uint8_t* mask;
+  // fused bilinear x2 upsample of source 1 (Up blocks): the low-resolution tensor the interpolation reads
+  const __nv_bfloat16* low;  // (B, low_h, low_w, kb1*64) NHWC, null when source 1 is a plain tensor map
+  int low_h, low_w;
+  int pad_y, pad_x;          // offset of the interpolated image inside the skip-sized frame (Up.forward's F.pad)
+  float ry, rx;              // align_corners=True scales (h-1)/(2h-1), (w-1)/(2w-1)
 };
 
 constexpr int AUX_SHIFT_FLOATS = 512;   // BN shift of every output channel of the layer
@@ -387,8 +392,55 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
   }
 }
 
-template <int BN, bool RESIDENT>
-__global__ void __launch_bounds__(CONV_THREADS, 1)
+constexpr int INTERP_WARPS = 4;
+constexpr int CONV_THREADS_INTERP = CONV_THREADS + INTERP_WARPS * 32;
+
+// Low-resolution source patch of one halo block: 18x10 output pixels at x2 span at most 11x7 source pixels.
+constexpr int PATCH_W = 7, PATCH_H = 11;
+constexpr int PATCH_BYTES = PATCH_W * PATCH_H * 128;  // 9856
+constexpr int PATCH_STRIDE = 10 * 1024;
+constexpr int PATCH_STAGES = 2;
+
+// Bilinear x2 (align_corners=True) + zero pad of one 16-byte chunk (8 channels) of one halo pixel, read from the
+// source patch in shared memory, in the same fp32 operation order as k_upsample2x, so that fusing the interpolation
+// into the convolution changes no bit.
+__device__ __forceinline__ uint4 interp_chunk(const ConvParams& p, const uint8_t* patch, int sy0, int sx0, int ys, int xs, int j) {
+  uint4 o = make_uint4(0, 0, 0, 0);
+  const int yo = ys - p.pad_y, xo = xs - p.pad_x;
+  if (ys < 0 || ys >= p.H || xs < 0 || xs >= p.W || yo < 0 || yo >= 2 * p.low_h || xo < 0 || xo >= 2 * p.low_w) return o;
+  const int h = p.low_h, w = p.low_w;
+  const float fy = p.ry * (float)yo, fx = p.rx * (float)xo;
+  const int y0 = (int)fy, x0 = (int)fx;
+  const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
+  const float ly1 = fy - (float)y0, ly0 = 1.f - ly1, lx1 = fx - (float)x0, lx0 = 1.f - lx1;
+  const uint4* base = reinterpret_cast<const uint4*>(patch) + j;
+  const int r0 = (y0 - sy0) * PATCH_W - sx0, r1 = (y1 - sy0) * PATCH_W - sx0;
+  const uint4 v00 = base[(r0 + x0) * 8], v01 = base[(r0 + x1) * 8];
+  const uint4 v10 = base[(r1 + x0) * 8], v11 = base[(r1 + x1) * 8];
+  const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
+  const __nv_bfloat162* b = reinterpret_cast<const __nv_bfloat162*>(&v01);
+  const __nv_bfloat162* c = reinterpret_cast<const __nv_bfloat162*>(&v10);
+  const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&v11);
+  __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float2 fa = __bfloat1622float2(a[q]), fb = __bfloat1622float2(b[q]);
+    const float2 fc = __bfloat1622float2(c[q]), fd = __bfloat1622float2(d[q]);
+    const float e0 = ly0 * (lx0 * fa.x + lx1 * fb.x) + ly1 * (lx0 * fc.x + lx1 * fd.x);
+    const float e1 = ly0 * (lx0 * fa.y + lx1 * fb.y) + ly1 * (lx0 * fc.y + lx1 * fd.y);
+    po[q] = __floats2bfloat162_rn(e0, e1);
+  }
+  return o;
+}
+
+// first source row / column a tile's halo needs (monotone in the output coordinate, so it matches interp_chunk)
+__device__ __forceinline__ int patch_origin(float r, int first_out, int pad) {
+  const int o = first_out - pad;
+  return (int)(r * (float)(o > 0 ? o : 0));
+}
+
+template <int BN, bool RESIDENT, bool INTERP>
+__global__ void __launch_bounds__(INTERP ? CONV_THREADS_INTERP : CONV_THREADS, 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
                const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
   constexpr int B_BLOCK = BN * BLOCK_K * 2;  // one 64-wide weight slice
@@ -398,7 +450,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
   const int b_bytes = RESIDENT ? 9 * ncb * B_BLOCK : cfg.sb * B_BLOCK;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + b_bytes);
+  uint8_t* smem_l = smem_b + b_bytes;  // low-resolution source patches (INTERP only)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_l + (INTERP ? PATCH_STAGES * PATCH_STRIDE : 0));
   uint64_t* full_a = bars;                          // [HALO_MAX_STAGES]
   uint64_t* empty_a = bars + HALO_MAX_STAGES;       // [HALO_MAX_STAGES]
   uint64_t* full_b = bars + 2 * HALO_MAX_STAGES;    // [HALO_MAX_STAGES]
@@ -406,7 +459,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint64_t* w_full = bars + 4 * HALO_MAX_STAGES;    // [1]
   uint64_t* acc_full = w_full + 1;                  // [2]
   uint64_t* acc_empty = w_full + 3;                 // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 5);
+  uint64_t* full_l = w_full + 5;                    // [PATCH_STAGES]
+  uint64_t* empty_l = w_full + 5 + PATCH_STAGES;    // [PATCH_STAGES]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 5 + 2 * PATCH_STAGES);
   float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -427,6 +482,10 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], 4);
     }
+    for (int s = 0; s < PATCH_STAGES; ++s) {
+      mbar_init(&full_l[s], 1);
+      mbar_init(&empty_l[s], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
@@ -444,7 +503,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
           for (int tap = 0; tap < 9; ++tap)
             tma_load_2d(smem_b + (cb * 9 + tap) * B_BLOCK, &map_w, tap * p.cin_pad + cb * BLOCK_K, 0, w_full);
       }
-      uint32_t sa = 0, pa = 0, sb = 0, pb = 0;
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, sl = 0, pl = 0;
       for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
         const int nt = work % p.n_tiles;
         int m = work / p.n_tiles;
@@ -452,12 +511,30 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         const int ty = m % p.tiles_y;
         const int n = m / p.tiles_y;
         const int x0 = tx * 8, y0 = ty * 16;
+        // INTERP: source patches of the interpolated blocks, PATCH_STAGES ahead of the block being consumed (a patch
+        // slot frees when the interpolation warps finish a block, which never depends on loads not yet issued)
+        const int sy0 = INTERP ? patch_origin(p.ry, y0 - 1, p.pad_y) : 0, sx0 = INTERP ? patch_origin(p.rx, x0 - 1, p.pad_x) : 0;
+        int next_patch = p.kb0;
+        auto issue_patch = [&]() {
+          mbar_wait(&empty_l[sl], pl ^ 1);
+          mbar_arrive_expect_tx(&full_l[sl], PATCH_BYTES);
+          tma_load_4d(smem_l + sl * PATCH_STRIDE, &map_src1, (next_patch - p.kb0) * BLOCK_K, sx0, sy0, n, &full_l[sl]);
+          if (++sl == PATCH_STAGES) { sl = 0; pl ^= 1; }
+          ++next_patch;
+        };
+        if (INTERP) {
+          for (int i = 0; i < PATCH_STAGES && next_patch < ncb; ++i) issue_patch();
+        }
         for (int cb = 0; cb < ncb; ++cb) {
           const CUtensorMap* src = cb < p.kb0 ? &map_src0 : &map_src1;
           const int c0 = (cb < p.kb0 ? cb : cb - p.kb0) * BLOCK_K;
+          // Every party that walks the ring waits for every stage, also the ones it does not fill: parity waits only
+          // tell adjacent phases apart, so nobody may run more than one round ahead of the consumer.
           mbar_wait(&empty_a[sa], pa ^ 1);
-          mbar_arrive_expect_tx(&full_a[sa], HALO_BYTES);
-          tma_load_4d(smem_a + sa * HALO_STRIDE, src, c0, x0 - 1, y0 - 1, n, &full_a[sa]);
+          if (!INTERP || cb < p.kb0) {  // with INTERP the interpolation warps fill the stages of source 1
+            mbar_arrive_expect_tx(&full_a[sa], HALO_BYTES);
+            tma_load_4d(smem_a + sa * HALO_STRIDE, src, c0, x0 - 1, y0 - 1, n, &full_a[sa]);
+          }
           if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
           if (!RESIDENT) {
 #pragma unroll 1
@@ -468,6 +545,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
               if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
             }
           }
+          if (INTERP && cb >= p.kb0 && next_patch < ncb) issue_patch();
         }
       }
     }
@@ -478,6 +556,40 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         halo_mma_loop<BN, RESIDENT, true>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
       else
         halo_mma_loop<BN, RESIDENT, false>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
+    }
+  } else if (INTERP && warp >= 6) {
+    // ================= interpolation producers (warps 6..9): halo blocks of the upsampled branch =================
+    const int t = threadIdx.x - 6 * 32;   // 0..127
+    const int j = t & 7;                  // 16-byte chunk (8 channels) this thread owns
+    uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+      int m = work / p.n_tiles;
+      const int tx = m % p.tiles_x; m /= p.tiles_x;
+      const int ty = m % p.tiles_y;
+      const int x0 = tx * 8 - 1, y0 = ty * 16 - 1;
+      const int sy0 = patch_origin(p.ry, y0, p.pad_y), sx0 = patch_origin(p.rx, x0, p.pad_x);
+      for (int cb = 0; cb < ncb; ++cb) {
+        mbar_wait(&empty_a[sa], pa ^ 1);  // also for stages the TMA thread fills (see the producer's note)
+        if (cb >= p.kb0) {
+          mbar_wait(&full_l[sl], pl);
+          uint8_t* stage = smem_a + sa * HALO_STRIDE;
+          const uint8_t* patch = smem_l + sl * PATCH_STRIDE;
+#pragma unroll 4
+          for (int px = t >> 3; px < HALO_W * HALO_H; px += 16) {
+            const int hy = px / HALO_W, hx = px - hy * HALO_W;
+            const uint4 v = interp_chunk(p, patch, sy0, sx0, y0 + hy, x0 + hx, j);
+            *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;  // TMA's 128-byte swizzle
+          }
+          fence_proxy_async();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (t == 0) {
+            mbar_arrive(&full_a[sa]);
+            mbar_arrive(&empty_l[sl]);
+          }
+          if (++sl == PATCH_STAGES) { sl = 0; pl ^= 1; }
+        }
+        if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+      }
     }
   } else {
     // ================= epilogue (warps 2..5) =================
@@ -799,7 +911,8 @@ static EncodeTiledFn encode_fn() {
 }
 
 // 4-D map over an NHWC bf16 activation: dims (C, W, H, B), box (64, tile_w, tile_h, 1), 128-byte swizzle.
-static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w, int box_h) {
+static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w, int box_h,
+                        bool swizzle = true) {
   EncodeTiledFn fn = encode_fn();
   RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
@@ -807,8 +920,8 @@ static int make_act_map(CUtensorMap* m, const void* ptr, int B, int H, int W, in
   cuuint32_t box[4] = {BLOCK_K, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(activation %dx%dx%dx%d) failed: %d", B, H, W, C, (int)r);
   return RDP_OK;
 }
@@ -931,16 +1044,16 @@ int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const ConvParams& p
   }
 }
 
-template <int BN, bool RESIDENT>
+template <int BN, bool RESIDENT, bool INTERP>
 int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p,
                        const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
     attr_set = true;
   }
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
-  k_conv3x3_halo<BN, RESIDENT><<<grid, CONV_THREADS, HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
+  k_conv3x3_halo<BN, RESIDENT, INTERP><<<grid, INTERP ? CONV_THREADS_INTERP : CONV_THREADS, HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
   return RDP_OK;
 }
 
@@ -948,20 +1061,22 @@ template <int BN>
 int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms,
                      cudaStream_t stream) {
   const int ncb = p.kb0 + p.kb1, b_block = BN * BLOCK_K * 2;
-  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES;
+  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (p.low ? PATCH_STAGES * PATCH_STRIDE : 0);
   static const int env_sa = getenv("RDP_HALO_SA") ? atoi(getenv("RDP_HALO_SA")) : 0;
   HaloCfg cfg{};
   const int w_bytes = 9 * ncb * b_block;
-  if (p.n_tiles == 1 && w_bytes + 3 * HALO_STRIDE <= budget) {
+  if (p.n_tiles == 1 && w_bytes + (p.low ? 2 : 3) * HALO_STRIDE <= budget) {
     cfg.sb = 0;
     cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / HALO_STRIDE);
-    return launch_conv_halo_t<BN, true>(s0, s1, wm, p, cfg, num_sms, stream);
+    return p.low ? launch_conv_halo_t<BN, true, true>(s0, s1, wm, p, cfg, num_sms, stream)
+                 : launch_conv_halo_t<BN, true, false>(s0, s1, wm, p, cfg, num_sms, stream);
   }
   // streamed weights: a halo block lasts 9 taps, so few A stages suffice; the weight ring must cover the
   // bandwidth-latency product of one 64-wide slice per tap
   cfg.sa = env_sa ? env_sa : (BN == 256 ? 2 : 3);
   cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * HALO_STRIDE) / b_block);
-  return launch_conv_halo_t<BN, false>(s0, s1, wm, p, cfg, num_sms, stream);
+  return p.low ? launch_conv_halo_t<BN, false, true>(s0, s1, wm, p, cfg, num_sms, stream)
+               : launch_conv_halo_t<BN, false, false>(s0, s1, wm, p, cfg, num_sms, stream);
 }
 
 }  // namespace
@@ -1035,6 +1150,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
   static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
+  static const bool fuse_all_up = getenv("RDP_FUSE_ALL_UP") != nullptr;
+  static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
   static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
   static const char* sel_env = getenv("RDP_CONV_SEL");
@@ -1076,7 +1193,9 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   }
 
   // one conv launch: sources (src0 with c0 channels [+ src1 with c1 channels]) at level `lvl` -> act[i]
-  auto conv = [&](int i, const __nv_bfloat16* src0, int c0, const __nv_bfloat16* src1, int c1, int taps) -> int {
+  struct LowSrc { const __nv_bfloat16* ptr; int h, w, pad_y, pad_x; };
+  auto conv = [&](int i, const __nv_bfloat16* src0, int c0, const __nv_bfloat16* src1, int c1, int taps,
+                  const LowSrc* low = nullptr) -> int {
     const Level L = buf.lv[kConvLevel[i]];
     ConvParams p{};
     p.B = B; p.H = L.H; p.W = L.W;
@@ -1101,11 +1220,19 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       p.logits = logits;
       p.mask = mask;
     }
+    if (low) {
+      p.low = low->ptr;
+      p.low_h = low->h; p.low_w = low->w;
+      p.pad_y = low->pad_y; p.pad_x = low->pad_x;
+      p.ry = 2 * low->h > 1 ? (float)(low->h - 1) / (float)(2 * low->h - 1) : 0.f;
+      p.rx = 2 * low->w > 1 ? (float)(low->w - 1) / (float)(2 * low->w - 1) : 0.f;
+    }
     CUtensorMap m0, m1;
     const int box_w = halo ? HALO_W : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
     int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
-    rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
+    if (low) rc = make_act_map(&m1, low->ptr, B, low->h, low->w, c1, PATCH_W, PATCH_H, /*swizzle=*/false);
+    else rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
     if (halo) {
       switch (net->bn[i]) {
@@ -1150,9 +1277,18 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const int Cl = net->w.conv[low_i].cout, Cs = net->w.conv[skip_i].cout;
     const int dy = Ls.H - 2 * Ll.H, dx = Ls.W - 2 * Ll.W;
     const int C8 = Cl / 8;
-    k_upsample2x<<<dim3((Ls.W * C8 + 255) / 256, Ls.H, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, log2_exact(C8), Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
-    mark();
-    RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, buf.up[j], Cl, 9));
+    // up4.0 (64 output channels) has too little MMA time per block to hide the interpolation: it keeps the copy
+    const bool fuse_up = !force_v1 && !no_fuse_up && sel[10 + 2 * j] == 'h' && (net->bn[10 + 2 * j] >= 128 || fuse_all_up);
+    if (fuse_up) {
+      // the convolution's interpolation warps read the low-resolution tensor directly: no upsampled copy in HBM
+      mark();
+      const LowSrc low{buf.act[low_i], Ll.H, Ll.W, dy / 2, dx / 2};
+      RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, nullptr, Cl, 9, &low));
+    } else {
+      k_upsample2x<<<dim3((Ls.W * C8 + 255) / 256, Ls.H, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, log2_exact(C8), Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
+      mark();
+      RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, buf.up[j], Cl, 9));
+    }
     RDP_TRY(conv(11 + 2 * j, buf.act[10 + 2 * j], net->w.conv[10 + 2 * j].cout, nullptr, 0, 9));
   }
 #undef RDP_TRY
