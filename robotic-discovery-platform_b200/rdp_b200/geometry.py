@@ -15,7 +15,7 @@ from . import _lib
 
 NUM_SAMPLES = 100
 NUM_BINS = 50
-LAUNCH_NAMES = ["memset", "deproject", "bin_hist", "bin_offsets", "scatter", "select_sort", "fit"]
+LAUNCH_NAMES = ["memset", "deproject", "bin_hist", "bin_offsets", "scatter", "select_sort", "fit", "fit_knots"]
 
 
 @dataclass
@@ -27,6 +27,8 @@ class CurvatureBatch:
     n_points: torch.Tensor         # (B,) i32
     n_edge: torch.Tensor           # (B,) i32
     fit_residual: torch.Tensor     # (B,) f64
+    n_knots: torch.Tensor = None   # (B,) i32, 8 = single cubic (FITPACK ier=-2), more = knot insertion + smoothing
+    fit_ier: torch.Tensor = None   # (B,) i32, FITPACK's ier
     points_xyz: torch.Tensor | None = None    # (B,H*W,3) f32, first n_points rows valid
     edge_pixels: torch.Tensor | None = None   # (B,ecap) u32 as int32 view, first n_edge valid
     bin_counts: torch.Tensor | None = None    # (B,50) i32
@@ -76,6 +78,8 @@ def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_
             n_points=torch.empty(B, dtype=torch.int32, device=dev),
             n_edge=torch.empty(B, dtype=torch.int32, device=dev),
             fit_residual=torch.empty(B, dtype=torch.float64, device=dev),
+            n_knots=torch.zeros(B, dtype=torch.int32, device=dev),
+            fit_ier=torch.zeros(B, dtype=torch.int32, device=dev),
             workspace=workspace,
         )
         out = _lib.CurvatureOut()
@@ -83,6 +87,7 @@ def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_
         out.spline_points, out.status = res.spline_points.data_ptr(), res.status.data_ptr()
         out.n_points, out.n_edge = res.n_points.data_ptr(), res.n_edge.data_ptr()
         out.fit_residual = res.fit_residual.data_ptr()
+        out.n_knots, out.fit_ier = res.n_knots.data_ptr(), res.fit_ier.data_ptr()
         if want_points:
             res.points_xyz = torch.empty((B, H * W, 3), dtype=torch.float32, device=dev)
             out.points_xyz = res.points_xyz.data_ptr()

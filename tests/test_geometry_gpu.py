@@ -30,9 +30,6 @@ def _check_frame(r, i, f, curv_rtol=1e-9):
     if o.n_points >= gp.MIN_POINTS and o.status != gp.DEGENERATE_BINS:
         assert np.array_equal(r.bin_counts[i].cpu().numpy(), o.bin_counts)        # bit-exact bin indices
     st = int(r.status[i])
-    if o.status == gp.OK and o.n_knots > 8:
-        assert st == 5                                                             # RDP_FRAME_NEEDS_KNOTS
-        return o
     assert st == o.status, (st, o.status)
     if o.status != gp.OK:
         assert float(r.mean_curvature[i]) == 0.0 and float(r.max_curvature[i]) == 0.0
@@ -41,6 +38,9 @@ def _check_frame(r, i, f, curv_rtol=1e-9):
     assert E == o.n_edge
     edge = r.edge_pixels[i, :E].cpu().numpy().astype(np.int64)
     assert np.array_equal(edge, o.edge_pix)                                        # bit-exact selection and order
+    assert int(r.n_knots[i]) == o.n_knots and int(r.fit_ier[i]) == o.ier
+    if o.n_knots > 8:       # knot insertion + smoothing: same knots, looser (still far inside the 1e-3 bar) numerics
+        curv_rtol = max(curv_rtol, 1e-6)
     assert abs(float(r.fit_residual[i]) - o.fp) <= 1e-9 * max(o.fp, 1e-12)
     assert abs(float(r.mean_curvature[i]) - o.mean_curvature) <= curv_rtol * abs(o.mean_curvature)
     assert abs(float(r.max_curvature[i]) - o.max_curvature) <= curv_rtol * abs(o.max_curvature)
@@ -77,6 +77,30 @@ def test_matches_reference_golden_vectors(manifest, golden):
         lut = {int(p): j for j, p in enumerate(pix)}
         pts = pcd[[lut[int(e)] for e in edge]]
         assert np.array_equal(pts[np.lexsort((pts[:, 1], pts[:, 0]))], g["edge_sorted"]), name
+
+
+def test_knot_insertion_regime_matches_reference(manifest, golden):
+    """FITPACK's general branch (fp of the 8-knot cubic > s): knot count, ier and curvature vs the reference's values.
+
+    The bar is 1e-3 relative (north_star); the kernel reproduces FITPACK's knot sequence exactly, so a far tighter
+    bound holds, including on the thousands-of-knots frame that SURVEY 0.6 expected to be chaotic.
+    """
+    from rdp_b200 import geometry
+    cases = [(k, v) for k, v in manifest["cases"].items() if v["kind"] == "geometry" and v["n_knots"] != 8]
+    assert len(cases) >= 4
+    frames = [synth.make_frame(v["seed"], v["H"], v["W"], v["fill"], v["depth"]) for _, v in cases]
+    r = _run(frames)
+    for i, (name, meta) in enumerate(cases):
+        g = golden(name)
+        assert int(r.status[i]) == 0, name
+        rel_mean = abs(float(r.mean_curvature[i]) - meta["mean_curvature"]) / meta["mean_curvature"]
+        rel_max = abs(float(r.max_curvature[i]) - meta["max_curvature"]) / meta["max_curvature"]
+        print(f"{name}: knots {int(r.n_knots[i])} (ref {meta['n_knots']}), ier {int(r.fit_ier[i])}, "
+              f"rel err mean {rel_mean:.2e} max {rel_max:.2e}")
+        assert int(r.n_knots[i]) == meta["n_knots"] and int(r.fit_ier[i]) == meta["ier"], name
+        tight = 1e-8 if meta["n_knots"] <= 500 else 1e-6
+        assert rel_mean <= tight and rel_max <= tight, name
+        np.testing.assert_allclose(r.spline_points[i].cpu().numpy(), g["spline_points"], rtol=0, atol=1e-8)
 
 
 def test_degenerate_and_mixed_batch():
