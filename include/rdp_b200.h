@@ -157,8 +157,8 @@ int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int dept
  *   pixel_ids   [B][H*W]    uint32 flat pixel index v*W+u of every point         (output, device)
  *   n_points    [B]         int32  number of valid points per frame              (output, device)
  *
- * Limits: at most 64 frames and at most 16384 tiles of 4096 pixels per call (B * ceil(H*W/4096)); larger batches
- * are refused with RDP_ERR_UNSUPPORTED.  The array (about 200 KB) is held by every GPU that loads the library
+ * Limits: at most 64 frames and at most 4096 tiles of 16384 pixels per call (B * ceil(H*W/16384)); larger batches
+ * are refused with RDP_ERR_UNSUPPORTED.  The array (about 100 KB) is held by every GPU that loads the library
  * until the process exits.  The call itself performs no allocation of any kind.
  *
  * The first call on each device looks up the array's device address; make that first call with the device

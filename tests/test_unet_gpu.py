@@ -109,3 +109,15 @@ def test_batch_is_frame_independent():
     for i in (0, 3, 5):
         _, one, _ = model.forward_mask(rgb[i:i + 1], want_logits=True)
         assert torch.equal(one[0], all_logits[i])
+
+
+def test_hd_frame_720p():
+    """One 1280x720 frame (BASELINE config C3 resolution; H/16 = 45 is odd, so the Up pad path is exercised)."""
+    sd = synth.make_state_dict(2, planted=True)
+    batch = synth.make_batch((12,), 720, 1280, 0.15, "u16")
+    model = _model(sd)
+    mask, logits, _ = model.forward_mask(torch.from_numpy(batch["rgb"]).cuda(), want_logits=True)
+    ref = unet_port.unet_forward(sd, unet_port.rgb_u8_to_input(batch["rgb"]))
+    agree, hard_misses, listed = _agreement(mask.cpu().numpy(), ref)
+    print(f"1280x720: agreement {agree:.6f}, hard misses {hard_misses}, borderline listed {len(listed)}")
+    assert agree >= 0.999 and hard_misses == 0

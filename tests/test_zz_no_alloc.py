@@ -66,6 +66,6 @@ def test_static_scratch_rejects_oversized_batches():
     rc = lib.rdp_geom_deproject_static(dummy, dummy, _lib.DEPTH_U16, 65, 480, 640, k4, 0.001, dummy, dummy, dummy, None)
     assert rc == -2 and b"at most 64 frames" in lib.rdp_last_error()
     rc = lib.rdp_geom_deproject_static(dummy, dummy, _lib.DEPTH_U16, 64, 1080, 1920, k4, 0.001, dummy, dummy, dummy, None)
-    assert rc == -2 and b"16384 tiles" in lib.rdp_last_error()
+    assert rc == -2 and b"4096 tiles" in lib.rdp_last_error()
     rc = lib.rdp_geom_deproject_static(None, dummy, _lib.DEPTH_U16, 1, 480, 640, k4, 0.001, dummy, dummy, dummy, None)
     assert rc == -1
