@@ -9,7 +9,7 @@
 //
 // Data layout (HBM): mask u8 [B][P], depth u16|f32 [B][P] (P = H*W), workspace arrays indexed [b][i].
 // Kernels (one launch each per batch, all on the caller's stream, no host sync):
-//   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once, writes 4N (pixel ids) + 12N (fp32 xyz)
+//   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once, writes 4N (pixel ids) + 12N (fp32 xyz); 16384-pixel tiles
 //   k_bin_hist     L2/HBM      reads 4N + gathers 2N, writes N (bin ids)
 //   k_bin_offsets  tiny        50 bins per frame -> k per bin, offsets, status
 //   k_scatter      L2/HBM      reads 5N, writes 4N (pixel ids grouped by bin)
@@ -32,8 +32,9 @@ constexpr double SMOOTH_S = 0.1;  // :78
 constexpr double FIT_TOL = 1e-3;  // FITPACK parcur tol
 
 constexpr int DP_THREADS = 256;
-constexpr int DP_PX_PER_THREAD = 16;
-constexpr int TILE_PX = DP_THREADS * DP_PX_PER_THREAD;  // 4096 pixels per deprojection tile
+constexpr int DP_CHUNKS = 4;                             // 16-pixel chunks per thread, all loads issued before use
+constexpr int DP_PX_PER_THREAD = 16 * DP_CHUNKS;
+constexpr int TILE_PX = DP_THREADS * DP_PX_PER_THREAD;  // 16384 pixels per deprojection tile
 constexpr int PT_THREADS = 256;
 constexpr int PT_PER_BLOCK = 2048;  // points per block in the histogram / scatter passes
 constexpr int SEL_THREADS = 256;
@@ -156,7 +157,7 @@ __device__ __forceinline__ int lookback_exclusive(volatile unsigned long long* s
 
 template <bool VEC>
 __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
-  __shared__ uint32_t s_pix[TILE_PX];
+  __shared__ uint16_t s_pix[TILE_PX];  // tile-relative pixel offsets of the valid points
   __shared__ int s_warp[DP_THREADS / 32];
   __shared__ unsigned long long s_red[2][DP_THREADS / 32];
   __shared__ int s_ticket, s_base, s_total;
@@ -167,46 +168,65 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   const size_t fbase = (size_t)b * p.P;
   const int px0 = t * TILE_PX + tid * DP_PX_PER_THREAD;
 
-  unsigned valid = 0;
-  if (VEC && px0 + DP_PX_PER_THREAD <= p.P) {
-    // 128-bit loads: 16 mask bytes, then the 16 depths
-    const uint4 m4 = __ldg(reinterpret_cast<const uint4*>(p.mask + fbase + px0));
-    const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
-    if (p.depth_fmt == RDP_DEPTH_U16) {
-      const uint4* dp = reinterpret_cast<const uint4*>((const uint16_t*)p.depth + fbase + px0);
-      const uint4 d0 = __ldg(dp), d1 = __ldg(dp + 1);
-      const uint32_t dw[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+  // 64 consecutive pixels per thread: 4 x (16 mask bytes + 16 depths), every load in flight before the first use
+  unsigned valid[DP_CHUNKS];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const uint32_t mb = (mw[i >> 2] >> (8 * (i & 3))) & 0xffu;
-        const uint32_t dv = (dw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
-        if (mb && __dmul_rn((double)dv, p.scale) > 0.0) valid |= 1u << i;
+  for (int c = 0; c < DP_CHUNKS; ++c) valid[c] = 0;
+  if (VEC && px0 + DP_PX_PER_THREAD <= p.P) {
+    uint4 m4[DP_CHUNKS];
+    const uint4* mp = reinterpret_cast<const uint4*>(p.mask + fbase + px0);
+#pragma unroll
+    for (int c = 0; c < DP_CHUNKS; ++c) m4[c] = __ldg(mp + c);
+    if (p.depth_fmt == RDP_DEPTH_U16) {
+      uint4 d4[2 * DP_CHUNKS];
+      const uint4* dp = reinterpret_cast<const uint4*>((const uint16_t*)p.depth + fbase + px0);
+#pragma unroll
+      for (int c = 0; c < 2 * DP_CHUNKS; ++c) d4[c] = __ldg(dp + c);
+#pragma unroll
+      for (int c = 0; c < DP_CHUNKS; ++c) {
+        const uint32_t mw[4] = {m4[c].x, m4[c].y, m4[c].z, m4[c].w};
+        const uint32_t dw[8] = {d4[2 * c].x, d4[2 * c].y, d4[2 * c].z, d4[2 * c].w,
+                                d4[2 * c + 1].x, d4[2 * c + 1].y, d4[2 * c + 1].z, d4[2 * c + 1].w};
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const uint32_t mb = (mw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+          const uint32_t dv = (dw[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+          if (mb && __dmul_rn((double)dv, p.scale) > 0.0) valid[c] |= 1u << i;
+        }
       }
     } else {
       const float4* dp = reinterpret_cast<const float4*>((const float*)p.depth + fbase + px0);
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float4 d = __ldg(dp + q);
-        const float dv[4] = {d.x, d.y, d.z, d.w};
+      for (int c = 0; c < DP_CHUNKS; ++c) {
+        float4 d[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-          const int i = q * 4 + r;
-          const uint32_t mb = (mw[i >> 2] >> (8 * (i & 3))) & 0xffu;
-          const double z = p.depth_fmt == RDP_DEPTH_F32 ? (double)__fmul_rn(dv[r], p.scale_f32)
-                                                        : __dmul_rn((double)dv[r], p.scale);
-          if (mb && z > 0.0) valid |= 1u << i;
+        for (int q = 0; q < 4; ++q) d[q] = __ldg(dp + 4 * c + q);
+        const uint32_t mw[4] = {m4[c].x, m4[c].y, m4[c].z, m4[c].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float dv[4] = {d[q].x, d[q].y, d[q].z, d[q].w};
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const int i = q * 4 + r;
+            const uint32_t mb = (mw[i >> 2] >> (8 * (i & 3))) & 0xffu;
+            const double z = p.depth_fmt == RDP_DEPTH_F32 ? (double)__fmul_rn(dv[r], p.scale_f32)
+                                                          : __dmul_rn((double)dv[r], p.scale);
+            if (mb && z > 0.0) valid[c] |= 1u << i;
+          }
         }
       }
     }
   } else {
     for (int i = 0; i < DP_PX_PER_THREAD; ++i) {
       const int px = px0 + i;
-      if (px < p.P && p.mask[fbase + px] && depth_to_z(p, fbase + px) > 0.0) valid |= 1u << i;
+      if (px < p.P && p.mask[fbase + px] && depth_to_z(p, fbase + px) > 0.0) valid[i >> 4] |= 1u << (i & 15);
     }
   }
 
   // block-wide exclusive scan of the per-thread counts
-  const int cnt = __popc(valid);
+  int cnt = 0;
+#pragma unroll
+  for (int c = 0; c < DP_CHUNKS; ++c) cnt += __popc(valid[c]);
   int incl = cnt;
 #pragma unroll
   for (int o = 1; o < 32; o <<= 1) {
@@ -234,10 +254,14 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   }
   __syncthreads();
   int local = s_warp[warp] + incl - cnt;
-  while (valid) {
-    const int i = __ffs(valid) - 1;
-    valid &= valid - 1;
-    s_pix[local++] = (uint32_t)(px0 + i);
+#pragma unroll
+  for (int c = 0; c < DP_CHUNKS; ++c) {
+    unsigned v = valid[c];
+    while (v) {
+      const int i = __ffs(v) - 1;
+      v &= v - 1;
+      s_pix[local++] = (uint16_t)(tid * DP_PX_PER_THREAD + c * 16 + i);
+    }
   }
   __syncthreads();
 
@@ -245,7 +269,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   const int total = s_total, base = s_base;
   unsigned long long kmax = 0, kmin_inv = 0;
   for (int j = tid; j < total; j += DP_THREADS) {
-    const uint32_t px = s_pix[j];
+    const uint32_t px = (uint32_t)(t * TILE_PX) + s_pix[j];
     const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
     const double z = depth_to_z(p, fbase + px);
     const double x = deproject_axis((double)u, p.cx, z, p.fx);
@@ -839,7 +863,6 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   __shared__ double s_red[KN_THREADS / 32];
   __shared__ int s_scan[KN_THREADS / 32];
   __shared__ int s_i[8];
-  __shared__ double s_d[8];
   __shared__ unsigned long long s_best[KN_THREADS / 32];
   __shared__ int s_besti[KN_THREADS / 32];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1417,7 +1440,7 @@ extern "C" int rdp_geom_curvature_profiled(const uint8_t* mask, const void* dept
 // (stream-ordered), and two calls that overlap on the GPU would race: issue them on one stream, or otherwise make
 // sure one has finished before the next starts.
 constexpr int STATIC_MAX_FRAMES = 64;
-constexpr int STATIC_MAX_TILES = 16384;  // sum over the batch of ceil(H*W / 4096)
+constexpr int STATIC_MAX_TILES = 4096;  // sum over the batch of ceil(H*W / 16384)
 constexpr size_t STATIC_SCRATCH_BYTES =
     ((sizeof(rdp::geom::FrameState) * STATIC_MAX_FRAMES + 255) / 256) * 256 + sizeof(unsigned long long) * STATIC_MAX_TILES + 256;
 static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
@@ -1466,7 +1489,7 @@ extern "C" int rdp_geom_deproject_static(const uint8_t* mask, const void* depth,
   const int tiles = (P + TILE_PX - 1) / TILE_PX;
   RDP_REQUIRE(B <= STATIC_MAX_FRAMES && (long long)B * tiles <= STATIC_MAX_TILES, RDP_ERR_UNSUPPORTED,
               "rdp_geom_deproject_static: batch of %d frames x %d tiles exceeds the built-in scratch (at most %d frames and "
-              "%d tiles of 4096 pixels per call); use rdp_geom_curvature with a workspace for larger batches",
+              "%d tiles of 16384 pixels per call); use rdp_geom_curvature with a workspace for larger batches",
               B, tiles, STATIC_MAX_FRAMES, STATIC_MAX_TILES);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   void* scratch = nullptr;
