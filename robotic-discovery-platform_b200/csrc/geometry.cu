@@ -10,9 +10,9 @@
 // Data layout (HBM): mask u8 [B][P], depth u16|f32 [B][P] (P = H*W), workspace arrays indexed [b][i].
 // Kernels (one launch each per batch, all on the caller's stream, no host sync):
 //   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once, writes 4N (pixel ids) + 12N (fp32 xyz); 16384-pixel tiles
-//   k_bin_hist     L2/HBM      reads 4N + gathers 2N, writes N (bin ids)
+//   k_bin_hist     L2/HBM      reads 4N + gathers 2N, writes N (bin ids) + 8N (fp64 y keys for the selection)
 //   k_bin_offsets  tiny        50 bins per frame -> k per bin, offsets, status
-//   k_scatter      L2/HBM      reads 5N, writes 4N (pixel ids grouped by bin)
+//   k_scatter      L2/HBM      reads 13N, writes 12N (pixel ids and y keys grouped by bin)
 //   k_select_sort  latency     one CTA per (frame, bin): radix select of the k largest y, bitonic sort by x
 //   k_fit          latency     one CTA per frame: chord-length scan, 4x4 normal equations in fp64, curvature
 #include <stdarg.h>
@@ -37,9 +37,8 @@ constexpr int DP_PX_PER_THREAD = 16 * DP_CHUNKS;
 constexpr int TILE_PX = DP_THREADS * DP_PX_PER_THREAD;  // 16384 pixels per deprojection tile
 constexpr int PT_THREADS = 256;
 constexpr int PT_PER_BLOCK = 2048;  // points per block in the histogram / scatter passes
-constexpr int SEL_THREADS = 256;
-constexpr int STAGE_CAP = 6144;  // bin segment staged in shared memory up to this many points
-constexpr int SORT_CAP = 2048;   // selected points sorted in shared memory up to this many
+constexpr int SEL_THREADS = 128;
+constexpr int SORT_CAP = 1024;   // selected points sorted in shared memory up to this many (global memory beyond)
 
 struct FrameState {
   unsigned long long xmax_key;      // atomicMax over ordered keys of x
@@ -70,6 +69,8 @@ struct Params {
   uint32_t* pix;       // [B][P] valid pixel ids, row-major order
   uint8_t* bins;       // [B][P] bin id per valid point
   uint32_t* binned;    // [B][P] pixel ids grouped by bin
+  unsigned long long* ykey_c;  // [B][P] ordered fp64 y key per valid point (compacted order)
+  unsigned long long* ykey_b;  // [B][P] the same, grouped by bin like `binned`
   uint32_t* edge_pix;  // [B][ecap] selected pixel ids, ordered by x
   unsigned long long* edge_key;  // [B][ecap] sort keys (only touched when a bin overflows SORT_CAP)
   double* edge_xyz;    // [B][ecap][3]
@@ -320,9 +321,11 @@ __global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
   for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
     const uint32_t px = p.pix[fbase + i];
     const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
-    const double x = deproject_axis((double)u, p.cx, depth_to_z(p, fbase + px), p.fx);
+    const double z = depth_to_z(p, fbase + px);
+    const double x = deproject_axis((double)u, p.cx, z, p.fx);
     const int bin = bin_of(x, x_min, width);
     p.bins[fbase + i] = (uint8_t)bin;
+    p.ykey_c[fbase + i] = ordered_key(deproject_axis((double)v, p.cy, z, p.fy));  // selection key for k_select_sort
     atomicAdd(&s_hist[bin], 1);
   }
   __syncthreads();
@@ -381,7 +384,9 @@ __global__ void __launch_bounds__(PT_THREADS) k_scatter(const Params p) {
   __syncthreads();
   for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
     const int bin = p.bins[fbase + i];
-    p.binned[fbase + s_base[bin] + atomicAdd(&s_cnt[bin], 1)] = p.pix[fbase + i];
+    const int pos = s_base[bin] + atomicAdd(&s_cnt[bin], 1);
+    p.binned[fbase + pos] = p.pix[fbase + i];
+    p.ykey_b[fbase + pos] = p.ykey_c[fbase + i];
   }
 }
 
@@ -402,11 +407,8 @@ __device__ __forceinline__ bool key_has_prefix(unsigned long long yk, uint32_t n
 }
 
 __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  unsigned long long* s_yk = reinterpret_cast<unsigned long long*>(s_raw);                  // [STAGE_CAP]
-  uint32_t* s_px = reinterpret_cast<uint32_t*>(s_yk + STAGE_CAP);                            // [STAGE_CAP]
-  unsigned long long* s_sk = reinterpret_cast<unsigned long long*>(s_px + STAGE_CAP);        // [SORT_CAP]
-  uint32_t* s_sp = reinterpret_cast<uint32_t*>(s_sk + SORT_CAP);                             // [SORT_CAP]
+  __shared__ unsigned long long s_sk[SORT_CAP];  // x sort keys of the selected points
+  __shared__ uint32_t s_sp[SORT_CAP];            // their pixel ids
   __shared__ int s_hist[256];
   __shared__ unsigned long long s_ph, s_mm[2][SEL_THREADS / 32];
   __shared__ uint32_t s_pl;
@@ -418,23 +420,13 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
   const int cnt = f.bin_count[bin], k = f.bin_k[bin];
   if (cnt == 0) return;
   const size_t fbase = (size_t)b * p.P;
-  const uint32_t* seg = p.binned + fbase + f.bin_off[bin];
-  const bool staged = cnt <= STAGE_CAP;
+  const uint32_t* seg = p.binned + fbase + f.bin_off[bin];              // pixel ids of the bin
+  const unsigned long long* ykeys = p.ykey_b + fbase + f.bin_off[bin];  // their ordered fp64 y keys
 
-  auto y_key_of = [&](uint32_t px) {
-    const int v = (int)(px / (uint32_t)p.W);
-    return ordered_key(deproject_axis((double)v, p.cy, depth_to_z(p, fbase + px), p.fy));
-  };
-
-  // stage the segment and find the common leading digits of the y keys
+  // common leading digits of the y keys (they are clustered: a bin spans a few centimetres)
   unsigned long long kmax = 0, kmin_inv = 0;
   for (int i = tid; i < cnt; i += SEL_THREADS) {
-    const uint32_t px = seg[i];
-    const unsigned long long yk = y_key_of(px);
-    if (staged) {
-      s_yk[i] = yk;
-      s_px[i] = px;
-    }
+    const unsigned long long yk = ykeys[i];
     kmax = yk > kmax ? yk : kmax;
     kmin_inv = ~yk > kmin_inv ? ~yk : kmin_inv;
   }
@@ -456,41 +448,51 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
     s_ph = d0 == 0 ? 0ull : (d0 == 8 ? kmax : (kmax >> (64 - 8 * d0)) << (64 - 8 * d0));
     s_pl = 0;
     s_krem = k;
-    s_done = (k >= cnt);  // everything is selected (cnt < 20 -> k = 1 = cnt, or tiny bins)
+    s_done = (k >= cnt);  // everything is selected (tiny bins)
     s_nsel = 0;
   }
   __syncthreads();
 
   if (!s_done) {
     for (int d = s_start; d < 12; ++d) {
-      s_hist[tid] = 0;
+      for (int i = tid; i < 256; i += SEL_THREADS) s_hist[i] = 0;
       __syncthreads();
       const unsigned long long ph = s_ph;
       const uint32_t pl = s_pl;
       for (int i = tid; i < cnt; i += SEL_THREADS) {
-        unsigned long long yk;
-        uint32_t px;
-        if (staged) {
-          yk = s_yk[i];
-          px = s_px[i];
-        } else {
-          px = seg[i];
-          yk = y_key_of(px);
-        }
-        if (key_has_prefix(yk, ~px, d, ph, pl)) atomicAdd(&s_hist[key_digit(yk, ~px, d)], 1);
+        const unsigned long long yk = ykeys[i];
+        const uint32_t npx = d >= 8 ? ~seg[i] : 0u;  // the pixel id only matters once the whole y key is tied
+        if (key_has_prefix(yk, npx, d, ph, pl)) atomicAdd(&s_hist[key_digit(yk, npx, d)], 1);
       }
       __syncthreads();
-      if (tid == 0) {
-        int krem = s_krem, cum = 0, dig = 255;
-        for (; dig > 0; --dig) {
-          if (cum + s_hist[dig] >= krem) break;
-          cum += s_hist[dig];
+      if (warp == 0) {
+        // digit of the k-th largest key: lane l owns buckets 8l..8l+7, suffix sums across lanes by shuffles
+        int h[8], own = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          h[e] = s_hist[8 * lane + e];
+          own += h[e];
         }
-        krem -= cum;
-        if (d < 8) s_ph |= (unsigned long long)dig << (56 - 8 * d);
-        else s_pl |= (uint32_t)dig << (24 - 8 * (d - 8));
-        s_krem = krem;
-        if (s_hist[dig] == krem) s_done = 1;  // the whole bucket is taken: threshold = prefix with zeros below
+        int above = 0;  // keys in buckets of higher lanes
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int v = __shfl_down_sync(0xffffffffu, own + above, o);
+          if (lane + o < 32) above += v;
+        }
+        const int krem = s_krem;
+        const bool mine = above < krem && krem <= above + own;
+        if (mine) {
+          int cum = above, dig = 7;
+          for (; dig > 0; --dig) {
+            if (cum + h[dig] >= krem) break;
+            cum += h[dig];
+          }
+          const int digit = 8 * lane + dig;
+          if (d < 8) s_ph |= (unsigned long long)digit << (56 - 8 * d);
+          else s_pl |= (uint32_t)digit << (24 - 8 * (d - 8));
+          s_krem = krem - cum;
+          if (h[dig] == krem - cum) s_done = 1;  // the whole bucket is taken: threshold = prefix with zeros below
+        }
       }
       __syncthreads();
       if (s_done) break;
@@ -505,16 +507,10 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
   unsigned long long* sk = sort_in_smem ? s_sk : p.edge_key + ebase;
   uint32_t* sp = sort_in_smem ? s_sp : p.edge_pix + ebase;
   for (int i = tid; i < cnt; i += SEL_THREADS) {
-    unsigned long long yk;
-    uint32_t px;
-    if (staged) {
-      yk = s_yk[i];
-      px = s_px[i];
-    } else {
-      px = seg[i];
-      yk = y_key_of(px);
-    }
-    if (yk > th || (yk == th && ~px >= tl)) {
+    const unsigned long long yk = ykeys[i];
+    if (yk < th) continue;
+    const uint32_t px = seg[i];
+    if (yk > th || ~px >= tl) {
       const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
       const int pos = atomicAdd(&s_nsel, 1);
       if (pos < k) {
@@ -1278,7 +1274,6 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   }
 }
 
-constexpr size_t SELECT_SMEM = (size_t)STAGE_CAP * 12 + (size_t)SORT_CAP * 12;
 
 struct Plan {
   size_t header_bytes, total_bytes;
@@ -1316,6 +1311,8 @@ static Plan carve(Params& p, KnotWs& kn, void* ws, int B, int H, int W) {
   p.pix = c.take<uint32_t>(B * P);
   p.bins = c.take<uint8_t>(B * P);
   p.binned = c.take<uint32_t>(B * P);
+  p.ykey_c = c.take<unsigned long long>(B * P);
+  p.ykey_b = c.take<unsigned long long>(B * P);
   p.edge_pix = c.take<uint32_t>((size_t)B * pl.ecap);
   p.edge_key = c.take<unsigned long long>((size_t)B * pl.ecap);
   p.edge_xyz = c.take<double>((size_t)B * pl.ecap * 3);
@@ -1369,11 +1366,6 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   p.scale_f32 = (float)depth_scale;
   p.out = *out;
 
-  static bool smem_opt_in = false;  // idempotent attribute; a benign race sets it twice at worst
-  if (!smem_opt_in) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_select_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SELECT_SMEM));
-    smem_opt_in = true;
-  }
   int n_marks = 0;
   auto mark = [&]() {
     if (marks) cudaEventRecord(marks[n_marks++], stream);
@@ -1393,7 +1385,7 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   mark();
   k_scatter<<<pgrid, PT_THREADS, 0, stream>>>(p);
   mark();
-  k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, SELECT_SMEM, stream>>>(p);
+  k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, 0, stream>>>(p);
   mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
   mark();

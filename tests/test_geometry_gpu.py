@@ -148,7 +148,7 @@ def test_numpy_promotion_modes():
 
 
 def test_large_bin_uses_global_paths():
-    """All points but one fall into a single x-bin: exercises the unstaged select and the global-memory sort."""
+    """All points but one fall into a single x-bin: exercises a 66k-point select and the global-memory sort."""
     H, W = 480, 640
     f = synth.make_frame(44, H, W, 0.5, "f32")
     m = np.zeros((H, W), np.uint8); m[:, 200:420] = f["mask_gt"][:, 200:420]; m[240, 0] = 1
