@@ -160,9 +160,11 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     }
   }
   // accumulator stage drained: hand it back to the MMA warp
-  tc_fence_before();
-  __syncwarp();
-  if (lane == 0) mbar_arrive(acc_empty_bar);
+  if (acc_empty_bar != nullptr) {
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(acc_empty_bar);
+  }
   if (BN == 64 && head_on && inside) {
     const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
 #pragma unroll
@@ -311,9 +313,12 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
 // L2 -> shared-memory traffic for A drops from 9 x 16 KB to 22.5 KB per channel block (6.4x).
 // Weights stay resident in shared memory for the whole kernel when all 9*Cin/64 slices fit (the 64-wide
 // full-resolution layers), otherwise they stream through their own ring, one 64-wide slice per tap.
-constexpr int HALO_W = 10, HALO_H = 18;
-constexpr int HALO_BYTES = HALO_W * HALO_H * 128;  // 23040
-constexpr int HALO_STRIDE = 23 * 1024;             // stage stride, keeps every stage 1024-byte aligned
+// TILES = 1: one 8x16 tile per work item (halo 18x10).  TILES = 2: a 16x16 super-tile, i.e. two 8x16 tiles that share
+// one 18x18 halo box and, above all, every streamed weight slice (half the L2 -> shared-memory weight traffic).
+constexpr int HALO_H = 18;
+__host__ __device__ constexpr int halo_w(int tiles) { return 8 * tiles + 2; }
+__host__ __device__ constexpr int halo_bytes(int tiles) { return halo_w(tiles) * HALO_H * 128; }  // 23040 / 41472
+__host__ __device__ constexpr int halo_stride(int tiles) { return (halo_bytes(tiles) + 1023) / 1024 * 1024; }
 constexpr int HALO_SMEM_TOTAL = 227 * 1024;
 constexpr int HALO_MAX_STAGES = 12;
 constexpr int HALO_BAR_BYTES = 512 + AUX_BYTES;
@@ -334,13 +339,14 @@ __device__ __forceinline__ uint64_t desc_pack(uint32_t lo, uint32_t hi) { return
 // (base + immediate) low words, taps are unrolled, and when the TMEM allocation starts at column 0 (BASE0, the
 // usual case with one CTA per SM) the accumulator address is an immediate as well: the tile loop is unrolled
 // over the two accumulator stages.
-template <int BN, bool RESIDENT, bool BASE0>
+template <int BN, bool RESIDENT, bool BASE0, int TILES>
 __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg& cfg, uint8_t* smem_a, uint8_t* smem_b,
                                               uint64_t* full_a, uint64_t* empty_a, uint64_t* full_b, uint64_t* empty_b,
                                               uint64_t* w_full, uint64_t* acc_full, uint64_t* acc_empty, uint32_t tmem_base) {
   constexpr int B_BLOCK = BN * BLOCK_K * 2;
   constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
-  constexpr uint32_t hi_a = desc_hi(HALO_W * 128), hi_b = desc_hi(1024);
+  constexpr int HW = halo_w(TILES);
+  constexpr uint32_t hi_a = desc_hi(HW * 128), hi_b = desc_hi(1024);
   const int ncb = p.kb0 + p.kb1;
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
   const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
@@ -355,11 +361,11 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
       if (work < p.total_work) {
         mbar_wait(&acc_empty[as], aphase ^ 1);
         tc_fence_after();
-        const uint32_t tmem_acc = BASE0 ? (uint32_t)(as * BN) : tmem_base + as * BN;
+        const uint32_t tmem_acc = BASE0 ? (uint32_t)(as * TILES * BN) : tmem_base + as * TILES * BN;
         for (int cb = 0; cb < ncb; ++cb) {
           mbar_wait(&full_a[sa], pa);
           tc_fence_after();
-          const uint32_t a_lo = a_lo0 + sa * (HALO_STRIDE >> 4);
+          const uint32_t a_lo = a_lo0 + sa * (halo_stride(TILES) >> 4);
           const uint32_t bres_lo = b_lo0 + cb * (9 * B_BLOCK >> 4);
 #pragma unroll
           for (int tap = 0; tap < 9; ++tap) {
@@ -371,11 +377,14 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
               tc_fence_after();
               b_lo = b_lo0 + sb * (B_BLOCK >> 4);
             }
-            const uint32_t at_lo = a_lo + ((tap / 3) * HALO_W + tap % 3) * 8;  // 128 bytes per halo row
+            const uint32_t at_lo = a_lo + ((tap / 3) * HW + tap % 3) * 8;  // 128 bytes per halo row
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-              mma_bf16_ss(tmem_acc, desc_pack(at_lo + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc,
-                          (cb | tap | k) != 0);
+            for (int h = 0; h < TILES; ++h) {  // the tiles of a super-tile reuse the weight slice
+#pragma unroll
+              for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                mma_bf16_ss(tmem_acc + h * BN, desc_pack(at_lo + h * 64 + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc,
+                            (cb | tap | k) != 0);
+            }
             if (!RESIDENT) {
               tc_commit(&empty_b[sb]);
               if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
@@ -392,19 +401,20 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
   }
 }
 
-constexpr int INTERP_WARPS = 4;
-constexpr int CONV_THREADS_INTERP = CONV_THREADS + INTERP_WARPS * 32;
+__host__ __device__ constexpr int interp_warps(int tiles) { return 4 * tiles; }  // a super-tile's halo is 1.8x larger
+__host__ __device__ constexpr int conv_threads(bool interp, int tiles) { return CONV_THREADS + (interp ? interp_warps(tiles) * 32 : 0); }
 
 // Low-resolution source patch of one halo block: 18x10 output pixels at x2 span at most 11x7 source pixels.
-constexpr int PATCH_W = 7, PATCH_H = 11;
-constexpr int PATCH_BYTES = PATCH_W * PATCH_H * 128;  // 9856
-constexpr int PATCH_STRIDE = 10 * 1024;
+constexpr int PATCH_H = 11;
+__host__ __device__ constexpr int patch_w(int tiles) { return tiles == 1 ? 7 : 11; }  // 10 / 18 output columns at x2
+__host__ __device__ constexpr int patch_bytes(int tiles) { return patch_w(tiles) * PATCH_H * 128; }
+__host__ __device__ constexpr int patch_stride(int tiles) { return (patch_bytes(tiles) + 1023) / 1024 * 1024; }
 constexpr int PATCH_STAGES = 2;
 
 // Bilinear x2 (align_corners=True) + zero pad of one 16-byte chunk (8 channels) of one halo pixel, read from the
 // source patch in shared memory, in the same fp32 operation order as k_upsample2x, so that fusing the interpolation
 // into the convolution changes no bit.
-__device__ __forceinline__ uint4 interp_chunk(const ConvParams& p, const uint8_t* patch, int sy0, int sx0, int ys, int xs, int j) {
+__device__ __forceinline__ uint4 interp_chunk(const ConvParams& p, const uint8_t* patch, int pw, int sy0, int sx0, int ys, int xs, int j) {
   uint4 o = make_uint4(0, 0, 0, 0);
   const int yo = ys - p.pad_y, xo = xs - p.pad_x;
   if (ys < 0 || ys >= p.H || xs < 0 || xs >= p.W || yo < 0 || yo >= 2 * p.low_h || xo < 0 || xo >= 2 * p.low_w) return o;
@@ -414,7 +424,7 @@ __device__ __forceinline__ uint4 interp_chunk(const ConvParams& p, const uint8_t
   const int y1 = y0 + (y0 < h - 1 ? 1 : 0), x1 = x0 + (x0 < w - 1 ? 1 : 0);
   const float ly1 = fy - (float)y0, ly0 = 1.f - ly1, lx1 = fx - (float)x0, lx0 = 1.f - lx1;
   const uint4* base = reinterpret_cast<const uint4*>(patch) + j;
-  const int r0 = (y0 - sy0) * PATCH_W - sx0, r1 = (y1 - sy0) * PATCH_W - sx0;
+  const int r0 = (y0 - sy0) * pw - sx0, r1 = (y1 - sy0) * pw - sx0;
   const uint4 v00 = base[(r0 + x0) * 8], v01 = base[(r0 + x1) * 8];
   const uint4 v10 = base[(r1 + x0) * 8], v11 = base[(r1 + x1) * 8];
   const __nv_bfloat162* a = reinterpret_cast<const __nv_bfloat162*>(&v00);
@@ -439,8 +449,8 @@ __device__ __forceinline__ int patch_origin(float r, int first_out, int pad) {
   return (int)(r * (float)(o > 0 ? o : 0));
 }
 
-template <int BN, bool RESIDENT, bool INTERP>
-__global__ void __launch_bounds__(INTERP ? CONV_THREADS_INTERP : CONV_THREADS, 1)
+template <int BN, bool RESIDENT, bool INTERP, int TILES>
+__global__ void __launch_bounds__(conv_threads(INTERP, TILES), 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
                const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
   constexpr int B_BLOCK = BN * BLOCK_K * 2;  // one 64-wide weight slice
@@ -448,6 +458,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const int ncb = p.kb0 + p.kb1;
   uint8_t* smem_a = smem;
+  constexpr int HW = halo_w(TILES), HALO_BYTES = halo_bytes(TILES), HALO_STRIDE = halo_stride(TILES);
+  constexpr int PATCH_W = patch_w(TILES), PATCH_BYTES = patch_bytes(TILES), PATCH_STRIDE = patch_stride(TILES);
+  static_assert(2 * TILES * BN <= 512, "accumulators exceed TMEM");
   uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
   const int b_bytes = RESIDENT ? 9 * ncb * B_BLOCK : cfg.sb * B_BLOCK;
   uint8_t* smem_l = smem_b + b_bytes;  // low-resolution source patches (INTERP only)
@@ -488,7 +501,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 2 * BN);
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * TILES * BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -510,7 +523,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         const int tx = m % p.tiles_x; m /= p.tiles_x;
         const int ty = m % p.tiles_y;
         const int n = m / p.tiles_y;
-        const int x0 = tx * 8, y0 = ty * 16;
+        const int x0 = tx * 8 * TILES, y0 = ty * 16;
         // INTERP: source patches of the interpolated blocks, PATCH_STAGES ahead of the block being consumed (a patch
         // slot frees when the interpolation warps finish a block, which never depends on loads not yet issued)
         const int sy0 = INTERP ? patch_origin(p.ry, y0 - 1, p.pad_y) : 0, sx0 = INTERP ? patch_origin(p.rx, x0 - 1, p.pad_x) : 0;
@@ -553,20 +566,21 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     if (lane == 0) {
       // ================= MMA issuer =================
       if (tmem_base == 0)
-        halo_mma_loop<BN, RESIDENT, true>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
+        halo_mma_loop<BN, RESIDENT, true, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
       else
-        halo_mma_loop<BN, RESIDENT, false>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
+        halo_mma_loop<BN, RESIDENT, false, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
     }
   } else if (INTERP && warp >= 6) {
-    // ================= interpolation producers (warps 6..9): halo blocks of the upsampled branch =================
-    const int t = threadIdx.x - 6 * 32;   // 0..127
+    // ================= interpolation producers (warps 6..): halo blocks of the upsampled branch =================
+    constexpr int IT = interp_warps(TILES) * 32;
+    const int t = threadIdx.x - 6 * 32;   // 0..IT-1
     const int j = t & 7;                  // 16-byte chunk (8 channels) this thread owns
     uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
       int m = work / p.n_tiles;
       const int tx = m % p.tiles_x; m /= p.tiles_x;
       const int ty = m % p.tiles_y;
-      const int x0 = tx * 8 - 1, y0 = ty * 16 - 1;
+      const int x0 = tx * 8 * TILES - 1, y0 = ty * 16 - 1;
       const int sy0 = patch_origin(p.ry, y0, p.pad_y), sx0 = patch_origin(p.rx, x0, p.pad_x);
       for (int cb = 0; cb < ncb; ++cb) {
         mbar_wait(&empty_a[sa], pa ^ 1);  // also for stages the TMA thread fills (see the producer's note)
@@ -575,13 +589,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
           uint8_t* stage = smem_a + sa * HALO_STRIDE;
           const uint8_t* patch = smem_l + sl * PATCH_STRIDE;
 #pragma unroll 4
-          for (int px = t >> 3; px < HALO_W * HALO_H; px += 16) {
-            const int hy = px / HALO_W, hx = px - hy * HALO_W;
-            const uint4 v = interp_chunk(p, patch, sy0, sx0, y0 + hy, x0 + hx, j);
+          for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
+            const int hy = px / HW, hx = px - hy * HW;
+            const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
             *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;  // TMA's 128-byte swizzle
           }
           fence_proxy_async();
-          asm volatile("bar.sync 1, 128;" ::: "memory");
+          asm volatile("bar.sync 1, %0;" ::"n"(IT) : "memory");
           if (t == 0) {
             mbar_arrive(&full_a[sa]);
             mbar_arrive(&empty_l[sl]);
@@ -602,12 +616,16 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       const int tx = m % p.tiles_x; m /= p.tiles_x;
       const int ty = m % p.tiles_y;
       const int n = m / p.tiles_y;
-      const int y = ty * 16 + (row >> 3), x = tx * 8 + (row & 7);
-      const bool inside = y < p.H && x < p.W;
+      const int y = ty * 16 + (row >> 3);
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
-      epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, &acc_empty[as], lane);
+#pragma unroll
+      for (int h = 0; h < TILES; ++h) {
+        const int x = tx * 8 * TILES + h * 8 + (row & 7);
+        const bool inside = y < p.H && x < p.W;
+        const uint32_t taddr = tmem_base + (as * TILES + h) * BN + ((uint32_t)(quarter * 32) << 16);
+        epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
+      }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
@@ -616,7 +634,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 2 * BN);
+    tmem_dealloc(tmem_base, 2 * TILES * BN);
   }
 }
 
@@ -1044,39 +1062,54 @@ int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const ConvParams& p
   }
 }
 
-template <int BN, bool RESIDENT, bool INTERP>
+template <int BN, bool RESIDENT, bool INTERP, int TILES>
 int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p,
                        const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT, INTERP>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT, INTERP, TILES>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
     attr_set = true;
   }
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
-  k_conv3x3_halo<BN, RESIDENT, INTERP><<<grid, INTERP ? CONV_THREADS_INTERP : CONV_THREADS, HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
+  k_conv3x3_halo<BN, RESIDENT, INTERP, TILES><<<grid, conv_threads(INTERP, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
   return RDP_OK;
 }
 
+// Super-tiles (two 8x16 tiles per work item) pay off where weights stream from L2 and two accumulator pairs fit TMEM.
+inline int halo_tiles_for(int bn, int n_tiles, int ncb, bool interp) {
+  static const int env = getenv("RDP_HALO_TILES") ? atoi(getenv("RDP_HALO_TILES")) : 0;
+  if (env == 1) return 1;
+  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (interp ? PATCH_STAGES * patch_stride(1) : 0);
+  const bool resident = n_tiles == 1 && 9 * ncb * bn * BLOCK_K * 2 + (interp ? 2 : 3) * halo_stride(1) <= budget;
+  return (!resident && bn == 128) ? 2 : 1;
+}
+
 template <int BN>
-int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms,
-                     cudaStream_t stream) {
+int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int tiles,
+                     int num_sms, cudaStream_t stream) {
   const int ncb = p.kb0 + p.kb1, b_block = BN * BLOCK_K * 2;
-  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (p.low ? PATCH_STAGES * PATCH_STRIDE : 0);
+  const int HALO_STRIDE = halo_stride(tiles);
+  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (p.low ? PATCH_STAGES * patch_stride(tiles) : 0);
   static const int env_sa = getenv("RDP_HALO_SA") ? atoi(getenv("RDP_HALO_SA")) : 0;
   HaloCfg cfg{};
   const int w_bytes = 9 * ncb * b_block;
-  if (p.n_tiles == 1 && w_bytes + (p.low ? 2 : 3) * HALO_STRIDE <= budget) {
+  if (tiles == 1 && p.n_tiles == 1 && w_bytes + (p.low ? 2 : 3) * HALO_STRIDE <= budget) {
     cfg.sb = 0;
     cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / HALO_STRIDE);
-    return p.low ? launch_conv_halo_t<BN, true, true>(s0, s1, wm, p, cfg, num_sms, stream)
-                 : launch_conv_halo_t<BN, true, false>(s0, s1, wm, p, cfg, num_sms, stream);
+    return p.low ? launch_conv_halo_t<BN, true, true, 1>(s0, s1, wm, p, cfg, num_sms, stream)
+                 : launch_conv_halo_t<BN, true, false, 1>(s0, s1, wm, p, cfg, num_sms, stream);
   }
   // streamed weights: a halo block lasts 9 taps, so few A stages suffice; the weight ring must cover the
   // bandwidth-latency product of one 64-wide slice per tap
-  cfg.sa = env_sa ? env_sa : (BN == 256 ? 2 : 3);
+  cfg.sa = env_sa ? env_sa : ((BN == 256 || tiles == 2) ? 2 : 3);
   cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * HALO_STRIDE) / b_block);
-  return p.low ? launch_conv_halo_t<BN, false, true>(s0, s1, wm, p, cfg, num_sms, stream)
-               : launch_conv_halo_t<BN, false, false>(s0, s1, wm, p, cfg, num_sms, stream);
+  if constexpr (BN == 128) {
+    if (tiles == 2)
+      return p.low ? launch_conv_halo_t<BN, false, true, 2>(s0, s1, wm, p, cfg, num_sms, stream)
+                   : launch_conv_halo_t<BN, false, false, 2>(s0, s1, wm, p, cfg, num_sms, stream);
+  }
+  return p.low ? launch_conv_halo_t<BN, false, true, 1>(s0, s1, wm, p, cfg, num_sms, stream)
+               : launch_conv_halo_t<BN, false, false, 1>(s0, s1, wm, p, cfg, num_sms, stream);
 }
 
 }  // namespace
@@ -1200,7 +1233,9 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     ConvParams p{};
     p.B = B; p.H = L.H; p.W = L.W;
     const bool halo = taps == 9 && !force_v1 && sel[i] == 'h';
-    if (halo) { p.tile_w = 8; p.tile_h = 16; }
+    const int cout_i = net->w.conv[i].cout;
+    const int tiles = halo ? halo_tiles_for(net->bn[i], cout_i / net->bn[i], (c0 + c1) / 64, low != nullptr) : 1;
+    if (halo) { p.tile_w = 8 * tiles; p.tile_h = 16; }
     else pick_tile(L.H, L.W, p.tile_w, p.tile_h);
     p.tiles_x = (L.W + p.tile_w - 1) / p.tile_w;
     p.tiles_y = (L.H + p.tile_h - 1) / p.tile_h;
@@ -1228,17 +1263,17 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       p.rx = 2 * low->w > 1 ? (float)(low->w - 1) / (float)(2 * low->w - 1) : 0.f;
     }
     CUtensorMap m0, m1;
-    const int box_w = halo ? HALO_W : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
+    const int box_w = halo ? halo_w(tiles) : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
     int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
-    if (low) rc = make_act_map(&m1, low->ptr, B, low->h, low->w, c1, PATCH_W, PATCH_H, /*swizzle=*/false);
+    if (low) rc = make_act_map(&m1, low->ptr, B, low->h, low->w, c1, patch_w(tiles), PATCH_H, /*swizzle=*/false);
     else rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
     if (rc != RDP_OK) return rc;
     if (halo) {
       switch (net->bn[i]) {
-        case 64: rc = launch_conv_halo<64>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
-        case 128: rc = launch_conv_halo<128>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
-        default: rc = launch_conv_halo<256>(m0, m1, net->wmap[i], p, net->num_sms, stream); break;
+        case 64: rc = launch_conv_halo<64>(m0, m1, net->wmap[i], p, tiles, net->num_sms, stream); break;
+        case 128: rc = launch_conv_halo<128>(m0, m1, net->wmap[i], p, tiles, net->num_sms, stream); break;
+        default: rc = launch_conv_halo<256>(m0, m1, net->wmap[i], p, tiles, net->num_sms, stream); break;
       }
       mark();
       return rc;
