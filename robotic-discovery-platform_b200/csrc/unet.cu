@@ -61,6 +61,7 @@ struct ConvParams {
   int low_h, low_w;
   int pad_y, pad_x;          // offset of the interpolated image inside the skip-sized frame (Up.forward's F.pad)
   float ry, rx;              // align_corners=True scales (h-1)/(2h-1), (w-1)/(2w-1)
+  int debug_waits;           // development aid: CTA 0 prints where its MMA and epilogue threads waited
 };
 
 constexpr int AUX_SHIFT_FLOATS = 512;   // BN shift of every output channel of the layer
@@ -350,6 +351,7 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
   const int ncb = p.kb0 + p.kb1;
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
   const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
+  long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64(), t0;
   if (RESIDENT) {
     mbar_wait(w_full, 0);
     tc_fence_after();
@@ -359,11 +361,15 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
 #pragma unroll
     for (int as = 0; as < 2; ++as) {
       if (work < p.total_work) {
+        t0 = clock64();
         mbar_wait(&acc_empty[as], aphase ^ 1);
+        w_acc += clock64() - t0;
         tc_fence_after();
         const uint32_t tmem_acc = BASE0 ? (uint32_t)(as * TILES * BN) : tmem_base + as * TILES * BN;
         for (int cb = 0; cb < ncb; ++cb) {
+          t0 = clock64();
           mbar_wait(&full_a[sa], pa);
+          w_a += clock64() - t0;
           tc_fence_after();
           const uint32_t a_lo = a_lo0 + sa * (halo_stride(TILES) >> 4);
           const uint32_t bres_lo = b_lo0 + cb * (9 * B_BLOCK >> 4);
@@ -373,7 +379,9 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
             if (RESIDENT) {
               b_lo = bres_lo + tap * (B_BLOCK >> 4);
             } else {
+              t0 = clock64();
               mbar_wait(&full_b[sb], pb);
+              w_b += clock64() - t0;
               tc_fence_after();
               b_lo = b_lo0 + sb * (B_BLOCK >> 4);
             }
@@ -382,27 +390,31 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
             for (int h = 0; h < TILES; ++h) {  // the tiles of a super-tile reuse the weight slice
 #pragma unroll
               for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
-                mma_bf16_ss(tmem_acc + h * BN, desc_pack(at_lo + h * 64 + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc,
+                mma_bf16_ss_elect(tmem_acc + h * BN, desc_pack(at_lo + h * 64 + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc,
                             (cb | tap | k) != 0);
             }
             if (!RESIDENT) {
-              tc_commit(&empty_b[sb]);
+              tc_commit_elect(&empty_b[sb]);
               if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
             }
           }
-          tc_commit(&empty_a[sa]);
+          tc_commit_elect(&empty_a[sa]);
           if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
         }
-        tc_commit(&acc_full[as]);
+        tc_commit_elect(&acc_full[as]);
         work += gridDim.x;
       }
     }
     aphase ^= 1;
   }
+  if (p.debug_waits && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
+    printf("  mma thread: total %lld cyc, waiting acc_empty %lld, full_a %lld, full_b %lld (BN %d tiles %d resident %d)\n",
+           clock64() - t_begin, w_acc, w_a, w_b, BN, TILES, (int)RESIDENT);
 }
 
-__host__ __device__ constexpr int interp_warps(int tiles) { return 4 * tiles; }  // a super-tile's halo is 1.8x larger
-__host__ __device__ constexpr int conv_threads(bool interp, int tiles) { return CONV_THREADS + (interp ? interp_warps(tiles) * 32 : 0); }
+// interpolation warps: 8 where a block's MMA time is short (64-wide layers) or its halo large (super-tiles), else 4
+__host__ __device__ constexpr int interp_warps(int bn, int tiles) { return (bn == 64 || tiles == 2) ? 8 : 4; }
+__host__ __device__ constexpr int conv_threads(bool interp, int bn, int tiles) { return CONV_THREADS + (interp ? interp_warps(bn, tiles) * 32 : 0); }
 
 // Low-resolution source patch of one halo block: 18x10 output pixels at x2 span at most 11x7 source pixels.
 constexpr int PATCH_H = 11;
@@ -450,7 +462,7 @@ __device__ __forceinline__ int patch_origin(float r, int first_out, int pad) {
 }
 
 template <int BN, bool RESIDENT, bool INTERP, int TILES>
-__global__ void __launch_bounds__(conv_threads(INTERP, TILES), 1)
+__global__ void __launch_bounds__(conv_threads(INTERP, BN, TILES), 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
                const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
   constexpr int B_BLOCK = BN * BLOCK_K * 2;  // one 64-wide weight slice
@@ -563,16 +575,14 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ================= MMA issuer =================
-      if (tmem_base == 0)
-        halo_mma_loop<BN, RESIDENT, true, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
-      else
-        halo_mma_loop<BN, RESIDENT, false, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
-    }
+    // ================= MMA issuer: the whole warp walks the loop, one elected lane issues =================
+    if (tmem_base == 0)
+      halo_mma_loop<BN, RESIDENT, true, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
+    else
+      halo_mma_loop<BN, RESIDENT, false, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
   } else if (INTERP && warp >= 6) {
     // ================= interpolation producers (warps 6..): halo blocks of the upsampled branch =================
-    constexpr int IT = interp_warps(TILES) * 32;
+    constexpr int IT = interp_warps(BN, TILES) * 32;
     const int t = threadIdx.x - 6 * 32;   // 0..IT-1
     const int j = t & 7;                  // 16-byte chunk (8 channels) this thread owns
     uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
@@ -610,6 +620,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     uint32_t as = 0, aphase = 0;
+    long long epi_wait = 0;
+    const long long epi_begin = clock64();
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
       const int nt = work % p.n_tiles;
       int m = work / p.n_tiles;
@@ -617,7 +629,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       const int ty = m % p.tiles_y;
       const int n = m / p.tiles_y;
       const int y = ty * 16 + (row >> 3);
+      const long long e0 = clock64();
       mbar_wait(&acc_full[as], aphase);
+      epi_wait += clock64() - e0;
       tc_fence_after();
 #pragma unroll
       for (int h = 0; h < TILES; ++h) {
@@ -628,6 +642,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       }
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
+      printf("  epilogue warp: total %lld cyc, waiting acc_full %lld\n", clock64() - epi_begin, epi_wait);
   }
 
   tc_fence_before();
@@ -1071,7 +1087,7 @@ int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUten
     attr_set = true;
   }
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
-  k_conv3x3_halo<BN, RESIDENT, INTERP, TILES><<<grid, conv_threads(INTERP, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
+  k_conv3x3_halo<BN, RESIDENT, INTERP, TILES><<<grid, conv_threads(INTERP, BN, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
   return RDP_OK;
 }
 
@@ -1182,6 +1198,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_forward: workspace %zu < required %zu bytes", workspace_bytes, buf.bytes);
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
+  static const bool debug_waits = getenv("RDP_DEBUG_WAITS") != nullptr;  // development aid, see ConvParams::debug_waits
   static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
   static const bool fuse_all_up = getenv("RDP_FUSE_ALL_UP") != nullptr;
   static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
@@ -1246,6 +1263,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.cin_pad = net->cin_pad[i];
     p.total_work = B * p.tiles_y * p.tiles_x * p.n_tiles;
     p.shift = net->w.conv[i].shift;
+    p.debug_waits = debug_waits;
+    if (debug_waits) { cudaStreamSynchronize(stream); printf("conv %d:\n", i); fflush(stdout); }
     p.out = debug_nostore ? nullptr : buf.act[i];
     if (i == 17) {
       if (!keep_all) p.out = nullptr;  // nobody reads up4.3's activation: the head consumes it in registers
