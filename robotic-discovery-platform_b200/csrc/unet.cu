@@ -133,16 +133,16 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
       for (int cls = 0; cls < 8; ++cls) {
         if (cls < p.n_classes) {
           const float4* hw4 = reinterpret_cast<const float4*>(s_aux + AUX_SHIFT_FLOATS + cls * 64 + c * 32);
-          float a = head[cls];
+          float a0 = head[cls], a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four chains instead of one 64-long dependency
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             const float4 w = hw4[q];
-            a = fmaf(v[4 * q + 0], w.x, a);
-            a = fmaf(v[4 * q + 1], w.y, a);
-            a = fmaf(v[4 * q + 2], w.z, a);
-            a = fmaf(v[4 * q + 3], w.w, a);
+            a0 = fmaf(v[4 * q + 0], w.x, a0);
+            a1 = fmaf(v[4 * q + 1], w.y, a1);
+            a2 = fmaf(v[4 * q + 2], w.z, a2);
+            a3 = fmaf(v[4 * q + 3], w.w, a3);
           }
-          head[cls] = a;
+          head[cls] = (a0 + a1) + (a2 + a3);
         }
       }
     }
@@ -414,7 +414,12 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
 
 // interpolation warps: 8 where a block's MMA time is short (64-wide layers) or its halo large (super-tiles), else 4
 __host__ __device__ constexpr int interp_warps(int bn, int tiles) { return (bn == 64 || tiles == 2) ? 8 : 4; }
-__host__ __device__ constexpr int conv_threads(bool interp, int bn, int tiles) { return CONV_THREADS + (interp ? interp_warps(bn, tiles) * 32 : 0); }
+// epilogue groups of 4 warps: the 64-wide layers finish a tile's MMAs faster than one group drains it, so two groups
+// alternate tiles (each owns one accumulator stage)
+__host__ __device__ constexpr int epi_groups(int bn) { return bn == 64 ? 2 : 1; }
+__host__ __device__ constexpr int conv_threads(bool interp, int bn, int tiles) {
+  return 64 + 128 * epi_groups(bn) + (interp ? interp_warps(bn, tiles) * 32 : 0);
+}
 
 // Low-resolution source patch of one halo block: 18x10 output pixels at x2 span at most 11x7 source pixels.
 constexpr int PATCH_H = 11;
@@ -580,10 +585,10 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       halo_mma_loop<BN, RESIDENT, true, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
     else
       halo_mma_loop<BN, RESIDENT, false, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
-  } else if (INTERP && warp >= 6) {
-    // ================= interpolation producers (warps 6..): halo blocks of the upsampled branch =================
+  } else if (INTERP && warp >= 2 + 4 * epi_groups(BN)) {
+    // ================= interpolation producers (last warps): halo blocks of the upsampled branch =================
     constexpr int IT = interp_warps(BN, TILES) * 32;
-    const int t = threadIdx.x - 6 * 32;   // 0..IT-1
+    const int t = threadIdx.x - (2 + 4 * epi_groups(BN)) * 32;   // 0..IT-1
     const int j = t & 7;                  // 16-byte chunk (8 channels) this thread owns
     uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
@@ -616,13 +621,17 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       }
     }
   } else {
-    // ================= epilogue (warps 2..5) =================
+    // ================= epilogue (groups of 4 warps; with two groups each owns one accumulator stage) =================
+    constexpr int EG = epi_groups(BN);
+    const int group = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    uint32_t as = 0, aphase = 0;
     long long epi_wait = 0;
     const long long epi_begin = clock64();
-    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+    int it = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
+      if (EG > 1 && (it % EG) != group) continue;
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
       const int nt = work % p.n_tiles;
       int m = work / p.n_tiles;
       const int tx = m % p.tiles_x; m /= p.tiles_x;
@@ -640,7 +649,6 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         const uint32_t taddr = tmem_base + (as * TILES + h) * BN + ((uint32_t)(quarter * 32) << 16);
         epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
       }
-      if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
       printf("  epilogue warp: total %lld cyc, waiting acc_full %lld\n", clock64() - epi_begin, epi_wait);
@@ -727,19 +735,33 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, cons
       const int ty = m % p.tiles_y;
       const int n = m / p.tiles_y;
       const int y = ty * p.tile_h + ry, x = tx * p.tile_w + rx;
+      // all 9*C loads are issued before the first table look-up (one dependent chain per tile, not 27)
       uint16_t v[64];
 #pragma unroll
       for (int k = 0; k < 64; ++k) v[k] = 0;
       if (y < p.H && x < p.W) {
+        if (U8) {
+          uint8_t raw[9 * C];
+          bool ok[9];
 #pragma unroll
-        for (int tap = 0; tap < 9; ++tap) {
-          const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
-          if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+          for (int tap = 0; tap < 9; ++tap) {
+            const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+            ok[tap] = yy >= 0 && yy < p.H && xx >= 0 && xx < p.W;
+            const uint8_t* src = (const uint8_t*)in + (((size_t)n * p.H + (ok[tap] ? yy : y)) * p.W + (ok[tap] ? xx : x)) * C;
 #pragma unroll
-            for (int c = 0; c < C; ++c) {
-              if (U8) {
-                v[tap * C + c] = s_lut[__ldg((const uint8_t*)in + (((size_t)n * p.H + yy) * p.W + xx) * C + c)];
-              } else {
+            for (int c = 0; c < C; ++c) raw[tap * C + c] = __ldg(src + c);
+          }
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+            for (int c = 0; c < C; ++c) v[tap * C + c] = ok[tap] ? s_lut[raw[tap * C + c]] : (uint16_t)0;
+        } else {
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+            if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+#pragma unroll
+              for (int c = 0; c < C; ++c) {
                 const __nv_bfloat16 b = __float2bfloat16_rn(__ldg((const float*)in + (((size_t)n * C + c) * p.H + yy) * p.W + xx));
                 v[tap * C + c] = *reinterpret_cast<const uint16_t*>(&b);
               }
@@ -1199,6 +1221,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
   static const bool debug_waits = getenv("RDP_DEBUG_WAITS") != nullptr;  // development aid, see ConvParams::debug_waits
+  static const bool debug_nohead = getenv("RDP_DEBUG_NOHEAD") != nullptr;    // timing experiments only
   static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
   static const bool fuse_all_up = getenv("RDP_FUSE_ALL_UP") != nullptr;
   static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
@@ -1266,7 +1289,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.debug_waits = debug_waits;
     if (debug_waits) { cudaStreamSynchronize(stream); printf("conv %d:\n", i); fflush(stdout); }
     p.out = debug_nostore ? nullptr : buf.act[i];
-    if (i == 17) {
+    if (i == 17 && !debug_nohead) {
       if (!keep_all) p.out = nullptr;  // nobody reads up4.3's activation: the head consumes it in registers
       p.head_w = net->w.outc_weight;
       p.head_b = net->w.outc_bias;
