@@ -62,6 +62,8 @@ struct ConvParams {
   int pad_y, pad_x;          // offset of the interpolated image inside the skip-sized frame (Up.forward's F.pad)
   float ry, rx;              // align_corners=True scales (h-1)/(2h-1), (w-1)/(2w-1)
   int debug_waits;           // development aid: CTA 0 prints where its MMA and epilogue threads waited
+  // fused MaxPool2d(2): second, pooled output of the layers that feed a Down block (8-wide tiles only)
+  __nv_bfloat16* pool_out;   // (B, H/2, W/2, cout) NHWC or null
 };
 
 constexpr int AUX_SHIFT_FLOATS = 512;   // BN shift of every output channel of the layer
@@ -102,7 +104,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // Drains one 128 x BN fp32 accumulator tile: BN shift + ReLU -> bf16 NHWC store; for the last layer also the 1x1
 // OutConv (+ mask rule).  Thread = one pixel (TMEM lane); 32-column chunks, the next chunk's tcgen05.ld is in
 // flight while the current one is processed.
-template <int BN>
+template <int BN, bool POOL = false>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* s_aux, uint32_t taddr, int nt, int n, int y,
                                               int x, bool inside, uint64_t* acc_empty_bar, int lane) {
   const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
@@ -146,7 +148,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
         }
       }
     }
-    if (inside && p.out != nullptr) {
+    if (p.out != nullptr) {
       // 32 bytes (one full DRAM sector) per store instruction
       __nv_bfloat16* dst = p.out + pixel * p.cout + nt * BN + c * 32;
 #pragma unroll
@@ -154,9 +156,31 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
         uint32_t o[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) o[e] = pack_bf16x2<true>(v[16 * q + 2 * e], v[16 * q + 2 * e + 1]);
-        asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * q), "r"(o[0]), "r"(o[1]),
-                     "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
-                     : "memory");
+        if (inside)
+          asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * q), "r"(o[0]), "r"(o[1]),
+                       "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
+                       : "memory");
+        if (POOL && p.pool_out != nullptr) {
+          // MaxPool2d(2) on the rounded values (rounding is monotone, so max commutes with it).  In an 8-wide tile
+          // the pixel is (lane >> 3, lane & 7) within the warp's four rows: window partners are lanes ^1 and ^8.
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            __nv_bfloat162 a = *reinterpret_cast<__nv_bfloat162*>(&o[e]);
+            uint32_t t1 = __shfl_xor_sync(0xffffffffu, o[e], 1);
+            a = __hmax2(a, *reinterpret_cast<__nv_bfloat162*>(&t1));
+            uint32_t au = *reinterpret_cast<uint32_t*>(&a);
+            uint32_t t8 = __shfl_xor_sync(0xffffffffu, au, 8);
+            a = __hmax2(a, *reinterpret_cast<__nv_bfloat162*>(&t8));
+            o[e] = *reinterpret_cast<uint32_t*>(&a);
+          }
+          const int Ho = p.H >> 1, Wo = p.W >> 1, yo = y >> 1, xo = x >> 1;
+          if (!(lane & 9) && yo < Ho && xo < Wo) {
+            __nv_bfloat16* pd = p.pool_out + (((size_t)n * Ho + yo) * Wo + xo) * p.cout + nt * BN + c * 32 + 16 * q;
+            asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(pd), "r"(o[0]), "r"(o[1]), "r"(o[2]),
+                         "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
+                         : "memory");
+          }
+        }
       }
     }
   }
@@ -647,7 +671,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         const int x = tx * 8 * TILES + h * 8 + (row & 7);
         const bool inside = y < p.H && x < p.W;
         const uint32_t taddr = tmem_base + (as * TILES + h) * BN + ((uint32_t)(quarter * 32) << 16);
-        epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
+        epilogue_tile<BN, true>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
       }
     }
     if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
@@ -1223,6 +1247,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   static const bool debug_waits = getenv("RDP_DEBUG_WAITS") != nullptr;  // development aid, see ConvParams::debug_waits
   static const bool debug_nohead = getenv("RDP_DEBUG_NOHEAD") != nullptr;    // timing experiments only
   static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
+  static const bool no_fuse_pool = getenv("RDP_NO_FUSE_POOL") != nullptr;  // development switch: separate pooling kernel
   static const bool fuse_all_up = getenv("RDP_FUSE_ALL_UP") != nullptr;
   static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
   static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
@@ -1268,7 +1293,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   // one conv launch: sources (src0 with c0 channels [+ src1 with c1 channels]) at level `lvl` -> act[i]
   struct LowSrc { const __nv_bfloat16* ptr; int h, w, pad_y, pad_x; };
   auto conv = [&](int i, const __nv_bfloat16* src0, int c0, const __nv_bfloat16* src1, int c1, int taps,
-                  const LowSrc* low = nullptr) -> int {
+                  const LowSrc* low = nullptr, __nv_bfloat16* pool_out = nullptr) -> int {
     const Level L = buf.lv[kConvLevel[i]];
     ConvParams p{};
     p.B = B; p.H = L.H; p.W = L.W;
@@ -1287,6 +1312,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.total_work = B * p.tiles_y * p.tiles_x * p.n_tiles;
     p.shift = net->w.conv[i].shift;
     p.debug_waits = debug_waits;
+    p.pool_out = pool_out;
     if (debug_waits) { cudaStreamSynchronize(stream); printf("conv %d:\n", i); fflush(stdout); }
     p.out = debug_nostore ? nullptr : buf.act[i];
     if (i == 17 && !debug_nohead) {
@@ -1336,15 +1362,20 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
 
   // encoder: inc, down1..down4 (segmentation_model.py:110-114)
   if (!first_fused) RDP_TRY(conv(0, buf.col, 64, nullptr, 0, 1));
-  RDP_TRY(conv(1, buf.act[0], 64, nullptr, 0, 9));
+  // MaxPool2d(2) of x1..x4 is a second output of the producing conv's epilogue (halo kernels); the stand-alone
+  // pooling kernel remains for the per-tap fallback
+  auto fused_pool = [&](int i) { return !force_v1 && !no_fuse_pool && sel[i] == 'h'; };
+  RDP_TRY(conv(1, buf.act[0], 64, nullptr, 0, 9, nullptr, fused_pool(1) ? buf.pool[0] : nullptr));
   for (int d = 0; d < 4; ++d) {
     const Level L = buf.lv[d];
     const int C = net->w.conv[2 * d + 1].cout;
     const int C8 = C / 8;
-    k_maxpool2<<<dim3(((L.W / 2) * C8 + 255) / 256, L.H / 2, B), 256, 0, stream>>>(buf.act[2 * d + 1], L.H, L.W, C8, log2_exact(C8), buf.pool[d]);
+    if (!fused_pool(2 * d + 1))
+      k_maxpool2<<<dim3(((L.W / 2) * C8 + 255) / 256, L.H / 2, B), 256, 0, stream>>>(buf.act[2 * d + 1], L.H, L.W, C8, log2_exact(C8), buf.pool[d]);
     mark();
     RDP_TRY(conv(2 * d + 2, buf.pool[d], C, nullptr, 0, 9));
-    RDP_TRY(conv(2 * d + 3, buf.act[2 * d + 2], net->w.conv[2 * d + 2].cout, nullptr, 0, 9));
+    RDP_TRY(conv(2 * d + 3, buf.act[2 * d + 2], net->w.conv[2 * d + 2].cout, nullptr, 0, 9, nullptr,
+                 (d < 3 && fused_pool(2 * d + 3)) ? buf.pool[d + 1] : nullptr));
   }
   // decoder: up1..up4 (segmentation_model.py:115-118); skip channels first, then the upsampled branch
   for (int j = 0; j < 4; ++j) {
