@@ -92,6 +92,14 @@ __device__ __forceinline__ void stage_aux(const ConvParams& p, float* s_aux) {
   }
 }
 
+// 16-byte read from shared memory by shared-window address (a generic LD through a pointer the compiler cannot
+// prove to be shared is slower than LDS)
+__device__ __forceinline__ float4 lds_f4(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+
 // two fp32 -> packed bf16x2 (lo = first element), optionally clamped at zero by the conversion itself
 template <bool RELU>
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -118,11 +126,11 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
   for (int c = 0; c < BN / 32; ++c) {
     tmem_ld_wait();
     if (c + 1 < BN / 32) tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
-    const float4* sh4 = reinterpret_cast<const float4*>(s_aux + nt * BN + c * 32);
+    const uint32_t sh_addr = smem_u32(s_aux + nt * BN + c * 32);
     float v[32];
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
-      const float4 sh = sh4[q];
+      const float4 sh = lds_f4(sh_addr + 16 * q);
       v[4 * q + 0] = __uint_as_float(r[c & 1][4 * q + 0]) + sh.x;
       v[4 * q + 1] = __uint_as_float(r[c & 1][4 * q + 1]) + sh.y;
       v[4 * q + 2] = __uint_as_float(r[c & 1][4 * q + 2]) + sh.z;
@@ -134,11 +142,11 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
 #pragma unroll
       for (int cls = 0; cls < 8; ++cls) {
         if (cls < p.n_classes) {
-          const float4* hw4 = reinterpret_cast<const float4*>(s_aux + AUX_SHIFT_FLOATS + cls * 64 + c * 32);
+          const uint32_t hw_addr = smem_u32(s_aux + AUX_SHIFT_FLOATS + cls * 64 + c * 32);
           float a0 = head[cls], a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four chains instead of one 64-long dependency
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
-            const float4 w = hw4[q];
+            const float4 w = lds_f4(hw_addr + 16 * q);
             a0 = fmaf(v[4 * q + 0], w.x, a0);
             a1 = fmaf(v[4 * q + 1], w.y, a1);
             a2 = fmaf(v[4 * q + 2], w.z, a2);
@@ -440,9 +448,9 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
 __host__ __device__ constexpr int interp_warps(int bn, int tiles) { return (bn == 64 || tiles == 2) ? 8 : 4; }
 // epilogue groups of 4 warps: the 64-wide layers finish a tile's MMAs faster than one group drains it, so two groups
 // alternate tiles (each owns one accumulator stage)
-__host__ __device__ constexpr int epi_groups(int bn) { return bn == 64 ? 2 : 1; }
+__host__ __device__ constexpr int epi_groups(int bn, bool interp = false) { return (bn == 64 && !interp) ? 2 : 1; }
 __host__ __device__ constexpr int conv_threads(bool interp, int bn, int tiles) {
-  return 64 + 128 * epi_groups(bn) + (interp ? interp_warps(bn, tiles) * 32 : 0);
+  return 64 + 128 * epi_groups(bn, interp) + (interp ? interp_warps(bn, tiles) * 32 : 0);
 }
 
 // Low-resolution source patch of one halo block: 18x10 output pixels at x2 span at most 11x7 source pixels.
@@ -609,10 +617,10 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       halo_mma_loop<BN, RESIDENT, true, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, 0);
     else
       halo_mma_loop<BN, RESIDENT, false, TILES>(p, cfg, smem_a, smem_b, full_a, empty_a, full_b, empty_b, w_full, acc_full, acc_empty, tmem_base);
-  } else if (INTERP && warp >= 2 + 4 * epi_groups(BN)) {
+  } else if (INTERP && warp >= 2 + 4 * epi_groups(BN, INTERP)) {
     // ================= interpolation producers (last warps): halo blocks of the upsampled branch =================
     constexpr int IT = interp_warps(BN, TILES) * 32;
-    const int t = threadIdx.x - (2 + 4 * epi_groups(BN)) * 32;   // 0..IT-1
+    const int t = threadIdx.x - (2 + 4 * epi_groups(BN, INTERP)) * 32;   // 0..IT-1
     const int j = t & 7;                  // 16-byte chunk (8 channels) this thread owns
     uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
@@ -646,7 +654,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     }
   } else {
     // ================= epilogue (groups of 4 warps; with two groups each owns one accumulator stage) =================
-    constexpr int EG = epi_groups(BN);
+    constexpr int EG = epi_groups(BN, INTERP);
     const int group = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
