@@ -826,11 +826,16 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, cons
       const uint64_t db = make_sw128_desc(smem_u32(smem_b));
       uint32_t as = 0, aphase = 0;
       int it = 0;
+      long long w_acc = 0, w_a = 0, t_begin = clock64(), t0;
       for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
         const int stage = it % FIRST_STAGES;
         const uint32_t phase = (uint32_t)(it / FIRST_STAGES) & 1u;
+        t0 = clock64();
         mbar_wait(&acc_empty[as], aphase ^ 1);
+        w_acc += clock64() - t0;
+        t0 = clock64();
         mbar_wait(&a_full[stage], phase);
+        w_a += clock64() - t0;
         tc_fence_after();
         const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * A_STAGE_BYTES));
 #pragma unroll
@@ -839,6 +844,9 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, cons
         tc_commit(&acc_full[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
+      if (p.debug_waits && blockIdx.x == 0)
+        printf("first layer mma thread: total %lld cyc, waiting acc_empty (epilogue) %lld, a_full (producers) %lld\n",
+               clock64() - t_begin, w_acc, w_a);
     }
   } else {
     // ================= epilogue =================
@@ -1281,6 +1289,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.cout = 64; p.n_tiles = 1; p.kb0 = 1; p.taps = 1; p.cin_pad = 64;
     p.total_work = B * p.tiles_y * p.tiles_x;
     p.shift = net->w.conv[0].shift;
+    p.debug_waits = debug_waits;
     p.out = debug_nostore ? nullptr : buf.act[0];
     int rc = RDP_OK;
     mark();  // (slot of the im2col launch)
