@@ -137,8 +137,8 @@ int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, in
 int rdp_geom_launch_count(void);
 
 /* Measurement aid (no counterpart in the reference): as rdp_geom_curvature, with a CUDA event between launches;
- * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, bin_hist, bin_offsets,
- * scatter, select_sort, fit, fit_knots. */
+ * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, xrange, bin_hist,
+ * bin_offsets, scatter, select_sort, fit, fit_knots. */
 int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                                 const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
                                 void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);

@@ -10,7 +10,8 @@
 // Data layout (HBM): mask u8 [B][P], depth u16|f32 [B][P] (P = H*W), workspace arrays indexed [b][i].
 // Kernels (one launch each per batch, all on the caller's stream, no host sync):
 //   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once, writes 4N (pixel ids) + 12N (fp32 xyz); 16384-pixel tiles
-//   k_bin_hist     L2/HBM      reads 4N + gathers 2N, writes N (bin ids) + 8N (fp64 y keys for the selection)
+//   k_xrange       L2/HBM      reads 4N + gathers 2N, writes 16N (fp64 x and y keys), x range by atomics
+//   k_bin_hist     L2/HBM      reads 8N, writes N (bin ids)
 //   k_bin_offsets  tiny        50 bins per frame -> k per bin, offsets, status
 //   k_scatter      L2/HBM      reads 13N, writes 12N (pixel ids and y keys grouped by bin)
 //   k_select_sort  latency     one CTA per (frame, bin): radix select of the k largest y, bitonic sort by x
@@ -69,6 +70,7 @@ struct Params {
   uint32_t* pix;       // [B][P] valid pixel ids, row-major order
   uint8_t* bins;       // [B][P] bin id per valid point
   uint32_t* binned;    // [B][P] pixel ids grouped by bin
+  unsigned long long* xkey_c;  // [B][P] ordered fp64 x key per valid point (compacted order), written by k_xrange
   unsigned long long* ykey_c;  // [B][P] ordered fp64 y key per valid point (compacted order)
   unsigned long long* ykey_b;  // [B][P] the same, grouped by bin like `binned`
   uint32_t* edge_pix;  // [B][ecap] selected pixel ids, ordered by x
@@ -160,7 +162,6 @@ template <bool VEC>
 __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   __shared__ uint16_t s_pix[TILE_PX];  // tile-relative pixel offsets of the valid points
   __shared__ int s_warp[DP_THREADS / 32];
-  __shared__ unsigned long long s_red[2][DP_THREADS / 32];
   __shared__ int s_ticket, s_base, s_total;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_ticket = (int)atomicAdd(p.ticket, 1u);  // tiles are claimed in launch order: no look-back deadlock
@@ -266,27 +267,46 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   }
   __syncthreads();
 
-  // cooperative, coalesced emission of the tile's points
+  // cooperative, coalesced emission of the tile's points (the x range and the fp64 keys are k_xrange's job, which keeps
+  // this streaming kernel light; the fp32 cloud is only computed when the caller asked for it)
   const int total = s_total, base = s_base;
-  unsigned long long kmax = 0, kmin_inv = 0;
   for (int j = tid; j < total; j += DP_THREADS) {
     const uint32_t px = (uint32_t)(t * TILE_PX) + s_pix[j];
-    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
-    const double z = depth_to_z(p, fbase + px);
-    const double x = deproject_axis((double)u, p.cx, z, p.fx);
     const size_t o = fbase + base + j;
     p.pix[o] = px;
     if (p.out.points_xyz) {
-      const double y = deproject_axis((double)v, p.cy, z, p.fy);
+      const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
+      const double z = depth_to_z(p, fbase + px);
       float* dst = p.out.points_xyz + 3 * o;
-      dst[0] = (float)x;
-      dst[1] = (float)y;
+      dst[0] = (float)deproject_axis((double)u, p.cx, z, p.fx);
+      dst[1] = (float)deproject_axis((double)v, p.cy, z, p.fy);
       dst[2] = (float)z;
     }
-    const unsigned long long k = ordered_key(x);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_xrange: fp64 x / y keys of the valid points and the frame's x range (geometry_utils.py:114-115,124)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PT_THREADS) k_xrange(const Params p) {
+  __shared__ unsigned long long s_red[2][PT_THREADS / 32];
+  const int b = blockIdx.y;
+  const int n = p.fs[b].n_points, i0 = blockIdx.x * PT_PER_BLOCK;
+  if (i0 >= n) return;
+  const size_t fbase = (size_t)b * p.P;
+  const int i1 = min(n, i0 + PT_PER_BLOCK);
+  unsigned long long kmax = 0, kmin_inv = 0;
+  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
+    const uint32_t px = p.pix[fbase + i];
+    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
+    const double z = depth_to_z(p, fbase + px);
+    const unsigned long long k = ordered_key(deproject_axis((double)u, p.cx, z, p.fx));
+    p.xkey_c[fbase + i] = k;
+    p.ykey_c[fbase + i] = ordered_key(deproject_axis((double)v, p.cy, z, p.fy));  // selection key for k_select_sort
     kmax = k > kmax ? k : kmax;
     kmin_inv = ~k > kmin_inv ? ~k : kmin_inv;
   }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   kmax = warp_max(kmax);
   kmin_inv = warp_max(kmin_inv);
   if (lane == 0) {
@@ -294,8 +314,8 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
     s_red[1][warp] = kmin_inv;
   }
   __syncthreads();
-  if (tid == 0 && total > 0) {
-    for (int w = 1; w < DP_THREADS / 32; ++w) {
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < PT_THREADS / 32; ++w) {
       kmax = s_red[0][w] > kmax ? s_red[0][w] : kmax;
       kmin_inv = s_red[1][w] > kmin_inv ? s_red[1][w] : kmin_inv;
     }
@@ -319,13 +339,8 @@ __global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
   const size_t fbase = (size_t)b * p.P;
   const int i1 = min(n, i0 + PT_PER_BLOCK);
   for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
-    const uint32_t px = p.pix[fbase + i];
-    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
-    const double z = depth_to_z(p, fbase + px);
-    const double x = deproject_axis((double)u, p.cx, z, p.fx);
-    const int bin = bin_of(x, x_min, width);
+    const int bin = bin_of(key_to_double(p.xkey_c[fbase + i]), x_min, width);
     p.bins[fbase + i] = (uint8_t)bin;
-    p.ykey_c[fbase + i] = ordered_key(deproject_axis((double)v, p.cy, z, p.fy));  // selection key for k_select_sort
     atomicAdd(&s_hist[bin], 1);
   }
   __syncthreads();
@@ -1311,6 +1326,7 @@ static Plan carve(Params& p, KnotWs& kn, void* ws, int B, int H, int W) {
   p.pix = c.take<uint32_t>(B * P);
   p.bins = c.take<uint8_t>(B * P);
   p.binned = c.take<uint32_t>(B * P);
+  p.xkey_c = c.take<unsigned long long>(B * P);
   p.ykey_c = c.take<unsigned long long>(B * P);
   p.ykey_b = c.take<unsigned long long>(B * P);
   p.edge_pix = c.take<uint32_t>((size_t)B * pl.ecap);
@@ -1339,7 +1355,7 @@ extern "C" int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes) {
   return RDP_OK;
 }
 
-extern "C" int rdp_geom_launch_count(void) { return 8; }
+extern "C" int rdp_geom_launch_count(void) { return 9; }
 
 static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                           const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
@@ -1379,6 +1395,8 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   else k_deproject<false><<<tiles_total, DP_THREADS, 0, stream>>>(p);
   mark();
   const dim3 pgrid((p.P + PT_PER_BLOCK - 1) / PT_PER_BLOCK, B);
+  k_xrange<<<pgrid, PT_THREADS, 0, stream>>>(p);
+  mark();
   k_bin_hist<<<pgrid, PT_THREADS, 0, stream>>>(p);
   mark();
   k_bin_offsets<<<(B + 63) / 64, 64, 0, stream>>>(p);
