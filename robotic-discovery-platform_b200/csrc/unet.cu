@@ -706,18 +706,22 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
 constexpr int FIRST_STAGES = 4;
 constexpr int FIRST_PRODUCER_WARPS = 12;  // three groups of 128 threads
 constexpr int FIRST_MMA_WARP = FIRST_PRODUCER_WARPS;
-constexpr int FIRST_THREADS = (FIRST_PRODUCER_WARPS + 1 + 4) * 32;
-constexpr int FIRST_SMEM = FIRST_STAGES * A_STAGE_BYTES + 64 * BLOCK_K * 2 + 1024 + 256 + AUX_BYTES + 512;
+constexpr int FIRST_EPI_GROUPS = 2;  // each group of 4 warps owns one accumulator stage and one output staging tile
+constexpr int FIRST_THREADS = (FIRST_PRODUCER_WARPS + 1 + 4 * FIRST_EPI_GROUPS) * 32;
+constexpr int FIRST_OUT_BYTES = TILE_M * 64 * 2;  // bf16 output tile staged for the TMA store
+constexpr int FIRST_SMEM = FIRST_STAGES * A_STAGE_BYTES + 64 * BLOCK_K * 2 + 2 * FIRST_OUT_BYTES + 1024 + 256 + AUX_BYTES + 512;
 
 template <int C, bool U8>
 __global__ void __launch_bounds__(FIRST_THREADS, 1)
-k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, const void* __restrict__ in) {
+k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_out, const ConvParams p,
+             const void* __restrict__ in) {
   constexpr int BN = 64;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + FIRST_STAGES * A_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_b + BN * BLOCK_K * 2);
+  uint8_t* smem_o = smem_b + BN * BLOCK_K * 2;  // two output tiles (one per accumulator stage), 1024-byte aligned
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + 2 * FIRST_OUT_BYTES);
   uint64_t* a_full = bars;                   // [FIRST_STAGES], 128 producer arrivals each
   uint64_t* a_empty = bars + FIRST_STAGES;   // [FIRST_STAGES]
   uint64_t* w_full = bars + 2 * FIRST_STAGES;
@@ -730,6 +734,7 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     prefetch_tensormap(&map_w);
+    prefetch_tensormap(&map_out);
     for (int s = 0; s < FIRST_STAGES; ++s) {
       mbar_init(&a_full[s], 128);
       mbar_init(&a_empty[s], 1);
@@ -849,23 +854,57 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const ConvParams p, cons
                clock64() - t_begin, w_acc, w_a);
     }
   } else {
-    // ================= epilogue =================
+    // ================= epilogue: TMEM -> shift, ReLU, bf16 -> swizzled smem tile -> one TMA store =================
+    // A thread owns a pixel (128 bytes of channels); storing that straight to global memory touches 32 different
+    // 128-byte lines per warp instruction.  Staging the tile and letting the TMA unit write it (full lines, image
+    // borders clipped by the tensor map) removes that cost from the epilogue, which is this layer's bottleneck.
+    const int group = (warp - FIRST_MMA_WARP - 1) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    uint32_t as = 0, aphase = 0;
-    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
+    const bool issuer = ((warp - FIRST_MMA_WARP - 1) & 3) == 0 && lane == 0;
+    int it = 0;
+    for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
+      if ((it % FIRST_EPI_GROUPS) != group) continue;
+      const uint32_t as = it & 1, aphase = (it >> 1) & 1;   // with two groups: as == group
       int m = work;
       const int tx = m % p.tiles_x; m /= p.tiles_x;
       const int ty = m % p.tiles_y;
       const int n = m / p.tiles_y;
-      const int y = ty * p.tile_h + row / p.tile_w, x = tx * p.tile_w + row % p.tile_w;
-      const bool inside = y < p.H && x < p.W;
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
+      if (issuer) tma_store_wait_read<0>();       // this group's previous store has finished reading the buffer
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + group) : "memory");
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
-      epilogue_tile<BN>(p, s_aux, taddr, 0, n, y, x, inside, &acc_empty[as], lane);
-      if (++as == 2) { as = 0; aphase ^= 1; }
+      uint8_t* orow = smem_o + as * FIRST_OUT_BYTES + row * 128;
+      uint32_t r[2][32];
+      tmem_ld_32x32(taddr, r[0]);
+#pragma unroll
+      for (int c = 0; c < BN / 32; ++c) {
+        tmem_ld_wait();
+        if (c + 1 < BN / 32) tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+        const uint32_t sh_addr = smem_u32(s_aux + c * 32);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {   // four 16-byte pieces of 8 channels
+          const float4 s0 = lds_f4(sh_addr + 32 * e), s1 = lds_f4(sh_addr + 32 * e + 16);
+          uint4 o;
+          o.x = pack_bf16x2<true>(__uint_as_float(r[c & 1][8 * e + 0]) + s0.x, __uint_as_float(r[c & 1][8 * e + 1]) + s0.y);
+          o.y = pack_bf16x2<true>(__uint_as_float(r[c & 1][8 * e + 2]) + s0.z, __uint_as_float(r[c & 1][8 * e + 3]) + s0.w);
+          o.z = pack_bf16x2<true>(__uint_as_float(r[c & 1][8 * e + 4]) + s1.x, __uint_as_float(r[c & 1][8 * e + 5]) + s1.y);
+          o.w = pack_bf16x2<true>(__uint_as_float(r[c & 1][8 * e + 6]) + s1.z, __uint_as_float(r[c & 1][8 * e + 7]) + s1.w);
+          *reinterpret_cast<uint4*>(orow + (((c * 4 + e) ^ (row & 7)) << 4)) = o;   // the tensor map's 128-byte swizzle
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[as]);
+      fence_proxy_async();                        // smem writes -> visible to the TMA unit
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + group) : "memory");
+      if (issuer && p.out != nullptr) {
+        tma_store_4d(&map_out, smem_o + as * FIRST_OUT_BYTES, 0, tx * p.tile_w, ty * p.tile_h, n);
+        tma_store_commit();
+      }
     }
+    if (issuer) tma_store_wait_read<0>();         // shared memory must outlive the last store's reads
   }
 
   tc_fence_before();
@@ -1115,27 +1154,28 @@ int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorM
 }
 
 template <int C, bool U8>
-int launch_conv_first_t(const CUtensorMap& wm, const ConvParams& p, const void* in, int num_sms, cudaStream_t stream) {
+int launch_conv_first_t(const CUtensorMap& wm, const CUtensorMap& om, const ConvParams& p, const void* in, int num_sms,
+                        cudaStream_t stream) {
   static bool attr_set = false;
   if (!attr_set) {
     RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv_first<C, U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FIRST_SMEM));
     attr_set = true;
   }
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
-  k_conv_first<C, U8><<<grid, FIRST_THREADS, FIRST_SMEM, stream>>>(wm, p, in);
+  k_conv_first<C, U8><<<grid, FIRST_THREADS, FIRST_SMEM, stream>>>(wm, om, p, in);
   return RDP_OK;
 }
 
 // returns 1 when a specialised kernel exists for this channel count (else the im2col path is used)
-int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const ConvParams& p, const void* in, int num_sms,
-                      cudaStream_t stream, int* rc) {
+int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const CUtensorMap& om, const ConvParams& p, const void* in,
+                      int num_sms, cudaStream_t stream, int* rc) {
   switch (C * 2 + (u8 ? 1 : 0)) {
-    case 3: *rc = launch_conv_first_t<1, true>(wm, p, in, num_sms, stream); return 1;
-    case 2: *rc = launch_conv_first_t<1, false>(wm, p, in, num_sms, stream); return 1;
-    case 7: *rc = launch_conv_first_t<3, true>(wm, p, in, num_sms, stream); return 1;
-    case 6: *rc = launch_conv_first_t<3, false>(wm, p, in, num_sms, stream); return 1;
-    case 9: *rc = launch_conv_first_t<4, true>(wm, p, in, num_sms, stream); return 1;
-    case 8: *rc = launch_conv_first_t<4, false>(wm, p, in, num_sms, stream); return 1;
+    case 3: *rc = launch_conv_first_t<1, true>(wm, om, p, in, num_sms, stream); return 1;
+    case 2: *rc = launch_conv_first_t<1, false>(wm, om, p, in, num_sms, stream); return 1;
+    case 7: *rc = launch_conv_first_t<3, true>(wm, om, p, in, num_sms, stream); return 1;
+    case 6: *rc = launch_conv_first_t<3, false>(wm, om, p, in, num_sms, stream); return 1;
+    case 9: *rc = launch_conv_first_t<4, true>(wm, om, p, in, num_sms, stream); return 1;
+    case 8: *rc = launch_conv_first_t<4, false>(wm, om, p, in, num_sms, stream); return 1;
     default: return 0;
   }
 }
@@ -1293,7 +1333,10 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.out = debug_nostore ? nullptr : buf.act[0];
     int rc = RDP_OK;
     mark();  // (slot of the im2col launch)
-    if (launch_conv_first(net->w.n_channels, in_fmt == RDP_IN_RGB_U8_NHWC, net->wmap[0], p, input, net->num_sms, stream, &rc)) {
+    CUtensorMap omap;
+    rc = make_act_map(&omap, buf.act[0], B, H, W, 64, p.tile_w, p.tile_h);
+    if (rc != RDP_OK) return rc;
+    if (launch_conv_first(net->w.n_channels, in_fmt == RDP_IN_RGB_U8_NHWC, net->wmap[0], omap, p, input, net->num_sms, stream, &rc)) {
       if (rc != RDP_OK) return rc;
       first_fused = true;
       mark();
