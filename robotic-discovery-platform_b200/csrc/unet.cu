@@ -87,8 +87,8 @@ __device__ __forceinline__ bool mask_rule(float logit) { return logit > 8.940697
 __device__ __forceinline__ void stage_aux(const ConvParams& p, float* s_aux) {
   for (int i = threadIdx.x; i < p.cout; i += blockDim.x) s_aux[i] = __ldg(p.shift + i);
   if (p.head_w != nullptr) {
-    for (int i = threadIdx.x; i < p.n_classes * 64; i += blockDim.x) s_aux[AUX_SHIFT_FLOATS + i] = __ldg(p.head_w + i);
-    if (threadIdx.x < p.n_classes) s_aux[AUX_SHIFT_FLOATS + AUX_HEAD_FLOATS + threadIdx.x] = __ldg(p.head_b + threadIdx.x);
+    for (int i = threadIdx.x; i < p.n_classes * 64; i += blockDim.x) s_aux[p.cout + i] = __ldg(p.head_w + i);
+    if (threadIdx.x < p.n_classes) s_aux[p.cout + AUX_HEAD_FLOATS + threadIdx.x] = __ldg(p.head_b + threadIdx.x);
   }
 }
 
@@ -142,7 +142,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
 #pragma unroll
       for (int cls = 0; cls < 8; ++cls) {
         if (cls < p.n_classes) {
-          const uint32_t hw_addr = smem_u32(s_aux + AUX_SHIFT_FLOATS + cls * 64 + c * 32);
+          const uint32_t hw_addr = smem_u32(s_aux + p.cout + cls * 64 + c * 32);
           float a0 = head[cls], a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four chains instead of one 64-long dependency
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -203,7 +203,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
 #pragma unroll
     for (int cls = 0; cls < 8; ++cls) {
       if (cls < p.n_classes) {
-        const float logit = head[cls] + s_aux[AUX_SHIFT_FLOATS + AUX_HEAD_FLOATS + cls];
+        const float logit = head[cls] + s_aux[p.cout + AUX_HEAD_FLOATS + cls];
         const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
         if (p.logits) p.logits[o] = logit;
         if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
@@ -354,10 +354,13 @@ __host__ __device__ constexpr int halo_bytes(int tiles) { return halo_w(tiles) *
 __host__ __device__ constexpr int halo_stride(int tiles) { return (halo_bytes(tiles) + 1023) / 1024 * 1024; }
 constexpr int HALO_SMEM_TOTAL = 227 * 1024;
 constexpr int HALO_MAX_STAGES = 12;
-constexpr int HALO_BAR_BYTES = 512 + AUX_BYTES;
+constexpr int HALO_BAR_BYTES = 512;  // barriers; the epilogue constants follow (aux_bytes())
+// shift[cout], then (only for the head layer) OutConv weights and bias
+inline int aux_bytes(int cout, bool head) { return (cout + (head ? AUX_HEAD_FLOATS + 8 : 0)) * 4; }
 
 struct HaloCfg {
   int sa, sb;  // A (halo) stages, B (weight slice) stages
+  int sl;      // source-patch stages of the fused upsample (1 or 2)
 };
 
 // High word of a SWIZZLE_128B K-major descriptor: stride between 8-row groups, version 1, layout type 2.
@@ -458,7 +461,7 @@ constexpr int PATCH_H = 11;
 __host__ __device__ constexpr int patch_w(int tiles) { return tiles == 1 ? 7 : 11; }  // 10 / 18 output columns at x2
 __host__ __device__ constexpr int patch_bytes(int tiles) { return patch_w(tiles) * PATCH_H * 128; }
 __host__ __device__ constexpr int patch_stride(int tiles) { return (patch_bytes(tiles) + 1023) / 1024 * 1024; }
-constexpr int PATCH_STAGES = 2;
+constexpr int PATCH_STAGES = 2;  // upper bound; HaloCfg::sl is what a launch uses
 
 // Bilinear x2 (align_corners=True) + zero pad of one 16-byte chunk (8 channels) of one halo pixel, read from the
 // source patch in shared memory, in the same fp32 operation order as k_upsample2x, so that fusing the interpolation
@@ -513,7 +516,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
   const int b_bytes = RESIDENT ? 9 * ncb * B_BLOCK : cfg.sb * B_BLOCK;
   uint8_t* smem_l = smem_b + b_bytes;  // low-resolution source patches (INTERP only)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_l + (INTERP ? PATCH_STAGES * PATCH_STRIDE : 0));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_l + (INTERP ? cfg.sl * PATCH_STRIDE : 0));
   uint64_t* full_a = bars;                          // [HALO_MAX_STAGES]
   uint64_t* empty_a = bars + HALO_MAX_STAGES;       // [HALO_MAX_STAGES]
   uint64_t* full_b = bars + 2 * HALO_MAX_STAGES;    // [HALO_MAX_STAGES]
@@ -581,11 +584,11 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
           mbar_wait(&empty_l[sl], pl ^ 1);
           mbar_arrive_expect_tx(&full_l[sl], PATCH_BYTES);
           tma_load_4d(smem_l + sl * PATCH_STRIDE, &map_src1, (next_patch - p.kb0) * BLOCK_K, sx0, sy0, n, &full_l[sl]);
-          if (++sl == PATCH_STAGES) { sl = 0; pl ^= 1; }
+          if (++sl == (uint32_t)cfg.sl) { sl = 0; pl ^= 1; }
           ++next_patch;
         };
         if (INTERP) {
-          for (int i = 0; i < PATCH_STAGES && next_patch < ncb; ++i) issue_patch();
+          for (int i = 0; i < cfg.sl && next_patch < ncb; ++i) issue_patch();
         }
         for (int cb = 0; cb < ncb; ++cb) {
           const CUtensorMap* src = cb < p.kb0 ? &map_src0 : &map_src1;
@@ -647,7 +650,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
             mbar_arrive(&full_a[sa]);
             mbar_arrive(&empty_l[sl]);
           }
-          if (++sl == PATCH_STAGES) { sl = 0; pl ^= 1; }
+          if (++sl == (uint32_t)cfg.sl) { sl = 0; pl ^= 1; }
         }
         if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
       }
@@ -1197,8 +1200,8 @@ int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUten
 inline int halo_tiles_for(int bn, int n_tiles, int ncb, bool interp) {
   static const int env = getenv("RDP_HALO_TILES") ? atoi(getenv("RDP_HALO_TILES")) : 0;
   if (env == 1) return 1;
-  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (interp ? PATCH_STAGES * patch_stride(1) : 0);
-  const bool resident = n_tiles == 1 && 9 * ncb * bn * BLOCK_K * 2 + (interp ? 2 : 3) * halo_stride(1) <= budget;
+  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - aux_bytes(bn * n_tiles, false) - (interp ? patch_stride(1) : 0);
+  const bool resident = n_tiles == 1 && 9 * ncb * bn * BLOCK_K * 2 + 3 * halo_stride(1) <= budget;
   return (!resident && bn == 128) ? 2 : 1;
 }
 
@@ -1207,19 +1210,27 @@ int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtenso
                      int num_sms, cudaStream_t stream) {
   const int ncb = p.kb0 + p.kb1, b_block = BN * BLOCK_K * 2;
   const int HALO_STRIDE = halo_stride(tiles);
-  const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - (p.low ? PATCH_STAGES * patch_stride(tiles) : 0);
+  // everything but the rings: alignment slack, barriers, epilogue constants, one source-patch stage when fused
+  const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(p.cout, p.head_w != nullptr) + (p.low ? patch_stride(tiles) : 0);
+  int budget = HALO_SMEM_TOTAL - fixed;
   static const int env_sa = getenv("RDP_HALO_SA") ? atoi(getenv("RDP_HALO_SA")) : 0;
   HaloCfg cfg{};
+  cfg.sl = 1;
   const int w_bytes = 9 * ncb * b_block;
-  if (tiles == 1 && p.n_tiles == 1 && w_bytes + (p.low ? 2 : 3) * HALO_STRIDE <= budget) {
+  if (tiles == 1 && p.n_tiles == 1 && w_bytes + 3 * HALO_STRIDE <= budget) {
     cfg.sb = 0;
     cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / HALO_STRIDE);
+    if (p.low && budget - w_bytes - cfg.sa * HALO_STRIDE >= patch_stride(tiles)) cfg.sl = 2;
     return p.low ? launch_conv_halo_t<BN, true, true, 1>(s0, s1, wm, p, cfg, num_sms, stream)
                  : launch_conv_halo_t<BN, true, false, 1>(s0, s1, wm, p, cfg, num_sms, stream);
   }
   // streamed weights: a halo block lasts 9 taps, so few A stages suffice; the weight ring must cover the
   // bandwidth-latency product of one 64-wide slice per tap
   cfg.sa = env_sa ? env_sa : ((BN == 256 || tiles == 2) ? 2 : 3);
+  if (p.low) {  // streamed layers have room for a second patch stage
+    cfg.sl = 2;
+    budget -= patch_stride(tiles);
+  }
   cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * HALO_STRIDE) / b_block);
   if constexpr (BN == 128) {
     if (tiles == 2)
@@ -1304,7 +1315,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   static const bool debug_nohead = getenv("RDP_DEBUG_NOHEAD") != nullptr;    // timing experiments only
   static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
   static const bool no_fuse_pool = getenv("RDP_NO_FUSE_POOL") != nullptr;  // development switch: separate pooling kernel
-  static const bool fuse_all_up = getenv("RDP_FUSE_ALL_UP") != nullptr;
+  static const bool fuse_up4 = getenv("RDP_FUSE_UP4") != nullptr;  // development switch: fuse up4's upsample as well
   static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
   static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
@@ -1445,8 +1456,9 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const int Cl = net->w.conv[low_i].cout, Cs = net->w.conv[skip_i].cout;
     const int dy = Ls.H - 2 * Ll.H, dx = Ls.W - 2 * Ll.W;
     const int C8 = Cl / 8;
-    // up4.0 (64 output channels) has too little MMA time per block to hide the interpolation: it keeps the copy
-    const bool fuse_up = !force_v1 && !no_fuse_up && sel[10 + 2 * j] == 'h' && (net->bn[10 + 2 * j] >= 128 || fuse_all_up);
+    // up4.0 (64 output channels): interpolation warps slow the MMA issue warp down as much as the copy costs - measured
+    // equal, so it keeps the simpler stand-alone upsample unless asked
+    const bool fuse_up = !force_v1 && !no_fuse_up && sel[10 + 2 * j] == 'h' && (net->bn[10 + 2 * j] >= 128 || fuse_up4);
     if (fuse_up) {
       // the convolution's interpolation warps read the low-resolution tensor directly: no upsampled copy in HBM
       mark();
