@@ -60,6 +60,15 @@ def geometry_bytes_per_frame(P: int, n_points: float) -> float:
     return 3.0 * P + 24.0 * n_points
 
 
+def load_traffic():
+    """DRAM bytes from the committed ncu --set full capture (profiles/), or None."""
+    path = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return json.load(fh)
+    return None
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -343,6 +352,7 @@ def run_b200(args):
     # k_deproject's own algorithmic bytes: 3P read, 4N pixel ids written (fp32 xyz only when the caller asks for it)
     dp_bytes = B * (3.0 * P + 4.0 * n_points)
     step_ms_prof = float(unet_ms.sum() + geom_ms.sum())
+    ncu = load_traffic() if (B, H, W) == (64, 480, 640) else None   # the capture was taken on this workload
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -363,14 +373,17 @@ def run_b200(args):
                        "curvature_batch -> D2H of mean/max/status/points, three streams, two slots"},
         "gpu_launches": int((eng.launches_per_forward + len(geometry.LAUNCH_NAMES) - 1) * args.steps),
         "roofline": {"bound": "tensor", "kernel": "k_conv3x3 (18 launches per step)", "achieved": conv_tflops,
-                     "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": conv_tflops / peaks["tflops"], "traffic": None,
+                     "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": conv_tflops / peaks["tflops"],
+                     "traffic": (ncu["conv_dram_bytes_per_step"] / ncu["conv_launches"]) if ncu else None,
+                     "traffic_note": (f"mean DRAM bytes per conv launch, {ncu['source']}" if ncu else None),
                      "peak_source": peaks["source"] + ", of measured",
                      "flops_per_frame": sum(flops), "conv_ms_per_step": conv_ms, "share_of_step": conv_ms / step_ms_prof,
                      "per_layer_tflops": per_layer,
                      "how": f"CUDA events between launches on the launching stream, mean of {prof_steps} steps"},
         "roofline_hbm": {"bound": "hbm", "kernel": "k_deproject", "achieved": dp_bytes / (dp_ms * 1e-3) / 1e9,
                          "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": dp_bytes / (dp_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                         "traffic": None, "ms": dp_ms, "geometry_ms_per_step": float(geom_ms.sum()),
+                         "traffic": ncu["deproject_dram_bytes_per_launch"] if ncu else None, "algorithmic_bytes": dp_bytes,
+                         "ms": dp_ms, "geometry_ms_per_step": float(geom_ms.sum()),
                          "geometry_launch_ms": {n: round(float(v), 4) for n, v in zip(geometry.LAUNCH_NAMES, geom_ms)},
                          "survey_bytes_per_frame": geometry_bytes_per_frame(P, n_points)},
         "launch_ms": {n: round(float(v), 4) for n, v in zip(names, unet_ms)},
