@@ -122,10 +122,23 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
   for (int c = 0; c < 8; ++c) head[c] = 0.f;
   uint32_t r[2][32];
   tmem_ld_32x32(taddr, r[0]);
+  if (BN == 64) {
+    // 64 columns fit the registers: read the whole accumulator and hand the TMEM stage back before any arithmetic.
+    // What matters to the MMA warp is how long a stage is held, and the 64-wide tiles are short.
+    tmem_ld_32x32(taddr + 32, r[1]);
+    tmem_ld_wait();
+    if (acc_empty_bar != nullptr) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(acc_empty_bar);
+    }
+  }
 #pragma unroll
   for (int c = 0; c < BN / 32; ++c) {
-    tmem_ld_wait();
-    if (c + 1 < BN / 32) tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+    if (BN != 64) {
+      tmem_ld_wait();
+      if (c + 1 < BN / 32) tmem_ld_32x32(taddr + (c + 1) * 32, r[(c + 1) & 1]);
+    }
     const uint32_t sh_addr = smem_u32(s_aux + nt * BN + c * 32);
     float v[32];
 #pragma unroll
@@ -139,21 +152,21 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     if (BN == 64 && head_on) {
 #pragma unroll
       for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+      // One rolled loop over the classes (the reference uses a single class): unrolling it eight times made the
+      // kernel outgrow the instruction cache and cost more than the arithmetic itself.
+#pragma unroll 1
+      for (int cls = 0; cls < p.n_classes; ++cls) {
+        const uint32_t hw_addr = smem_u32(s_aux + p.cout + cls * 64 + c * 32);
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four chains instead of one 64-long dependency
 #pragma unroll
-      for (int cls = 0; cls < 8; ++cls) {
-        if (cls < p.n_classes) {
-          const uint32_t hw_addr = smem_u32(s_aux + p.cout + cls * 64 + c * 32);
-          float a0 = head[cls], a1 = 0.f, a2 = 0.f, a3 = 0.f;  // four chains instead of one 64-long dependency
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 w = lds_f4(hw_addr + 16 * q);
-            a0 = fmaf(v[4 * q + 0], w.x, a0);
-            a1 = fmaf(v[4 * q + 1], w.y, a1);
-            a2 = fmaf(v[4 * q + 2], w.z, a2);
-            a3 = fmaf(v[4 * q + 3], w.w, a3);
-          }
-          head[cls] = (a0 + a1) + (a2 + a3);
+        for (int q = 0; q < 8; ++q) {
+          const float4 w = lds_f4(hw_addr + 16 * q);
+          a0 = fmaf(v[4 * q + 0], w.x, a0);
+          a1 = fmaf(v[4 * q + 1], w.y, a1);
+          a2 = fmaf(v[4 * q + 2], w.z, a2);
+          a3 = fmaf(v[4 * q + 3], w.w, a3);
         }
+        head[cls] += (a0 + a1) + (a2 + a3);
       }
     }
     if (p.out != nullptr) {
@@ -193,21 +206,19 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     }
   }
   // accumulator stage drained: hand it back to the MMA warp
-  if (acc_empty_bar != nullptr) {
+  if (BN != 64 && acc_empty_bar != nullptr) {
     tc_fence_before();
     __syncwarp();
     if (lane == 0) mbar_arrive(acc_empty_bar);
   }
   if (BN == 64 && head_on && inside) {
     const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
-#pragma unroll
-    for (int cls = 0; cls < 8; ++cls) {
-      if (cls < p.n_classes) {
-        const float logit = head[cls] + s_aux[p.cout + AUX_HEAD_FLOATS + cls];
-        const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
-        if (p.logits) p.logits[o] = logit;
-        if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
-      }
+#pragma unroll 1
+    for (int cls = 0; cls < p.n_classes; ++cls) {
+      const float logit = head[cls] + s_aux[p.cout + AUX_HEAD_FLOATS + cls];
+      const size_t o = ((size_t)n * p.n_classes + cls) * hw_px + off;
+      if (p.logits) p.logits[o] = logit;
+      if (p.mask) p.mask[o] = mask_rule(logit) ? 1 : 0;
     }
   }
 }
