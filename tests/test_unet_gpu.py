@@ -121,3 +121,27 @@ def test_hd_frame_720p():
     agree, hard_misses, listed = _agreement(mask.cpu().numpy(), ref)
     print(f"1280x720: agreement {agree:.6f}, hard misses {hard_misses}, borderline listed {len(listed)}")
     assert agree >= 0.999 and hard_misses == 0
+
+
+@pytest.mark.parametrize("n_channels,n_classes", [(1, 2), (4, 1), (5, 3)])
+def test_other_channel_and_class_counts(n_channels, n_classes):
+    """`UNet(n_channels, n_classes)` is general in the reference; 1/3/4 input channels use the fused first-layer
+    kernel, other counts the im2col fallback; several classes go through the rolled head loop."""
+    from pkg.segmentation_model import UNet
+    sd = synth.make_state_dict(4, n_channels=n_channels, n_classes=n_classes)
+    g = torch.Generator().manual_seed(99)
+    x = torch.rand(2, n_channels, 48, 64, generator=g)
+    model = UNet(n_channels, n_classes)
+    model.load_state_dict(sd)
+    model = model.cuda().eval()
+    out = model(x.cuda())
+    ref = unet_port.unet_forward(sd, x)
+    assert out.shape == ref.shape == (2, n_classes, 48, 64)
+    rel = float((out.cpu() - ref).abs().max() / ref.abs().max())
+    assert rel < 3e-2, rel
+    if n_channels == 4:   # uint8 fast path with 4 channels as well
+        u8 = (x * 255).round().to(torch.uint8).permute(0, 2, 3, 1).contiguous().cuda()
+        mask, logits, _ = model.forward_mask(u8, want_logits=True)
+        ref8 = unet_port.unet_forward(sd, u8.cpu().permute(0, 3, 1, 2).float() / 255.0)
+        assert float((logits.cpu() - ref8).abs().max() / ref8.abs().max()) < 3e-2
+        assert mask.shape == (2, 1, 48, 64)
