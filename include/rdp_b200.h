@@ -169,6 +169,28 @@ int rdp_geom_deproject_static(const uint8_t* mask, const void* depth, int depth_
                               const double* intrinsics, double depth_scale, float* points_xyz, uint32_t* pixel_ids,
                               int32_t* n_points, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------ */
+/* Server-side pre/post-processing around the hot path (services/vision_analysis/server.py)                 */
+/* ------------------------------------------------------------------------------------------------------ */
+
+/* Replaces `self.preprocess(image_rgb).unsqueeze(0)` (server.py:107-110,121): torchvision ToTensor (uint8/255,
+ * HWC -> CHW) followed by Resize((out_h,out_w), antialias=True) - ATen's separable antialiased bilinear filter,
+ * horizontal pass first, weights normalised per output index - in one pass, fp32.
+ *   rgb_nhwc [B][H][W][C] uint8 (device), C in 1..8      out_nchw [B][C][out_h][out_w] fp32 (device)
+ *   flags: 0 or RDP_PRE_SWAP_RB
+ * One launch, no workspace.  Agreement with torchvision: a few fp32 ulp (the tests hold it to 2e-6 absolute). */
+#define RDP_PRE_SWAP_RB 1 /* input is BGR (cv2.imdecode): also does cv2.cvtColor(.., COLOR_BGR2RGB), server.py:120 */
+int rdp_pre_resize(const uint8_t* rgb_nhwc, int B, int H, int W, int C, int out_h, int out_w, int flags,
+                   float* out_nchw, void* stream);
+
+/* Replaces `cv2.resize(mask_resized, (W, H), interpolation=cv2.INTER_NEAREST)` (server.py:125) and the count
+ * behind `mask_coverage_percent` (server.py:133): source index = min(floor(dst * (1 / (dst_size / src_size))),
+ * src_size - 1) in double, OpenCV's rule (not the half-pixel-centre one), exact.
+ *   mask [B][h][w] uint8 (device)     out [B][H][W] uint8 (device)
+ *   nonzero [B] int32 (device, optional): number of non-zero pixels of each up-sized mask; cleared by the call. */
+int rdp_post_mask_nearest(const uint8_t* mask, int B, int h, int w, int H, int W, uint8_t* out, int32_t* nonzero,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

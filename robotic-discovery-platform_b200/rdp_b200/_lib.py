@@ -20,6 +20,7 @@ EXPORTS = [
     "rdp_unet_read_activation", "rdp_unet_forward_profiled",
     "rdp_geom_workspace_bytes", "rdp_geom_curvature", "rdp_geom_launch_count", "rdp_geom_curvature_profiled",
     "rdp_geom_deproject_static",
+    "rdp_pre_resize", "rdp_post_mask_nearest",
 ]
 
 
@@ -79,6 +80,10 @@ def load() -> C.CDLL:
                                                   C.POINTER(C.c_double), C.c_double, C.c_void_p, C.c_void_p,
                                                   C.c_void_p, C.c_void_p]
         lib.rdp_geom_deproject_static.restype = C.c_int
+        lib.rdp_pre_resize.argtypes = [C.c_void_p] + [C.c_int] * 7 + [C.c_void_p, C.c_void_p]
+        lib.rdp_pre_resize.restype = C.c_int
+        lib.rdp_post_mask_nearest.argtypes = [C.c_void_p] + [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.rdp_post_mask_nearest.restype = C.c_int
         lib.rdp_unet_forward_profiled.argtypes = lib.rdp_unet_forward.argtypes + [C.POINTER(C.c_float)]
         lib.rdp_geom_curvature_profiled.argtypes = lib.rdp_geom_curvature.argtypes + [C.POINTER(C.c_float)]
         for name in ("rdp_unet_create", "rdp_unet_workspace_bytes", "rdp_unet_forward", "rdp_unet_launch_count",

@@ -1,0 +1,87 @@
+"""The body of the reference server's per-frame loop on the GPU (`services/vision_analysis/server.py:116-141`).
+
+    color (B,H,W,3) uint8 --rdp_pre_resize--> (B,3,S,S) f32 --UNet (mask rule fused)--> (B,S,S) u8
+          --rdp_post_mask_nearest--> (B,H,W) u8 + non-zero counts --rdp_geom_curvature(depth)--> curvature, coverage
+
+Decoding the PNG/JPEG payloads and the gRPC plumbing stay with the caller (out of scope); every
+array between them and the response fields stays in HBM.  No CPU fallback.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib, geometry
+
+MODEL_IMG_SIZE = 256  # server.py:58
+PRE_SWAP_RB = 1
+
+
+def _need_cuda_u8(t: torch.Tensor, what: str, ndim: int) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or t.device.type != "cuda":
+        raise _lib.RdpError(f"{what} must be a CUDA tensor; there is no CPU path")
+    if t.dtype != torch.uint8 or t.dim() != ndim:
+        raise _lib.RdpError(f"{what} must be uint8 with {ndim} dimensions (got {t.dtype} {tuple(t.shape)})")
+    return t.contiguous()
+
+
+def preprocess(color_u8: torch.Tensor, size: int | tuple = MODEL_IMG_SIZE, *, bgr: bool = False, out=None) -> torch.Tensor:
+    """(B,H,W,C) uint8 -> (B,C,size,size) float32: ToTensor + Resize(antialias=True) (`server.py:107-110,121`);
+    `bgr=True` also does the `cv2.cvtColor(BGR2RGB)` of `server.py:120`."""
+    x = _need_cuda_u8(color_u8, "color image batch", 4)
+    B, H, W, Cn = x.shape
+    oh, ow = (size, size) if isinstance(size, int) else size
+    if out is None:
+        out = torch.empty((B, Cn, oh, ow), dtype=torch.float32, device=x.device)
+    elif out.shape != (B, Cn, oh, ow) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != x.device:
+        raise _lib.RdpError("preprocess: `out` must be a contiguous float32 (B,C,oh,ow) tensor on the input's device")
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.load().rdp_pre_resize(x.data_ptr(), B, H, W, Cn, oh, ow, PRE_SWAP_RB if bgr else 0, out.data_ptr(),
+                                              torch.cuda.current_stream(x.device).cuda_stream), "rdp_pre_resize")
+    return out
+
+
+def upsize_mask(mask_small: torch.Tensor, H: int, W: int, *, want_count: bool = True):
+    """(B,h,w) uint8 -> ((B,H,W) uint8, non-zero count (B,) int32 or None): `cv2.resize(.., INTER_NEAREST)` and the
+    count behind `mask_coverage_percent` (`server.py:125,133`)."""
+    m = _need_cuda_u8(mask_small, "mask batch", 3)
+    B, h, w = m.shape
+    out = torch.empty((B, H, W), dtype=torch.uint8, device=m.device)
+    cnt = torch.empty(B, dtype=torch.int32, device=m.device) if want_count else None
+    with torch.cuda.device(m.device):
+        _lib.check(_lib.load().rdp_post_mask_nearest(m.data_ptr(), B, h, w, H, W, out.data_ptr(),
+                                                     cnt.data_ptr() if want_count else None,
+                                                     torch.cuda.current_stream(m.device).cuda_stream), "rdp_post_mask_nearest")
+    return out, cnt
+
+
+@dataclass
+class FrameAnalysis:
+    curvature: geometry.CurvatureBatch   # mean/max curvature, spline points, status per frame
+    final_mask: torch.Tensor             # (B,H,W) uint8, camera resolution
+    mask_coverage_percent: torch.Tensor  # (B,) float64
+    model_input: torch.Tensor            # (B,3,S,S) float32, what the U-Net saw
+    mask_small: torch.Tensor             # (B,S,S) uint8, the U-Net's own resolution
+
+
+@torch.no_grad()
+def analyze_frames(model, color_u8: torch.Tensor, depth: torch.Tensor, intrinsics, depth_scale, *,
+                   size: int = MODEL_IMG_SIZE, bgr: bool = False) -> FrameAnalysis:
+    """One pass of the server loop body over a batch of decoded frames (`server.py:120-141`).
+
+    `model` is the drop-in `pkg.segmentation_model.UNet` (eval mode, on the frames' device); `depth` is the decoded
+    depth image batch (B,H,W) uint16 | float32 at camera resolution."""
+    B, H, W, _ = color_u8.shape
+    x = preprocess(color_u8, size, bgr=bgr)
+    model._check(x)
+    _, mask, _ = model._engine_for(x.device).forward(x, want_logits=False, want_mask=True)   # sigmoid(logit) > 0.5
+    if mask.shape[1] != 1:
+        raise _lib.RdpError("the server's mask path is defined for n_classes == 1 (server.py:124-125)")
+    mask_small = mask[:, 0]
+    final_mask, cnt = upsize_mask(mask_small, H, W)
+    curv = geometry.curvature_batch(final_mask, depth, intrinsics, depth_scale)
+    # count / size * 100 in that order (server.py:133); tensor / tensor, because torch divides by a Python scalar
+    # through its reciprocal, which rounds differently
+    coverage = cnt.to(torch.float64) / torch.full_like(cnt, H * W, dtype=torch.float64) * 100.0
+    return FrameAnalysis(curv, final_mask, coverage, x, mask_small)

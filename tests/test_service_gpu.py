@@ -1,0 +1,112 @@
+"""CUDA pre/post-processing (rdp_pre_resize, rdp_post_mask_nearest) and the whole server loop body against the oracle
+restatement of `services/vision_analysis/server.py:107-141`, through the C ABI."""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import geometry_port as gp
+from oracle import service_port as sp
+from oracle import unet_port
+from oracle.make_golden_service import sample_positions, service_inputs
+from rdp_b200 import _lib, service, synth
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+RESIZE_ATOL = 2e-6     # fp32, values in [0,1]; the kernel sums the taps in a different order from ATen
+
+
+def _cases():
+    with open(os.path.join(GOLDEN, "service_manifest.json")) as fh:
+        return sorted(json.load(fh)["cases"].items())
+
+
+@pytest.mark.parametrize("name,meta", _cases())
+def test_resize_matches_torchvision_golden_and_oracle(name, meta, golden):
+    g = golden(name)
+    img, _ = service_inputs(meta["seed"], meta["H"], meta["W"], meta["size"])
+    x = service.preprocess(torch.from_numpy(img)[None].cuda(), meta["size"]).cpu().numpy()
+    assert np.abs(x.reshape(-1)[sample_positions(x.size)] - g["resize_val"]).max() <= RESIZE_ATOL
+    assert np.abs(x - sp.preprocess_np(img, meta["size"])).max() <= RESIZE_ATOL
+
+
+@pytest.mark.parametrize("name,meta", _cases())
+def test_nearest_upsize_and_coverage_are_exact(name, meta, golden):
+    g = golden(name)
+    _, m = service_inputs(meta["seed"], meta["H"], meta["W"], meta["size"])
+    up, cnt = service.upsize_mask(torch.from_numpy(m)[None].cuda(), meta["H"], meta["W"])
+    up = up.cpu().numpy()[0]
+    digest = np.frombuffer(hashlib.sha256(np.ascontiguousarray(up).tobytes()).digest(), np.uint8)
+    assert np.array_equal(digest, g["up_sha256"])
+    assert int(cnt[0]) == int(g["up_nonzero"])
+    assert np.array_equal(up, sp.upsize_mask_np(m, meta["H"], meta["W"]))
+
+
+def test_batched_bgr_other_sizes_and_repeat_calls():
+    rng = np.random.default_rng(8)
+    img = rng.integers(0, 256, (5, 120, 200, 3), dtype=np.uint8)
+    d = torch.from_numpy(img).cuda()
+    out = service.preprocess(d, (48, 80), bgr=True).cpu().numpy()
+    for i in range(5):
+        assert np.abs(out[i] - sp.preprocess_np(img[i][:, :, ::-1], (48, 80))[0]).max() <= RESIZE_ATOL
+    gray = service.preprocess(d[..., :1].contiguous(), 64).cpu().numpy()
+    assert np.abs(gray[2] - sp.preprocess_np(img[2][:, :, :1], 64)[0]).max() <= RESIZE_ATOL
+    m = (rng.random((5, 48, 80)) > 0.6).astype(np.uint8)
+    dm = torch.from_numpy(m).cuda()
+    for _ in range(2):                     # the counts are cleared by every call
+        up, cnt = service.upsize_mask(dm, 120, 200)
+        for i in range(5):
+            ref = sp.upsize_mask_np(m[i], 120, 200)
+            assert np.array_equal(up[i].cpu().numpy(), ref) and int(cnt[i]) == np.count_nonzero(ref)
+    down, cnt = service.upsize_mask(dm, 20, 33)      # INTER_NEAREST also shrinks
+    assert np.array_equal(down[1].cpu().numpy(), sp.upsize_mask_np(m[1], 20, 33))
+    empty, cnt = service.upsize_mask(torch.zeros((2, 16, 16), dtype=torch.uint8, device="cuda"), 40, 40)
+    assert int(cnt.sum()) == 0 and int(empty.sum()) == 0
+
+
+def test_bad_arguments_are_refused():
+    with pytest.raises(_lib.RdpError):
+        service.preprocess(torch.zeros((1, 8, 8, 3), dtype=torch.uint8), 4)                    # host tensor
+    with pytest.raises(_lib.RdpError):
+        service.preprocess(torch.zeros((1, 8, 8, 9), dtype=torch.uint8, device="cuda"), 4)     # 9 channels
+    with pytest.raises(_lib.RdpError):
+        service.preprocess(torch.zeros((1, 8, 8, 1), dtype=torch.uint8, device="cuda"), 4, bgr=True)
+    with pytest.raises(_lib.RdpError):
+        service.upsize_mask(torch.zeros((1, 8, 8), dtype=torch.float32, device="cuda"), 16, 16)
+
+
+def test_server_loop_body_matches_the_oracle_end_to_end():
+    """decode -> [resize -> U-Net -> threshold -> nearest up-size -> curvature, coverage] as server.py:120-141 does it."""
+    from pkg.segmentation_model import UNet
+    H, W, B = 480, 640, 3
+    sd = synth.make_state_dict(5, planted=True)
+    model = UNet(3, 1).eval()
+    model.load_state_dict(sd)
+    model = model.cuda()
+    frames = [synth.make_frame(200 + i, H, W, 0.30, "u16") for i in range(B)]
+    rgb = np.stack([f["rgb"] for f in frames])
+    depth = np.stack([f["depth"] for f in frames])
+    K, scale = frames[0]["K"], frames[0]["depth_scale"]
+    res = service.analyze_frames(model, torch.from_numpy(rgb).cuda(), torch.from_numpy(depth).cuda(), K, scale)
+    for i in range(B):
+        x = sp.preprocess_np(rgb[i])
+        assert np.abs(res.model_input[i].cpu().numpy() - x[0]).max() <= RESIZE_ATOL
+        # the U-Net leg has its own parity tests; here the oracle continues from the device's small mask so that a
+        # borderline logit (bf16 vs fp32) cannot hide a post-processing difference ...
+        small = res.mask_small[i].cpu().numpy()
+        final = sp.upsize_mask_np(small, H, W)
+        assert np.array_equal(res.final_mask[i].cpu().numpy(), final)
+        assert float(res.mask_coverage_percent[i]) == sp.coverage_percent(final)
+        o = gp.curvature_profile(final, depth[i], K, scale)
+        assert int(res.curvature.status[i]) == o.status
+        if o.status == _lib.FRAME_OK:
+            assert np.isclose(float(res.curvature.mean_curvature[i]), o.mean_curvature, rtol=1e-6)
+            assert np.isclose(float(res.curvature.max_curvature[i]), o.max_curvature, rtol=1e-6)
+        # ... and the oracle's own fp32 mask from the same input agrees with the device's except on borderline pixels
+        logits = unet_port.unet_forward(sd, torch.from_numpy(x)).numpy()[0, 0]
+        borderline = np.abs(logits) < 0.05
+        assert np.array_equal((logits > 0)[~borderline], small.astype(bool)[~borderline])
+        assert small.mean() > 0.02          # the planted weights segment something at 256x256
