@@ -19,6 +19,7 @@
 #include <stdarg.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "rdp_common.cuh"
 
@@ -798,11 +799,20 @@ __global__ void __launch_bounds__(FIT_THREADS) k_fit(const Params p) {
 constexpr int KN_THREADS = 256;
 constexpr int KN_MAXIT = 20;
 
+// FITPACK's bracket search multiplies and divides p by 0.04 and then compares with the bracket end it started from:
+// (p1 / 0.04) * 0.04 <= p1 holds in exact arithmetic and is decided by the last bit in floating point (true for about
+// 93 % of the values of p1), where p1 = nk1 / sum(diag R) carries the rounding of every rotation before it.  The order
+// of the rotations differs here, so that bit cannot be reproduced; the tie is resolved as exact arithmetic resolves
+// it, which is also FITPACK's own outcome in the large majority of cases.
+constexpr double KN_TIE_UP = 1.0 + 1e-12, KN_TIE_DOWN = 1.0 - 1e-12;
+constexpr int KN_CH = 16;  // data points per triangle task (an interval with more points is cut into several)
+
 struct KnotWs {
   double *t, *q, *term, *fpint, *tri, *R, *z, *c, *D;
-  int *lidx, *ibegin, *nrd, *nbeg;
+  int *lidx, *ibegin, *nrd, *nbeg, *tbeg, *tint, *tfirst;
   unsigned char* flag;
 };
+__host__ __device__ inline int knot_task_cap(int cap) { return cap + cap / KN_CH + 2; }
 
 __device__ __forceinline__ void givens(double piv, double& ww, double& cs, double& sn) {  // fpgivs
   const double store = fabs(piv);
@@ -860,6 +870,208 @@ __device__ __forceinline__ void band_rotate_in(double* R, double* z, int f, int 
   }
 }
 
+// The same plane rotation as fpgivs up to rounding, with one rsqrt on the dependency chain instead of two
+// divisions and a square root: dd = sqrt(ww^2 + piv^2), cs = ww/dd, sn = piv/dd.  piv == 0 is the identity
+// (FITPACK skips such pivots).  Magnitudes here (coordinates in metres, B-spline values, scaled penalty rows)
+// are far from the fp64 range limits, so the unscaled sum of squares is safe.
+// 1/sqrt(a) for a > 0 in the normal range without the library's special-case branch (a branch per rotation would
+// cut the merge into basic blocks and stop ptxas from interleaving independent rotations): hardware seed (about 22
+// bits) and two coupled Newton steps, g -> sqrt(a), h -> 1/(2 sqrt(a)); a few ulp.
+__device__ __forceinline__ double rsqrt_pos(double a) {
+  double y;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+  double g = a * y, h = 0.5 * y;
+  double r = fma(-g, h, 0.5);
+  g = fma(g, r, g);
+  h = fma(h, r, h);
+  r = fma(-g, h, 0.5);
+  h = fma(h, r, h);
+  return h + h;
+}
+__device__ __forceinline__ void givens_fast(double piv, double& ww, double& cs, double& sn) {
+  const double s2 = fma(piv, piv, ww * ww);
+  const double inv = rsqrt_pos(s2);
+  const bool nz = piv != 0.0;  // also covers s2 == 0 (inv = NaN, discarded)
+  cs = nz ? ww * inv : 1.0;
+  sn = nz ? piv * inv : 0.0;
+  ww = nz ? s2 * inv : ww;
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
+// Rotate a row of LEN entries h (right-hand side x) into rows S0.. of the register window of the band.
+template <int S0, int LEN>
+__device__ __forceinline__ void window_rotate_in(double (&Rw)[5][5], double (&zw)[5][3], double (&h)[5], double (&x)[3]) {
+#pragma unroll
+  for (int s = 0; s < LEN; ++s) {
+    double cs, sn;
+    givens_fast(h[s], Rw[S0 + s][0], cs, sn);
+#pragma unroll
+    for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], zw[S0 + s][d]);
+#pragma unroll
+    for (int e = s + 1; e < LEN; ++e) rota(cs, sn, h[e], Rw[S0 + s][e - s]);
+  }
+}
+
+// One thread merges the task triangles (in point order) and, when pinv > 0, the penalty rows into the banded
+// triangle R (5 entries per row) with right-hand side z, then back-substitutes into c.  Interval i's rows touch band
+// rows i..i+3 and penalty row i-1 touches i-1..i+3, so the five rows in flight live in registers and row i-1 is
+// final once interval i is done.  Inputs are prefetched into L1 a few intervals ahead: they were written by other
+// threads (or, for the back substitution, by this one: stores do not allocate in L1).
+// (No __restrict__/const-cache loads: every input was written earlier in this kernel.)
+template <bool PEN>
+__device__ __noinline__ void band_merge_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
+                                              double* R, double* z, double* c) {
+  double Rw[5][5], zw[5][3];
+#pragma unroll
+  for (int r = 0; r < 5; ++r) {
+#pragma unroll
+    for (int e = 0; e < 5; ++e) Rw[r][e] = 0.0;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) zw[r][d] = 0.0;
+  }
+  const int nk1 = nrint + 3;
+  // Rotates one task triangle (and, with WITH_PEN, the penalty row behind it) into the window as a wavefront.  Row q
+  // (q = 0: the triangle's last row, one entry ... q = 3: its first row, four entries; q = 4: the penalty row, five)
+  // starts at window row 4 - q, so its s-th rotation touches window row 4 - q + s: within one step s the rows touch
+  // different window rows, and a window row sees the rows in the order q = 0, 1, .. - the same result as rotating the
+  // rows in one after the other, but the (up to five) rotations of a step are independent.  Their Newton chains are
+  // written side by side, array-wise, so that the in-order issue stream interleaves them instead of stalling on one.
+  auto wave_in = [&](const double* o, const double* dr, double scale, auto with_pen) {
+    constexpr int NQ = decltype(with_pen)::value ? 5 : 4;
+    double v[22];
+#pragma unroll
+    for (int q = 0; q < 22; ++q) v[q] = o[q];
+    double h[5][5], x[5][3];
+    h[0][0] = v[9];
+    h[1][0] = v[7]; h[1][1] = v[8];
+    h[2][0] = v[4]; h[2][1] = v[5]; h[2][2] = v[6];
+    h[3][0] = v[0]; h[3][1] = v[1]; h[3][2] = v[2]; h[3][3] = v[3];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int d = 0; d < 3; ++d) x[q][d] = v[10 + 3 * (3 - q) + d];
+    if (NQ == 5) {
+#pragma unroll
+      for (int e = 0; e < 5; ++e) h[4][e] = dr[e] * scale;  // a zero row rotates as the identity
+      x[4][0] = x[4][1] = x[4][2] = 0.0;
+    }
+#pragma unroll
+    for (int st = 0; st < NQ; ++st) {
+      double s2[5], y[5], g[5], hh[5], r[5], cs[5], sn[5];
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) s2[q] = fma(h[q][st], h[q][st], Rw[4 - q + st][0] * Rw[4 - q + st][0]);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y[q]) : "d"(s2[q]));
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) {
+          g[q] = s2[q] * y[q];
+          hh[q] = 0.5 * y[q];
+        }
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) r[q] = fma(-g[q], hh[q], 0.5);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) {
+          g[q] = fma(g[q], r[q], g[q]);
+          hh[q] = fma(hh[q], r[q], hh[q]);
+        }
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) r[q] = fma(-g[q], hh[q], 0.5);
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) {
+          hh[q] = fma(hh[q], r[q], hh[q]);
+          const double inv = hh[q] + hh[q];
+          const bool nz = h[q][st] != 0.0;
+          double& ww = Rw[4 - q + st][0];
+          cs[q] = nz ? ww * inv : 1.0;
+          sn[q] = nz ? h[q][st] * inv : 0.0;
+          ww = nz ? s2[q] * inv : ww;
+        }
+#pragma unroll
+      for (int q = 0; q < NQ; ++q)
+        if (st <= q) {
+#pragma unroll
+          for (int e = st + 1; e <= q; ++e) rota(cs[q], sn[q], h[q][e], Rw[4 - q + st][e - st]);
+#pragma unroll
+          for (int d = 0; d < 3; ++d) rota(cs[q], sn[q], x[q][d], zw[4 - q + st][d]);
+        }
+    }
+  };
+  int t_next = tfirst[0], t_next2 = nrint > 1 ? tfirst[1] : 0;
+  for (int i = 0; i < nrint; ++i) {  // window row r = band row i - 1 + r
+    const double* o = tri + (size_t)t_next * 22;  // interval i's triangle (reduced onto its first task)
+    t_next = t_next2;
+    if (i + 2 < nrint) {
+      t_next2 = tfirst[i + 2];
+      const double* pf = tri + (size_t)t_next2 * 22;
+      prefetch_l1(pf);
+      prefetch_l1(pf + 16);
+    }
+    if (PEN) {
+      const double* dr = D + (size_t)max(i - 1, 0) * 5;
+      prefetch_l1(dr + 40);
+      wave_in(o, dr, i >= 1 ? pinv : 0.0, std::true_type{});
+    } else {
+      wave_in(o, nullptr, 0.0, std::false_type{});
+    }
+    if (i >= 1) {
+#pragma unroll
+      for (int e = 0; e < 5; ++e) R[(size_t)(i - 1) * 5 + e] = Rw[0][e];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) z[(size_t)(i - 1) * 3 + d] = zw[0][d];
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+#pragma unroll
+      for (int e = 0; e < 5; ++e) Rw[r][e] = Rw[r + 1][e];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) zw[r][d] = zw[r + 1][d];
+    }
+#pragma unroll
+    for (int e = 0; e < 5; ++e) Rw[4][e] = 0.0;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) zw[4][d] = 0.0;
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r) {  // rows nrint-1 .. nk1-1 are still in the window
+#pragma unroll
+    for (int e = 0; e < 5; ++e) R[(size_t)(nrint - 1 + r) * 5 + e] = Rw[r][e];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) z[(size_t)(nrint - 1 + r) * 3 + d] = zw[r][d];
+  }
+  // fpback: c_i = (z_i - sum_e R[i][e] c_{i+e}) / R[i][0]; the newest coefficient enters last (shortest chain).
+  // Entries of R past the last column were never touched and are zero.
+  double c1[3] = {0.0, 0.0, 0.0}, c2[3] = {0.0, 0.0, 0.0}, c3[3] = {0.0, 0.0, 0.0}, c4[3] = {0.0, 0.0, 0.0};
+  for (int i = nk1 - 1; i >= 0; --i) {
+    if (i >= 24) {
+      prefetch_l1(R + (size_t)(i - 24) * 5);
+      prefetch_l1(z + (size_t)(i - 24) * 3);
+    }
+    const double r0 = R[(size_t)i * 5], r1 = R[(size_t)i * 5 + 1], r2 = R[(size_t)i * 5 + 2], r3 = R[(size_t)i * 5 + 3],
+                 r4 = R[(size_t)i * 5 + 4];
+    const double inv = 1.0 / r0;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      double a = z[(size_t)i * 3 + d];
+      a = fma(-c4[d], r4, a);
+      a = fma(-c3[d], r3, a);
+      a = fma(-c2[d], r2, a);
+      a = fma(-c1[d], r1, a) * inv;
+      c4[d] = c3[d];
+      c3[d] = c2[d];
+      c2[d] = c1[d];
+      c1[d] = a;
+      c[(size_t)i * 3 + d] = a;
+    }
+  }
+}
+
 __device__ __forceinline__ double block_sum1(double v, double* s_red) {
   v = warp_sum(v);
   __syncthreads();
@@ -870,9 +1082,9 @@ __device__ __forceinline__ double block_sum1(double v, double* s_red) {
   return a;
 }
 
-__global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const KnotWs base, int cap) {
+__global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const KnotWs base, int cap, int debug) {
   __shared__ double s_red[KN_THREADS / 32];
-  __shared__ int s_scan[KN_THREADS / 32];
+  __shared__ int s_scan[KN_THREADS / 32], s_scan2[KN_THREADS / 32];
   __shared__ int s_i[8];
   __shared__ unsigned long long s_best[KN_THREADS / 32];
   __shared__ int s_besti[KN_THREADS / 32];
@@ -886,7 +1098,11 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   w.q = base.q + (size_t)b * p.ecap * 4;
   w.term = base.term + (size_t)b * p.ecap;
   w.fpint = base.fpint + (size_t)b * cap;
-  w.tri = base.tri + (size_t)b * cap * 22;
+  const int tcap = knot_task_cap(cap);
+  w.tri = base.tri + (size_t)b * tcap * 22;
+  w.tbeg = base.tbeg + (size_t)b * tcap;
+  w.tint = base.tint + (size_t)b * tcap;
+  w.tfirst = base.tfirst + (size_t)b * cap;
   w.R = base.R + (size_t)b * cap * 5;
   w.z = base.z + (size_t)b * cap * 3;
   w.c = base.c + (size_t)b * cap * 3;
@@ -909,25 +1125,34 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
   }
 
-  int n = 8, nrint = 1, nk1 = 4, nplus = 0, ier = 0;
+  int n = 8, nrint = 1, nk1 = 4, nplus = 0, ier = 0, ntasks = 0, max_tasks = 1;
+  long long tm_tri = 0, tm_merge = 0, tm_res = 0, tm_setup = 0, tm_knot = 0, tm_mark = 0;  // RDP_DEBUG_KNOTS
+  int n_solve = 0, n_iter = 0;
+  auto lap = [&](long long& acc) {
+    if (debug) {
+      const long long now = clock64();
+      acc += now - tm_mark;
+      tm_mark = now;
+    }
+  };
   double fp = 0.0, fp0 = 0.0, fpold = 0.0, fpms = 0.0;
   bool smoothing = false, finished = false;
 
   // ---- one least-squares (pinv = 0) or smoothing (pinv > 0) solve on the current knots: fills w.c, returns fp ----
   auto solve = [&](double pinv) -> double {
-    // (1) interval triangles, one thread per interval
-    for (int i = tid; i < nrint; i += KN_THREADS) {
+    lap(tm_setup);
+    ++n_solve;
+    // (1) task triangles, one thread per task (at most KN_CH consecutive points of one interval)
+    for (int k = tid; k < ntasks; k += KN_THREADS) {
       double T[4][4] = {}, Z[4][3] = {};
-      const int p0 = w.ibegin[i], p1 = i + 1 < nrint ? w.ibegin[i + 1] : m;
+      const int p0 = w.tbeg[k], p1 = k + 1 < ntasks ? w.tbeg[k + 1] : m;
       for (int it = p0; it < p1; ++it) {
         double h[4] = {w.q[4 * it], w.q[4 * it + 1], w.q[4 * it + 2], w.q[4 * it + 3]};
         double x[3] = {X[3 * it], X[3 * it + 1], X[3 * it + 2]};
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-          const double piv = h[r];
-          if (piv == 0.0) continue;
           double cs, sn;
-          givens(piv, T[r][r], cs, sn);
+          givens_fast(h[r], T[r][r], cs, sn);
 #pragma unroll
           for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], Z[r][d]);
 #pragma unroll
@@ -935,7 +1160,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
             if (e > r) rota(cs, sn, h[e], T[r][e]);
         }
       }
-      double* o = w.tri + (size_t)i * 22;
+      double* o = w.tri + (size_t)k * 22;
       int q = 0;
 #pragma unroll
       for (int r = 0; r < 4; ++r)
@@ -947,42 +1172,67 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
 #pragma unroll
         for (int d = 0; d < 3; ++d) o[q++] = Z[r][d];
     }
-    for (int i = tid; i < nk1 * 5; i += KN_THREADS) w.R[i] = 0.0;
-    for (int i = tid; i < nk1 * 3; i += KN_THREADS) w.z[i] = 0.0;
     __syncthreads();
+    // (1b) the triangles of one interval share their four columns: pairwise tree reduction down to one per interval
+    for (int r = 1; r < max_tasks; r <<= 1) {
+      for (int k = tid; k < ntasks; k += KN_THREADS) {
+        const int i = w.tint[k], j = k - w.tfirst[i];
+        if ((j & (2 * r - 1)) != 0 || k + r >= w.tfirst[i + 1]) continue;
+        double* a = w.tri + (size_t)k * 22;
+        const double* o = w.tri + (size_t)(k + r) * 22;
+        double T[4][4], Z[4][3];
+        {
+          int q = 0;
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) T[rr][e] = e >= rr ? a[q++] : 0.0;
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+            for (int d = 0; d < 3; ++d) Z[rr][d] = a[q++];
+        }
+        int q = 0;
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr) {  // row rr of the other triangle: columns rr..3
+          double h[4], x[3];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) h[e] = e >= rr ? o[q++] : 0.0;
+#pragma unroll
+          for (int d = 0; d < 3; ++d) x[d] = o[10 + rr * 3 + d];
+#pragma unroll
+          for (int pc = 0; pc < 4; ++pc) {
+            if (pc < rr) continue;
+            double cs, sn;
+            givens_fast(h[pc], T[pc][pc], cs, sn);
+#pragma unroll
+            for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], Z[pc][d]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (e > pc) rota(cs, sn, h[e], T[pc][e]);
+          }
+        }
+        q = 0;
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (e >= rr) a[q++] = T[rr][e];
+#pragma unroll
+        for (int rr = 0; rr < 4; ++rr)
+#pragma unroll
+          for (int d = 0; d < 3; ++d) a[q++] = Z[rr][d];
+      }
+      __syncthreads();
+    }
+    lap(tm_tri);
     // (2) merge into the band, penalty rows interleaved by last column; back substitution
     if (tid == 0) {
-      for (int i = 0; i < nrint; ++i) {
-        const double* o = w.tri + (size_t)i * 22;
-        int q = 0;
-        for (int r = 0; r < 4; ++r) {
-          double h[4], x[3];
-          for (int e = r; e < 4; ++e) h[e - r] = o[q++];
-          for (int d = 0; d < 3; ++d) x[d] = o[10 + r * 3 + d];
-          band_rotate_in(w.R, w.z, i + r, 4 - r, h, x);
-        }
-        if (pinv > 0.0 && i >= 1) {
-          double h[5], x[3] = {0.0, 0.0, 0.0};
-          for (int e = 0; e < 5; ++e) h[e] = w.D[(size_t)(i - 1) * 5 + e] * pinv;
-          band_rotate_in(w.R, w.z, i - 1, 5, h, x);
-        }
-      }
-      for (int i = nk1 - 1; i >= 0; --i) {  // fpback
-        double a0 = w.z[i * 3], a1 = w.z[i * 3 + 1], a2 = w.z[i * 3 + 2];
-        const int lim = min(4, nk1 - 1 - i);
-        for (int e = 1; e <= lim; ++e) {
-          const double r = w.R[i * 5 + e];
-          a0 -= w.c[(i + e) * 3] * r;
-          a1 -= w.c[(i + e) * 3 + 1] * r;
-          a2 -= w.c[(i + e) * 3 + 2] * r;
-        }
-        const double dg = w.R[i * 5];
-        w.c[i * 3] = a0 / dg;
-        w.c[i * 3 + 1] = a1 / dg;
-        w.c[i * 3 + 2] = a2 / dg;
-      }
+      if (pinv > 0.0) band_merge_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, w.R, w.z, w.c);
+      else band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
     }
     __syncthreads();
+    lap(tm_merge);
     // (3) residuals
     double part = 0.0;
     for (int it = tid; it < m; it += KN_THREADS) {
@@ -999,38 +1249,73 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       w.term[it] = tt;
       part += tt;
     }
-    return block_sum1(part, s_red);
+    const double total = block_sum1(part, s_red);
+    lap(tm_res);
+    return total;
   };
 
+  if (debug) tm_mark = clock64();
   for (int iter = 0; iter < m && !finished && !smoothing; ++iter) {
     // ---- knot vector, interval of every point and interval starts from the flags (block scan over the points) ----
-    int carry = 0;
+    int carry = 0, carry2 = 0;
     for (int i0 = 0; i0 < m; i0 += KN_THREADS) {
       const int i = i0 + tid;
       const int f = (i < m) ? w.flag[i] : 0;
-      int incl = f;
+      const int cut = (i < m) && (f || (i % KN_CH) == 0);  // a triangle task starts here
+      int incl = f, incl2 = cut;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
+        const int v = __shfl_up_sync(0xffffffffu, incl, o), v2 = __shfl_up_sync(0xffffffffu, incl2, o);
+        if (lane >= o) {
+          incl += v;
+          incl2 += v2;
+        }
       }
-      if (lane == 31) s_scan[warp] = incl;
+      if (lane == 31) {
+        s_scan[warp] = incl;
+        s_scan2[warp] = incl2;
+      }
       __syncthreads();
-      int woff = 0;
-      for (int k = 0; k < warp; ++k) woff += s_scan[k];
-      int tot = 0;
-      for (int k = 0; k < KN_THREADS / 32; ++k) tot += s_scan[k];
-      const int cnt = carry + woff + incl;  // knots at or before this point
+      int woff = 0, woff2 = 0;
+      for (int k = 0; k < warp; ++k) {
+        woff += s_scan[k];
+        woff2 += s_scan2[k];
+      }
+      int tot = 0, tot2 = 0;
+      for (int k = 0; k < KN_THREADS / 32; ++k) {
+        tot += s_scan[k];
+        tot2 += s_scan2[k];
+      }
+      const int cnt = carry + woff + incl;  // knots at or before this point = its interval
       if (i < m) {
         w.lidx[i] = 3 + cnt;
         if (f) {
           w.ibegin[cnt] = i;
           w.t[3 + cnt] = U[i];
         }
+        if (cut) {
+          const int k = carry2 + woff2 + incl2 - 1;
+          w.tbeg[k] = i;
+          w.tint[k] = cnt;
+          if (f || i == 0) w.tfirst[cnt] = k;  // the first task of interval cnt
+        }
       }
       carry += tot;
+      carry2 += tot2;
       __syncthreads();
     }
+    ntasks = carry2;
+    if (tid == 0) {
+      w.tfirst[carry + 1] = ntasks;  // sentinel behind the last interval
+      s_i[1] = 1;
+    }
+    __syncthreads();
+    for (int i = tid; i < carry + 1; i += KN_THREADS) {  // most tasks any interval has (block-uniform loop bound below)
+      const int c = w.tfirst[i + 1] - w.tfirst[i];
+      if (c > 1) atomicMax(&s_i[1], c);
+    }
+    __syncthreads();
+    max_tasks = s_i[1];
     n = 8 + carry;
     nrint = n - 7;
     nk1 = n - 4;
@@ -1057,6 +1342,11 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
 
     fp = solve(0.0);
+    if (debug > 1 && tid == 0) {
+      double sd = 0.0;
+      for (int i = 0; i < nk1; ++i) sd += w.R[i * 5];
+      printf("  frame %d lsq n %d fp %.17g sumdiag %.17g\n", b, n, fp, sd);
+    }
     if (n == 8) {
       ier = -2;
       fp0 = fp;
@@ -1079,6 +1369,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       ier = 0;
     }
     fpold = fp;
+    ++n_iter;
     // ---- residual per interval; the point sitting on a knot is shared half/half by its two intervals ----
     for (int i = tid; i < nrint; i += KN_THREADS) {
       const int p0 = w.ibegin[i], p1 = i + 1 < nrint ? w.ibegin[i + 1] : m;
@@ -1161,6 +1452,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       if (stop == 3) break;
     }
     __syncthreads();
+    lap(tm_knot);
   }
 
   if (smoothing) {
@@ -1193,6 +1485,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     for (int it = 1; it <= KN_MAXIT; ++it) {
       fp = solve(1.0 / pp);
       fpms = fp - s;
+      if (debug > 1 && tid == 0) printf("  frame %d smoothing it %d p %.17g fp %.17g (p1 %.17g p3 %.17g)\n", b, it, pp, fp, p1, p3);
       if (fabs(fpms) < acc) break;
       if (it == KN_MAXIT) { ier = 3; break; }
       const double p2 = pp, f2 = fpms;
@@ -1200,7 +1493,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
         if ((f2 - f3) <= acc) {
           p3 = p2; f3 = f2;
           pp = pp * 0.04;
-          if (pp <= p1) pp = p1 * 0.9 + p2 * 0.1;
+          if (pp <= p1 * KN_TIE_UP) pp = p1 * 0.9 + p2 * 0.1;
           continue;
         }
         if (f2 < 0.0) ich3 = true;
@@ -1210,7 +1503,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
           p1 = p2; f1 = f2;
           pp = pp / 0.04;
           if (p3 < 0.0) continue;
-          if (pp >= p3) pp = p2 * 0.1 + p3 * 0.9;
+          if (pp >= p3 * KN_TIE_DOWN) pp = p2 * 0.1 + p3 * 0.9;
           continue;
         }
         if (f2 > 0.0) ich1 = true;
@@ -1283,6 +1576,9 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     p.out.mean_curvature[b] = kcnt > 0.0 ? ksum / kcnt : 0.0;
     p.out.max_curvature[b] = kcnt > 0.0 ? key_to_double(kmax_key) : 0.0;
     p.out.status[b] = RDP_FRAME_OK;
+    if (debug && (debug > 1 || b == 0))
+      printf("k_fit_knots frame %d: m %d knots %d solves %d knot-iterations %d | kcycles setup %lld triangles %lld merge %lld residual %lld fpknot %lld\n",
+             b, m, n, n_solve, n_iter, tm_setup / 1000, tm_tri / 1000, tm_merge / 1000, tm_res / 1000, tm_knot / 1000);
     if (p.out.n_knots) p.out.n_knots[b] = n;
     if (p.out.fit_residual) p.out.fit_residual[b] = fp;
     if (p.out.fit_ier) p.out.fit_ier[b] = ier;
@@ -1301,7 +1597,8 @@ static void carve_knots(Carver& c, KnotWs& k, int B, int ecap) {
   k.q = c.take<double>(B * e * 4);
   k.term = c.take<double>(B * e);
   k.fpint = c.take<double>(B * cap);
-  k.tri = c.take<double>(B * cap * 22);
+  const size_t tcap = (size_t)knot_task_cap((int)cap);
+  k.tri = c.take<double>(B * tcap * 22);
   k.R = c.take<double>(B * cap * 5);
   k.z = c.take<double>(B * cap * 3);
   k.c = c.take<double>(B * cap * 3);
@@ -1310,6 +1607,9 @@ static void carve_knots(Carver& c, KnotWs& k, int B, int ecap) {
   k.ibegin = c.take<int>(B * cap);
   k.nrd = c.take<int>(B * cap);
   k.nbeg = c.take<int>(B * cap);
+  k.tbeg = c.take<int>(B * tcap);
+  k.tint = c.take<int>(B * tcap);
+  k.tfirst = c.take<int>(B * cap);
   k.flag = c.take<unsigned char>(B * e);
 }
 
@@ -1407,7 +1707,8 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
   mark();
-  k_fit_knots<<<B, KN_THREADS, 0, stream>>>(p, kn, pl.ecap + 8);  // exits at once for frames that need no extra knots
+  static const int knots_debug = getenv("RDP_DEBUG_KNOTS") ? atoi(getenv("RDP_DEBUG_KNOTS")) : 0;  // phase cycle counts
+  k_fit_knots<<<B, KN_THREADS, 0, stream>>>(p, kn, pl.ecap + 8, knots_debug);  // exits at once for frames that need no extra knots
   mark();
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
