@@ -1,0 +1,153 @@
+"""Request batching shim for the unchanged gRPC servicer.
+
+The reference server handles one frame per loop iteration on each of its 10 worker threads
+(`services/vision_analysis/server.py:113-152`, `ThreadPoolExecutor(max_workers=10)` at `:172`).  `MicroBatcher`
+sits behind those threads: every thread hands over its decoded frame and blocks; one dispatcher thread coalesces
+what has arrived (up to `max_batch` frames, waiting at most `max_wait_ms` after the first) into one GPU micro-batch,
+runs the loop body once (`rdp_b200.service.analyze_frames`) and hands each caller its own frame's results.  The wire
+format (`protos/vision.proto:21-35`) and the servicer's response-building code stay as they are.
+"""
+from __future__ import annotations
+
+import queue
+import threading
+import time
+from concurrent.futures import Future
+from dataclasses import dataclass
+from typing import Callable, List, Optional
+
+import numpy as np
+
+
+@dataclass
+class FrameResult:
+    """What one iteration of the server loop needs to fill its response (`server.py:127-143`)."""
+    curvature_results: object            # pkg.geometry_utils.CurvatureResult, as compute_curvature_profile returns it
+    final_mask: np.ndarray               # (H,W) uint8 {0,1}
+    mask_coverage: float                 # percent, server.py:133
+    batch_size: int = 1                  # how many frames shared the GPU pass (diagnostics)
+
+
+@dataclass
+class _Request:
+    color: np.ndarray
+    depth: np.ndarray
+    future: Future
+    key: tuple
+
+
+def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device) -> Callable:
+    """The default `run_batch`: stacked host frames -> list of FrameResult through the CUDA loop body."""
+    import torch
+
+    from pkg.geometry_utils import _to_result
+
+    from . import service
+
+    dev = torch.device(device)
+    staging = {}
+
+    def run(colors: List[np.ndarray], depths: List[np.ndarray]) -> List[FrameResult]:
+        B = len(colors)
+        key = (B, colors[0].shape, depths[0].shape, depths[0].dtype)
+        if key not in staging:  # pinned staging buffers per batch shape (bounded: B <= max_batch, few camera formats)
+            staging[key] = (torch.empty((B,) + colors[0].shape, dtype=torch.uint8).pin_memory(),
+                            torch.empty((B,) + depths[0].shape, dtype=torch.from_numpy(depths[0][:0]).dtype).pin_memory())
+        hc, hd = staging[key]
+        for i in range(B):
+            hc[i].numpy()[...] = colors[i]
+            hd[i].numpy()[...] = depths[i]
+        with torch.cuda.device(dev):
+            r = service.analyze_frames(model, hc.to(dev, non_blocking=True), hd.to(dev, non_blocking=True), intrinsics,
+                                       depth_scale, size=size, bgr=bgr)
+            status = r.curvature.status.cpu().numpy()
+            mean, mx = r.curvature.mean_curvature.cpu().numpy(), r.curvature.max_curvature.cpu().numpy()
+            pts = r.curvature.spline_points.cpu().numpy()
+            masks, cov = r.final_mask.cpu().numpy(), r.mask_coverage_percent.cpu().numpy()
+        return [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B) for i in range(B)]
+
+    return run
+
+
+class MicroBatcher:
+    """Thread-safe: any number of request threads call `analyze` (blocking) or `submit` (returns a Future)."""
+
+    def __init__(self, model=None, intrinsics=None, depth_scale=None, *, max_batch: int = 64, max_wait_ms: float = 2.0,
+                 bgr: bool = True, size: int = 256, device="cuda", run_batch: Optional[Callable] = None):
+        if max_batch < 1:
+            raise ValueError("max_batch must be >= 1")
+        self.max_batch, self.max_wait = int(max_batch), float(max_wait_ms) / 1e3
+        self._run = run_batch if run_batch is not None else _gpu_runner(model, intrinsics, depth_scale, bgr, size, device)
+        self._q: "queue.Queue[Optional[_Request]]" = queue.Queue()
+        self._closed = False
+        self.batches_run, self.frames_run = 0, 0
+        self._thread = threading.Thread(target=self._loop, name="rdp-microbatcher", daemon=True)
+        self._thread.start()
+
+    # ---- request side ------------------------------------------------------------------------------------
+    def submit(self, color_image: np.ndarray, depth_image: np.ndarray) -> Future:
+        if self._closed:
+            raise RuntimeError("MicroBatcher is closed")
+        color, depth = np.asarray(color_image), np.asarray(depth_image)
+        if color.ndim != 3 or color.dtype != np.uint8 or depth.shape != color.shape[:2]:
+            raise ValueError(f"expected (H,W,C) uint8 colour and (H,W) depth, got {color.shape} {color.dtype} / {depth.shape}")
+        fut: Future = Future()
+        # frames of different camera formats cannot share a batch
+        self._q.put(_Request(color, depth, fut, (color.shape, depth.dtype.str)))
+        return fut
+
+    def analyze(self, color_image: np.ndarray, depth_image: np.ndarray, timeout: Optional[float] = None) -> FrameResult:
+        return self.submit(color_image, depth_image).result(timeout)
+
+    def close(self) -> None:
+        if not self._closed:
+            self._closed = True
+            self._q.put(None)
+            self._thread.join()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # ---- dispatcher --------------------------------------------------------------------------------------
+    def _loop(self) -> None:
+        held: List[_Request] = []          # arrived, but for a different camera format than the batch being built
+        stop = False
+        while not (stop and not held):
+            first = held.pop(0) if held else self._q.get()
+            if first is None:
+                stop = True
+                continue
+            batch, deadline = [first], time.monotonic() + self.max_wait
+            rest, held = held, []
+            for r in rest:                  # older leftovers first, in arrival order
+                (batch if r.key == first.key and len(batch) < self.max_batch else held).append(r)
+            while len(batch) < self.max_batch and not stop:
+                left = deadline - time.monotonic()
+                try:
+                    r = self._q.get(timeout=left) if left > 0 else self._q.get_nowait()
+                except queue.Empty:
+                    break
+                if r is None:
+                    stop = True
+                elif r.key == first.key:
+                    batch.append(r)
+                else:
+                    held.append(r)
+            self._dispatch(batch)
+
+    def _dispatch(self, batch: List[_Request]) -> None:
+        try:
+            results = self._run([r.color for r in batch], [r.depth for r in batch])
+            if len(results) != len(batch):
+                raise RuntimeError(f"run_batch returned {len(results)} results for {len(batch)} frames")
+        except BaseException as e:  # every waiting request thread gets the error (server.py:154-158 reports it)
+            for r in batch:
+                r.future.set_exception(e)
+            return
+        self.batches_run += 1
+        self.frames_run += len(batch)
+        for r, res in zip(batch, results):
+            r.future.set_result(res)

@@ -110,3 +110,42 @@ def test_server_loop_body_matches_the_oracle_end_to_end():
         borderline = np.abs(logits) < 0.05
         assert np.array_equal((logits > 0)[~borderline], small.astype(bool)[~borderline])
         assert small.mean() > 0.02          # the planted weights segment something at 256x256
+
+
+def test_micro_batcher_serves_ten_request_threads_like_the_direct_call():
+    """server.py:172 runs 10 worker threads; each gets the same numbers as one direct batched pass (frames are
+    independent, so batch composition must not matter)."""
+    import threading
+
+    from pkg.segmentation_model import UNet
+    from rdp_b200.batching import MicroBatcher
+    H, W, n_threads, per_thread = 240, 320, 10, 3
+    model = UNet(3, 1).eval()
+    model.load_state_dict(synth.make_state_dict(5, planted=True))
+    model = model.cuda()
+    frames = [synth.make_frame(300 + i, H, W, 0.30, "u16") for i in range(n_threads * per_thread)]
+    K, scale = frames[0]["K"], frames[0]["depth_scale"]
+    bgr = [np.ascontiguousarray(f["rgb"][:, :, ::-1]) for f in frames]          # what cv2.imdecode hands the server
+    direct = service.analyze_frames(model, torch.from_numpy(np.stack(bgr)).cuda(),
+                                    torch.from_numpy(np.stack([f["depth"] for f in frames])).cuda(), K, scale, bgr=True)
+    got = {}
+    with MicroBatcher(model, K, scale, max_batch=16, max_wait_ms=5.0) as mb:
+        def worker(t):
+            for j in range(per_thread):
+                i = t * per_thread + j
+                got[i] = mb.analyze(bgr[i], frames[i]["depth"])
+        threads = [threading.Thread(target=worker, args=(t,)) for t in range(n_threads)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(120)
+        assert mb.frames_run == len(frames) and mb.batches_run < len(frames)
+    assert sorted(got) == list(range(len(frames)))
+    for i, r in got.items():
+        assert np.array_equal(r.final_mask, direct.final_mask[i].cpu().numpy())
+        assert r.mask_coverage == float(direct.mask_coverage_percent[i])
+        ok = int(direct.curvature.status[i]) == _lib.FRAME_OK
+        assert len(r.curvature_results.spline_points) == (100 if ok else 0)
+        if ok:
+            assert r.curvature_results.mean_curvature == float(direct.curvature.mean_curvature[i])
+            assert r.curvature_results.max_curvature == float(direct.curvature.max_curvature[i])
