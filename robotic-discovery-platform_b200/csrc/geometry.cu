@@ -811,6 +811,7 @@ struct KnotWs {
   double *t, *q, *term, *fpint, *tri, *R, *z, *c, *D;
   int *lidx, *ibegin, *nrd, *nbeg, *tbeg, *tint, *tfirst;
   unsigned char* flag;
+  double *cr_ga, *cr_gb, *cr_e, *cr_c, *cr_scr;  // cyclic-reduction buffers, see cr_solve
 };
 __host__ __device__ inline int knot_task_cap(int cap) { return cap + cap / KN_CH + 2; }
 
@@ -891,7 +892,10 @@ __device__ __forceinline__ double rsqrt_pos(double a) {
 __device__ __forceinline__ void givens_fast(double piv, double& ww, double& cs, double& sn) {
   const double s2 = fma(piv, piv, ww * ww);
   const double inv = rsqrt_pos(s2);
-  const bool nz = piv != 0.0;  // also covers s2 == 0 (inv = NaN, discarded)
+  // Entries that are zero in exact arithmetic survive as rounding noise and, rotated level after level by the
+  // cyclic reduction, shrink until their square underflows (1e-166 seen): below 1e-150 a pivot counts as zero.
+  // Nothing legitimate is that small here (coordinates in metres, basis values, scaled knot differences).
+  const bool nz = fabs(piv) > 1e-150;  // also covers s2 == 0 (inv = inf, discarded)
   cs = nz ? ww * inv : 1.0;
   sn = nz ? piv * inv : 0.0;
   ww = nz ? s2 * inv : ww;
@@ -987,7 +991,7 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
         if (st <= q) {
           hh[q] = fma(hh[q], r[q], hh[q]);
           const double inv = hh[q] + hh[q];
-          const bool nz = h[q][st] != 0.0;
+          const bool nz = fabs(h[q][st]) > 1e-150;
           double& ww = Rw[4 - q + st][0];
           cs[q] = nz ? ww * inv : 1.0;
           sn[q] = nz ? h[q][st] * inv : 0.0;
@@ -1072,6 +1076,234 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
   }
 }
 
+// ---- the same least-squares solve by block cyclic reduction (all threads of the CTA) -------------------------
+// The sweep above is one dependent chain of about 15 rotations per knot interval.  Cut the columns into blocks of
+// four: an interval's triangle (4 columns) and a penalty row (5 columns) touch at most two neighbouring blocks, so
+// the problem is block bidiagonal, "group" g coupling blocks g and g+1.  A group is kept as an 8x8 triangle with
+// its right-hand side.  One level eliminates every other block: the two groups around block b (columns ordered
+// [c_b | c_left | c_right]) are rotated into four pivot rows, which are kept for the back substitution, and the
+// remainders are compressed into the 8x8 triangle of the group that now couples b's neighbours.  log2(blocks)
+// levels, then one 8x8 triangular solve and the back substitution down the levels.  Every transformation is a plane
+// rotation, so the solution is the least-squares solution to rounding, like the sweep's; the triangular factor is a
+// different one (other column order), which is why sum(diag R) for FITPACK's first p still comes from the sweep.
+// Blocks are padded to 2^L + 1 with identity rows.  Prototype with the same indexing: tools/proto/cr_banded_lsq.py.
+struct CrWs {
+  double *Ga, *Gb, *E, *cpad, *scr;
+};
+constexpr int KN_CR_MIN = 48;  // intervals from which the cyclic reduction replaces the one-thread sweep
+__host__ __device__ inline int knot_group_cap(int cap) { return cap / 2 + 8; }
+__device__ __forceinline__ constexpr int tri8(int j, int e) { return j * 8 - j * (j - 1) / 2 + (e - j); }
+
+__device__ __forceinline__ void rotate_in_tri8(double (&R)[36], double (&Z)[8][3], double (&h)[8], double (&x)[3]) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (fabs(h[j]) > 1e-150) {
+      double cs, sn;
+      givens_fast(h[j], R[tri8(j, j)], cs, sn);
+#pragma unroll
+      for (int e = j + 1; e < 8; ++e) rota(cs, sn, h[e], R[tri8(j, e)]);
+#pragma unroll
+      for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], Z[j][d]);
+    }
+  }
+}
+
+template <bool PEN>
+__device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
+                                      CrWs cw, double* c) {
+  const int tid = threadIdx.x;
+  const int nk1 = nrint + 3;
+  int L = 1;
+  while ((4 << L) < nrint) ++L;  // every interval index below 4 * 2^L, so each interval has its group; 2^L + 1 >= NB follows
+  const int ng0 = 1 << L, nbp = ng0 + 1;
+  // ---- level 0: groups from the interval triangles, the penalty rows and the padding ----
+  for (int g = tid; g < ng0; g += KN_THREADS) {
+    double R[36], Z[8][3];
+#pragma unroll
+    for (int q = 0; q < 36; ++q) R[q] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) Z[j][0] = Z[j][1] = Z[j][2] = 0.0;
+    for (int t = 0; t < 4; ++t) {
+      const int i = 4 * g + t;  // local columns t.. of the group
+      if (i >= nrint) break;
+      const double* o = tri + (size_t)tfirst[i] * 22;
+      const double* dr = D + (size_t)i * 5;
+      const int nrow = (PEN && i < nrint - 1) ? 5 : 4;
+      for (int r = 0; r < nrow; ++r) {
+        double h[8], x[3];
+        if (r < 4) {
+          const int base = r * 4 - r * (r - 1) / 2 - r;  // packed index of entry (r, e) of the 4x4 triangle = base + e
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int e = k - t;
+            h[k] = (e >= r && e <= 3) ? o[base + e] : 0.0;
+          }
+#pragma unroll
+          for (int d = 0; d < 3; ++d) x[d] = o[10 + 3 * r + d];
+        } else {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int e = k - t;
+            h[k] = (e >= 0 && e <= 4) ? dr[e] * pinv : 0.0;
+          }
+          x[0] = x[1] = x[2] = 0.0;
+        }
+        rotate_in_tri8(R, Z, h, x);
+      }
+    }
+#pragma unroll
+    for (int lc = 4; lc < 8; ++lc)
+      if (4 * g + lc >= nk1) R[tri8(lc, lc)] = 1.0;  // padding column: no row touches it, identity row
+#pragma unroll
+    for (int q = 0; q < 36; ++q) cw.Ga[(size_t)q * ng0 + g] = R[q];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int d = 0; d < 3; ++d) cw.Ga[(size_t)(36 + 3 * j + d) * ng0 + g] = Z[j][d];
+  }
+  __syncthreads();
+  // ---- levels: eliminate block (2j+1) * 2^lvl between groups 2j and 2j+1 ----
+  double* Gin = cw.Ga;
+  double* Gout = cw.Gb;
+  int ngin = ng0;
+  for (int lvl = 0; lvl < L; ++lvl) {
+    const int ngout = ngin >> 1;
+    for (int j = tid; j < ngout; j += KN_THREADS) {
+      double P[4][12], PZ[4][3];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) {
+#pragma unroll
+        for (int e = 0; e < 12; ++e) P[a][e] = 0.0;
+        PZ[a][0] = PZ[a][1] = PZ[a][2] = 0.0;
+      }
+      for (int k = 0; k < 16; ++k) {  // rows of the left group (columns c_left | c_b), then of the right one (c_b | c_right)
+        const int gsel = 2 * j + (k >> 3), kk = k & 7;
+        const int base = kk * 8 - kk * (kk - 1) / 2 - kk;  // tri8(kk, e) = base + e
+        double r8[8], h[12], x[3];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) r8[e] = e >= kk ? Gin[(size_t)(base + e) * ngin + gsel] : 0.0;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) x[d] = Gin[(size_t)(36 + 3 * kk + d) * ngin + gsel];
+        const bool left = k < 8;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          h[e] = left ? r8[4 + e] : r8[e];
+          h[4 + e] = left ? r8[e] : 0.0;
+          h[8 + e] = left ? 0.0 : r8[4 + e];
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+          if (fabs(h[a]) > 1e-150) {
+            double cs, sn;
+            givens_fast(h[a], P[a][a], cs, sn);
+#pragma unroll
+            for (int e = a + 1; e < 12; ++e) rota(cs, sn, h[e], P[a][e]);
+#pragma unroll
+            for (int d = 0; d < 3; ++d) rota(cs, sn, x[d], PZ[a][d]);
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) cw.scr[(size_t)(k * 11 + e) * KN_THREADS + tid] = h[4 + e];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) cw.scr[(size_t)(k * 11 + 8 + d) * KN_THREADS + tid] = x[d];
+      }
+      const int b = (2 * j + 1) << lvl;
+      {
+        int q = 0;
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int e = 0; e < 12; ++e)
+            if (e >= a) cw.E[(size_t)(q++) * nbp + b] = P[a][e];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int d = 0; d < 3; ++d) cw.E[(size_t)(42 + 3 * a + d) * nbp + b] = PZ[a][d];
+      }
+      double R[36], Z[8][3];
+#pragma unroll
+      for (int q = 0; q < 36; ++q) R[q] = 0.0;
+#pragma unroll
+      for (int a = 0; a < 8; ++a) Z[a][0] = Z[a][1] = Z[a][2] = 0.0;
+      for (int k = 0; k < 16; ++k) {
+        double h[8], x[3];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) h[e] = cw.scr[(size_t)(k * 11 + e) * KN_THREADS + tid];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) x[d] = cw.scr[(size_t)(k * 11 + 8 + d) * KN_THREADS + tid];
+        rotate_in_tri8(R, Z, h, x);
+      }
+#pragma unroll
+      for (int q = 0; q < 36; ++q) Gout[(size_t)q * ngout + j] = R[q];
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) Gout[(size_t)(36 + 3 * a + d) * ngout + j] = Z[a][d];
+    }
+    __syncthreads();
+    double* sw = Gin;
+    Gin = Gout;
+    Gout = sw;
+    ngin = ngout;
+  }
+  // ---- the last group couples block 0 and block 2^L: 8x8 triangular solve ----
+  double* cp = cw.cpad;  // [4 * nbp][3]
+  if (tid == 0) {
+    double top[8][3];
+#pragma unroll
+    for (int j = 7; j >= 0; --j) {
+      const double dg = Gin[tri8(j, j)];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        double a = Gin[36 + 3 * j + d];
+#pragma unroll
+        for (int e = j + 1; e < 8; ++e) a -= Gin[tri8(j, e)] * top[e][d];
+        top[j][d] = dg != 0.0 ? a / dg : 0.0;
+        const int col = j < 4 ? j : 4 * ng0 + (j - 4);
+        cp[(size_t)col * 3 + d] = top[j][d];
+      }
+    }
+  }
+  __syncthreads();
+  // ---- back substitution down the levels ----
+  for (int lvl = L - 1; lvl >= 0; --lvl) {
+    const int cnt = 1 << (L - lvl - 1);
+    for (int j = tid; j < cnt; j += KN_THREADS) {
+      const int b = (2 * j + 1) << lvl, bl = b - (1 << lvl), br = b + (1 << lvl);
+      double side[8][3], cb[4][3];
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          side[e][d] = cp[(size_t)(4 * bl + e) * 3 + d];
+          side[4 + e][d] = cp[(size_t)(4 * br + e) * 3 + d];
+        }
+      int q = 42;  // packed index walks backwards: row 3 (9 entries), row 2 (10), row 1 (11), row 0 (12)
+#pragma unroll
+      for (int a = 3; a >= 0; --a) {
+        q -= 12 - a;
+        const double dg = cw.E[(size_t)q * nbp + b];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          double acc = cw.E[(size_t)(42 + 3 * a + d) * nbp + b];
+#pragma unroll
+          for (int e = a + 1; e < 4; ++e) acc -= cw.E[(size_t)(q + e - a) * nbp + b] * cb[e][d];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc -= cw.E[(size_t)(q + 4 - a + e) * nbp + b] * side[e][d];
+          cb[a][d] = dg != 0.0 ? acc / dg : 0.0;
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) cp[(size_t)(4 * b + a) * 3 + d] = cb[a][d];
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < nk1 * 3; i += KN_THREADS) c[i] = cp[i];
+  __syncthreads();
+}
+
 __device__ __forceinline__ double block_sum1(double v, double* s_red) {
   v = warp_sum(v);
   __syncthreads();
@@ -1103,6 +1335,13 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   w.tbeg = base.tbeg + (size_t)b * tcap;
   w.tint = base.tint + (size_t)b * tcap;
   w.tfirst = base.tfirst + (size_t)b * cap;
+  const size_t gcap = (size_t)knot_group_cap(cap);
+  CrWs cw;
+  cw.Ga = base.cr_ga + (size_t)b * gcap * 60;
+  cw.Gb = base.cr_gb + (size_t)b * (gcap / 2 + 4) * 60;
+  cw.E = base.cr_e + (size_t)b * (gcap + 1) * 54;
+  cw.cpad = base.cr_c + (size_t)b * (gcap + 1) * 12;
+  cw.scr = base.cr_scr + (size_t)b * 16 * 11 * KN_THREADS;
   w.R = base.R + (size_t)b * cap * 5;
   w.z = base.z + (size_t)b * cap * 3;
   w.c = base.c + (size_t)b * cap * 3;
@@ -1128,6 +1367,8 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   int n = 8, nrint = 1, nk1 = 4, nplus = 0, ier = 0, ntasks = 0, max_tasks = 1;
   long long tm_tri = 0, tm_merge = 0, tm_res = 0, tm_setup = 0, tm_knot = 0, tm_mark = 0;  // RDP_DEBUG_KNOTS
   int n_solve = 0, n_iter = 0;
+  bool band_R_valid = false;     // w.R holds the banded triangle of the last solve (the sweep's, not the cyclic reduction's)
+  const bool no_cr = (debug & 4) != 0;  // RDP_DEBUG_KNOTS=4: one-thread sweep for every solve (A/B timing)
   auto lap = [&](long long& acc) {
     if (debug) {
       const long long now = clock64();
@@ -1227,11 +1468,18 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     }
     lap(tm_tri);
     // (2) merge into the band, penalty rows interleaved by last column; back substitution
-    if (tid == 0) {
-      if (pinv > 0.0) band_merge_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, w.R, w.z, w.c);
-      else band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
+    if (nrint >= KN_CR_MIN && !no_cr) {
+      if (pinv > 0.0) cr_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, cw, w.c);
+      else cr_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, cw, w.c);
+      band_R_valid = false;
+    } else {
+      if (tid == 0) {
+        if (pinv > 0.0) band_merge_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, w.R, w.z, w.c);
+        else band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
+      }
+      band_R_valid = true;
+      __syncthreads();
     }
-    __syncthreads();
     lap(tm_merge);
     // (3) residuals
     double part = 0.0;
@@ -1342,7 +1590,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
 
     fp = solve(0.0);
-    if (debug > 1 && tid == 0) {
+    if ((debug & 2) && tid == 0 && band_R_valid) {
       double sd = 0.0;
       for (int i = 0; i < nk1; ++i) sd += w.R[i * 5];
       printf("  frame %d lsq n %d fp %.17g sumdiag %.17g\n", b, n, fp, sd);
@@ -1476,6 +1724,11 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
         ++lp;
       }
     }
+    if (!band_R_valid) {  // FITPACK's first p needs the diagonal of the banded triangle of the last least-squares fit
+      if (tid == 0) band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
+      __syncthreads();
+    }
+    lap(tm_merge);
     double sumdiag = 0.0;
     for (int i = tid; i < nk1; i += KN_THREADS) sumdiag += w.R[i * 5];
     sumdiag = block_sum1(sumdiag, s_red);
@@ -1485,7 +1738,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     for (int it = 1; it <= KN_MAXIT; ++it) {
       fp = solve(1.0 / pp);
       fpms = fp - s;
-      if (debug > 1 && tid == 0) printf("  frame %d smoothing it %d p %.17g fp %.17g (p1 %.17g p3 %.17g)\n", b, it, pp, fp, p1, p3);
+      if ((debug & 2) && tid == 0) printf("  frame %d smoothing it %d p %.17g fp %.17g (p1 %.17g p3 %.17g)\n", b, it, pp, fp, p1, p3);
       if (fabs(fpms) < acc) break;
       if (it == KN_MAXIT) { ier = 3; break; }
       const double p2 = pp, f2 = fpms;
@@ -1576,7 +1829,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     p.out.mean_curvature[b] = kcnt > 0.0 ? ksum / kcnt : 0.0;
     p.out.max_curvature[b] = kcnt > 0.0 ? key_to_double(kmax_key) : 0.0;
     p.out.status[b] = RDP_FRAME_OK;
-    if (debug && (debug > 1 || b == 0))
+    if (debug && ((debug & 2) || b == 0))
       printf("k_fit_knots frame %d: m %d knots %d solves %d knot-iterations %d | kcycles setup %lld triangles %lld merge %lld residual %lld fpknot %lld\n",
              b, m, n, n_solve, n_iter, tm_setup / 1000, tm_tri / 1000, tm_merge / 1000, tm_res / 1000, tm_knot / 1000);
     if (p.out.n_knots) p.out.n_knots[b] = n;
@@ -1611,6 +1864,12 @@ static void carve_knots(Carver& c, KnotWs& k, int B, int ecap) {
   k.tint = c.take<int>(B * tcap);
   k.tfirst = c.take<int>(B * cap);
   k.flag = c.take<unsigned char>(B * e);
+  const size_t gcap = (size_t)knot_group_cap((int)cap);
+  k.cr_ga = c.take<double>(B * gcap * 60);
+  k.cr_gb = c.take<double>(B * (gcap / 2 + 4) * 60);
+  k.cr_e = c.take<double>(B * (gcap + 1) * 54);
+  k.cr_c = c.take<double>(B * (gcap + 1) * 12);
+  k.cr_scr = c.take<double>((size_t)B * 16 * 11 * KN_THREADS);
 }
 
 static Plan carve(Params& p, KnotWs& kn, void* ws, int B, int H, int W) {

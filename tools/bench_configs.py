@@ -6,6 +6,8 @@
 C3  U-Net + curvature at 1280x720, batch 32
 C4  geometry only, 640x480 and 1280x720, mask fill 5..60 %, batch 256, each line labelled with the spline regime
 C5  streaming: N frames from a ring of 1024 pinned host frames through rdp_b200.pipeline.FramePipeline
+S   the server-shaped workload: resize to 256x256 -> U-Net -> nearest up-size -> curvature at camera
+    resolution (rdp_b200.service.analyze_frames), device-resident, and the same through MicroBatcher from 10 host threads
 Timing: CUDA events on the launching stream, 3 warm-up passes, inputs > L2 or rotated.
 """
 import argparse
@@ -125,11 +127,59 @@ def c5(n_frames):
             "seconds": ms * 1e-3, "frames_per_s": steps * B / ms * 1e3, "frames_ok": ok}
 
 
+def server_shaped():
+    import threading
+    import time
+
+    from rdp_b200 import service
+    from rdp_b200.batching import MicroBatcher
+    out = []
+    model = model_on_gpu()
+    for (H, W) in ((480, 640), (720, 1280)):
+        frames = [synth.make_frame(9500 + i, H, W, 0.30, "u16") for i in range(8)]
+        K, scale = frames[0]["K"], frames[0]["depth_scale"]
+        for B in (64, 256):
+            rgb = torch.from_numpy(np.stack([frames[i % 8]["rgb"] for i in range(B)])).cuda()
+            depth = torch.from_numpy(np.stack([frames[i % 8]["depth"] for i in range(B)])).cuda()
+            ms = timed(lambda: service.analyze_frames(model, rgb, depth, K, scale), 5)
+            r = service.analyze_frames(model, rgb, depth, K, scale)
+            lm = []
+            geometry.curvature_batch(r.final_mask, depth, K, scale, launch_ms=lm)
+            out.append({"config": f"S1: server loop body {W}x{H} -> 256x256 U-Net -> curvature at {W}x{H}, batch {B}, device-resident",
+                        "ms_per_batch": ms, "frames_per_s": B / ms * 1e3, "frames_ok": int((r.curvature.status == 0).sum()),
+                        "knots_min": int(r.curvature.n_knots.min()), "knots_max": int(r.curvature.n_knots.max()),
+                        "coverage_percent": float(r.mask_coverage_percent.mean()),
+                        "geometry_launch_ms": {k: round(v, 4) for k, v in zip(geometry.LAUNCH_NAMES, lm)}})
+            print(json.dumps(out[-1]), file=sys.stderr)
+        # N2: ten request threads (server.py:172) with host frames, results back on the host (mask included)
+        n_threads, per_thread = 10, 64
+        with MicroBatcher(model, K, scale, max_batch=64, max_wait_ms=2.0, bgr=False) as mb:
+            def worker(t):
+                for j in range(per_thread):
+                    f = frames[(t + j) % 8]
+                    mb.analyze(f["rgb"], f["depth"])
+            for rep in range(2):          # the first pass warms the staging buffers and the workspace allocator
+                threads = [threading.Thread(target=worker, args=(t,)) for t in range(n_threads)]
+                t0 = time.perf_counter()
+                for t in threads:
+                    t.start()
+                for t in threads:
+                    t.join()
+                dt = time.perf_counter() - t0
+            out.append({"config": f"S2: MicroBatcher, 10 request threads x {per_thread} frames {W}x{H} from host memory, "
+                                  "mask + curvature back on the host (wall clock)",
+                        "frames_per_s": n_threads * per_thread / dt, "batches": mb.batches_run, "frames": mb.frames_run,
+                        "mean_batch": mb.frames_run / max(1, mb.batches_run)})
+            print(json.dumps(out[-1]), file=sys.stderr)
+    return out
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--c3", action="store_true")
     ap.add_argument("--c4", action="store_true")
     ap.add_argument("--c5", type=int, default=0)
+    ap.add_argument("--server", action="store_true")
     a = ap.parse_args()
     res = {}
     if a.c3:
@@ -138,4 +188,6 @@ if __name__ == "__main__":
         res["C4"] = c4()
     if a.c5:
         res["C5"] = c5(a.c5)
+    if a.server:
+        res["S"] = server_shaped()
     print(json.dumps(res, indent=1))
