@@ -1320,6 +1320,8 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   __shared__ int s_i[8];
   __shared__ unsigned long long s_best[KN_THREADS / 32];
   __shared__ int s_besti[KN_THREADS / 32];
+  __shared__ unsigned long long s_knot_key[2][KN_THREADS / 32];
+  __shared__ int4 s_knot_meta[2][KN_THREADS / 32];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (p.out.status[b] != RDP_FRAME_NEEDS_KNOTS) return;
   const int m = p.fs[b].n_edge;
@@ -1367,6 +1369,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   int n = 8, nrint = 1, nk1 = 4, nplus = 0, ier = 0, ntasks = 0, max_tasks = 1;
   long long tm_tri = 0, tm_merge = 0, tm_res = 0, tm_setup = 0, tm_knot = 0, tm_mark = 0;  // RDP_DEBUG_KNOTS
   int n_solve = 0, n_iter = 0;
+  bool tri_valid = false;        // w.tri holds the per-interval triangles of the current knots
   bool band_R_valid = false;     // w.R holds the banded triangle of the last solve (the sweep's, not the cyclic reduction's)
   const bool no_cr = (debug & 4) != 0;  // RDP_DEBUG_KNOTS=4: one-thread sweep for every solve (A/B timing)
   auto lap = [&](long long& acc) {
@@ -1383,7 +1386,9 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   auto solve = [&](double pinv) -> double {
     lap(tm_setup);
     ++n_solve;
-    // (1) task triangles, one thread per task (at most KN_CH consecutive points of one interval)
+    // (1) task triangles, one thread per task (at most KN_CH consecutive points of one interval).  They depend on the
+    // knots only, not on the smoothing parameter: the root find reuses those of the last least-squares fit.
+    if (!tri_valid) {
     for (int k = tid; k < ntasks; k += KN_THREADS) {
       double T[4][4] = {}, Z[4][3] = {};
       const int p0 = w.tbeg[k], p1 = k + 1 < ntasks ? w.tbeg[k + 1] : m;
@@ -1466,6 +1471,8 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       }
       __syncthreads();
     }
+    tri_valid = true;
+    }
     lap(tm_tri);
     // (2) merge into the band, penalty rows interleaved by last column; back substitution
     if (nrint >= KN_CR_MIN && !no_cr) {
@@ -1505,6 +1512,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   if (debug) tm_mark = clock64();
   for (int iter = 0; iter < m && !finished && !smoothing; ++iter) {
     // ---- knot vector, interval of every point and interval starts from the flags (block scan over the points) ----
+    tri_valid = false;
     int carry = 0, carry2 = 0;
     for (int i0 = 0; i0 < m; i0 += KN_THREADS) {
       const int i = i0 + tid;
@@ -1630,74 +1638,95 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     }
     __syncthreads();
     // ---- fpknot x nplus: split the interval with the largest residual that still has interior points ----
+    // Node i (residual, interior point count, first interior point) belongs to thread i mod KN_THREADS: only its owner
+    // reads or writes it, so the nodes need no barrier.  Every thread keeps the best of its own nodes in registers;
+    // a split changes two nodes, and only their owners look through theirs again.  Per knot: one shuffle reduction,
+    // one barrier (the per-warp results are double-buffered), and every thread derives the same winner.
     int nn = nrint;
-    for (int l = 0; l < nplus; ++l) {
-      unsigned long long bestk = 0;
-      int besti = -1;
+    unsigned long long my_key = 0;  // residual as an integer (positive doubles order as their bit patterns); 0 = nothing
+    int my_beg = 0x7fffffff, my_nrd = 0, my_idx = -1;
+    auto rescan = [&]() {
+      my_key = 0;
+      my_beg = 0x7fffffff;
+      my_nrd = 0;
+      my_idx = -1;
       for (int i = tid; i < nn; i += KN_THREADS) {
-        if (w.nrd[i] == 0) continue;
+        const int nr = w.nrd[i];
+        if (nr == 0) continue;
         const double v = w.fpint[i];
         if (!(v > 0.0)) continue;  // FITPACK starts from fpmax = 0 with a strict comparison
-        const unsigned long long key = (unsigned long long)__double_as_longlong(v);  // positive doubles order as integers
-        if (key > bestk || (key == bestk && w.nbeg[i] < w.nbeg[besti])) {
-          bestk = key;
-          besti = i;
+        const unsigned long long key = (unsigned long long)__double_as_longlong(v);
+        const int nb = w.nbeg[i];
+        if (key > my_key || (key == my_key && nb < my_beg)) {  // larger residual first, earlier interval on ties
+          my_key = key;
+          my_beg = nb;
+          my_nrd = nr;
+          my_idx = i;
         }
       }
-      // block arg-max: larger residual first, earlier interval on ties
+    };
+    rescan();
+    for (int l = 0; l < nplus; ++l) {
+      unsigned long long bk = my_key;
+      int bb = my_beg, br = my_nrd, bi = my_idx;
+#pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bestk, o);
-        const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
-        const int ob = oi >= 0 ? w.nbeg[oi] : 0x7fffffff, mb = besti >= 0 ? w.nbeg[besti] : 0x7fffffff;
-        if (ok > bestk || (ok == bestk && ob < mb)) {
-          bestk = ok;
-          besti = oi;
+        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bk, o);
+        const int ob = __shfl_xor_sync(0xffffffffu, bb, o), orr = __shfl_xor_sync(0xffffffffu, br, o),
+                  oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ok > bk || (ok == bk && ob < bb)) {
+          bk = ok;
+          bb = ob;
+          br = orr;
+          bi = oi;
         }
       }
+      const int buf = l & 1;
       if (lane == 0) {
-        s_best[warp] = bestk;
-        s_besti[warp] = besti;
+        s_knot_key[buf][warp] = bk;
+        s_knot_meta[buf][warp] = make_int4(bb, br, bi, 0);
       }
       __syncthreads();
-      if (tid == 0) {
-        unsigned long long bk = 0;
-        int bi = -1;
-        for (int k = 0; k < KN_THREADS / 32; ++k) {
-          const int oi = s_besti[k];
-          if (oi < 0) continue;
-          if (bi < 0 || s_best[k] > bk || (s_best[k] == bk && w.nbeg[oi] < w.nbeg[bi])) {
-            bk = s_best[k];
-            bi = oi;
-          }
+      bk = 0;
+      bb = 0x7fffffff;
+      br = 0;
+      bi = -1;
+#pragma unroll
+      for (int k = 0; k < KN_THREADS / 32; ++k) {
+        const unsigned long long ok = s_knot_key[buf][k];
+        const int4 om = s_knot_meta[buf][k];
+        if (ok > bk || (ok == bk && om.x < bb)) {
+          bk = ok;
+          bb = om.x;
+          br = om.y;
+          bi = om.z;
         }
-        int stop = 0;  // 0 go on, 1 nothing left to split, 2 reached nmax (interpolation knots), 3 reached nest
-        if (bi < 0) {
-          stop = 1;
-        } else {
-          const double fpmax = w.fpint[bi];
-          const int maxpt = w.nrd[bi], maxbeg = w.nbeg[bi];
-          const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
-          w.flag[nrx - 1] = 1;
-          w.nrd[bi] = ihalf - 1;
-          w.fpint[bi] = fpmax * (double)(ihalf - 1) / (double)maxpt;
-          w.nrd[nn] = maxpt - ihalf;
-          w.nbeg[nn] = nrx;
-          w.fpint[nn] = fpmax * (double)(maxpt - ihalf) / (double)maxpt;
-          if (n + 1 == nmax) stop = 2;
-          else if (n + 1 == nest) stop = 3;
-        }
-        s_i[0] = stop;
       }
-      __syncthreads();
-      const int stop = s_i[0];
-      if (stop == 1) break;
+      if (bi < 0) break;  // nothing left to split (block-uniform: every thread derived the same winner)
+      const double fpmax = __longlong_as_double((long long)bk);
+      const int maxpt = br, maxbeg = bb;
+      const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
+      const bool own_old = (bi % KN_THREADS) == tid, own_new = (nn % KN_THREADS) == tid;
+      if (own_old) {
+        w.flag[nrx - 1] = 1;
+        w.nrd[bi] = ihalf - 1;
+        w.fpint[bi] = fpmax * (double)(ihalf - 1) / (double)maxpt;
+      }
+      if (own_new) {
+        w.nrd[nn] = maxpt - ihalf;
+        w.nbeg[nn] = nrx;
+        w.fpint[nn] = fpmax * (double)(maxpt - ihalf) / (double)maxpt;
+      }
+      const int stop = (n + 1 == nmax) ? 2 : ((n + 1 == nest) ? 3 : 0);  // nmax: interpolation knots, nest: storage limit
       ++n;
       ++nn;
       if (stop == 2) {  // n == nmax: knots as for interpolation, t[4+i] = u[2+i]
+        __syncthreads();  // the flag set above by another thread must not land after the rewrite below
         for (int i = tid; i < m; i += KN_THREADS) w.flag[i] = (i >= 2 && i <= m - 3) ? 1 : 0;
         break;
       }
       if (stop == 3) break;
+      if (own_old || own_new) rescan();
     }
     __syncthreads();
     lap(tm_knot);
