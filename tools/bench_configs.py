@@ -169,7 +169,8 @@ def server_shaped():
             out.append({"config": f"S2: MicroBatcher, 10 request threads x {per_thread} frames {W}x{H} from host memory, "
                                   "mask + curvature back on the host (wall clock)",
                         "frames_per_s": n_threads * per_thread / dt, "batches": mb.batches_run, "frames": mb.frames_run,
-                        "mean_batch": mb.frames_run / max(1, mb.batches_run)})
+                        "mean_batch": mb.frames_run / max(1, mb.batches_run),
+                        "dispatcher_seconds": {k: round(v, 4) for k, v in mb._run.seconds.items()}, "wall_seconds_last_pass": dt})
             print(json.dumps(out[-1]), file=sys.stderr)
     return out
 
