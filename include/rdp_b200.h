@@ -191,6 +191,18 @@ int rdp_pre_resize(const uint8_t* rgb_nhwc, int B, int H, int W, int C, int out_
 int rdp_post_mask_nearest(const uint8_t* mask, int B, int h, int w, int H, int W, uint8_t* out, int32_t* nonzero,
                           void* stream);
 
+/* Replaces `cv2.imencode('.png', final_mask * 255)` (server.py:142-143): the mask leaves the GPU as the PNG the
+ * response carries, not as H*W bytes for a host encoder.  The client reads it with cv2.imdecode(.., IMREAD_GRAYSCALE)
+ * (client.py:111-112); the bytes are not OpenCV's (1 bit per pixel, filter 0, one fixed-Huffman deflate block of
+ * literals and distance-1 matches), the decoded picture is: 255 where mask != 0, else 0.
+ *   mask [B][H][W] uint8 (device)
+ *   png  [B][png_stride] bytes (device, 4-byte aligned, png_stride a multiple of 4 and >= max_png_bytes)
+ *   png_bytes [B] int32 (device): length of each frame's PNG
+ * rdp_post_mask_png_sizes gives max_png_bytes (per frame, worst case) and the workspace the call needs.  Two launches. */
+int rdp_post_mask_png_sizes(int B, int H, int W, size_t* max_png_bytes, size_t* workspace_bytes);
+int rdp_post_mask_png(const uint8_t* mask, int B, int H, int W, uint8_t* png, size_t png_stride, int32_t* png_bytes,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -79,3 +79,17 @@ def upsize_mask_np(mask_small: np.ndarray, H: int, W: int) -> np.ndarray:
     ys = np.minimum(np.floor(np.arange(H) * ify).astype(np.int64), h - 1)
     xs = np.minimum(np.floor(np.arange(W) * ifx).astype(np.int64), w - 1)
     return mask_small.reshape(h, w)[ys][:, xs]
+
+
+def encode_mask_png(final_mask: np.ndarray) -> bytes:
+    """`cv2.imencode('.png', final_mask * 255)` + `.tobytes()` (`server.py:142-143`)."""
+    import cv2
+    ok, buf = cv2.imencode(".png", final_mask * 255)
+    assert ok
+    return buf.tobytes()
+
+
+def decode_mask_png(data: bytes) -> np.ndarray:
+    """What the client does with `response.mask` (`client.py:111-112`)."""
+    import cv2
+    return cv2.imdecode(np.frombuffer(data, dtype=np.uint8), cv2.IMREAD_GRAYSCALE)

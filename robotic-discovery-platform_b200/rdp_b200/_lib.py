@@ -20,7 +20,7 @@ EXPORTS = [
     "rdp_unet_read_activation", "rdp_unet_forward_profiled",
     "rdp_geom_workspace_bytes", "rdp_geom_curvature", "rdp_geom_launch_count", "rdp_geom_curvature_profiled",
     "rdp_geom_deproject_static",
-    "rdp_pre_resize", "rdp_post_mask_nearest",
+    "rdp_pre_resize", "rdp_post_mask_nearest", "rdp_post_mask_png_sizes", "rdp_post_mask_png",
 ]
 
 
@@ -84,6 +84,11 @@ def load() -> C.CDLL:
         lib.rdp_pre_resize.restype = C.c_int
         lib.rdp_post_mask_nearest.argtypes = [C.c_void_p] + [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.rdp_post_mask_nearest.restype = C.c_int
+        lib.rdp_post_mask_png_sizes.argtypes = [C.c_int] * 3 + [C.POINTER(C.c_size_t)] * 2
+        lib.rdp_post_mask_png_sizes.restype = C.c_int
+        lib.rdp_post_mask_png.argtypes = [C.c_void_p] + [C.c_int] * 3 + [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
+                                                                        C.c_size_t, C.c_void_p]
+        lib.rdp_post_mask_png.restype = C.c_int
         lib.rdp_unet_forward_profiled.argtypes = lib.rdp_unet_forward.argtypes + [C.POINTER(C.c_float)]
         lib.rdp_geom_curvature_profiled.argtypes = lib.rdp_geom_curvature.argtypes + [C.POINTER(C.c_float)]
         for name in ("rdp_unet_create", "rdp_unet_workspace_bytes", "rdp_unet_forward", "rdp_unet_launch_count",

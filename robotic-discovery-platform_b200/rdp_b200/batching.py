@@ -23,9 +23,10 @@ import numpy as np
 class FrameResult:
     """What one iteration of the server loop needs to fill its response (`server.py:127-143`)."""
     curvature_results: object            # pkg.geometry_utils.CurvatureResult, as compute_curvature_profile returns it
-    final_mask: np.ndarray               # (H,W) uint8 {0,1}
+    final_mask: Optional[np.ndarray]     # (H,W) uint8 {0,1}; None when the batcher was built with want_mask=False
     mask_coverage: float                 # percent, server.py:133
     batch_size: int = 1                  # how many frames shared the GPU pass (diagnostics)
+    mask_png: Optional[bytes] = None     # the response's `mask` field (server.py:142-143), encoded on the GPU (want_png=True)
 
 
 @dataclass
@@ -36,7 +37,7 @@ class _Request:
     key: tuple
 
 
-def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device) -> Callable:
+def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, want_mask: bool, want_png: bool) -> Callable:
     """The default `run_batch`: stacked host frames -> list of FrameResult through the CUDA loop body."""
     import torch
 
@@ -65,9 +66,12 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device) ->
             status = r.curvature.status.cpu().numpy()
             mean, mx = r.curvature.mean_curvature.cpu().numpy(), r.curvature.max_curvature.cpu().numpy()
             pts = r.curvature.spline_points.cpu().numpy()
-            masks, cov = r.final_mask.cpu().numpy(), r.mask_coverage_percent.cpu().numpy()
+            cov = r.mask_coverage_percent.cpu().numpy()
+            pngs = service.encode_mask_png(r.final_mask) if want_png else [None] * B   # a few KB per frame instead of H*W
+            masks = r.final_mask.cpu().numpy() if want_mask else [None] * B
         t2 = time.perf_counter()
-        out = [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B) for i in range(B)]
+        out = [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B, pngs[i])
+               for i in range(B)]
         t3 = time.perf_counter()
         run.seconds["stage"] += t1 - t0
         run.seconds["gpu_and_copies"] += t2 - t1
@@ -82,11 +86,13 @@ class MicroBatcher:
     """Thread-safe: any number of request threads call `analyze` (blocking) or `submit` (returns a Future)."""
 
     def __init__(self, model=None, intrinsics=None, depth_scale=None, *, max_batch: int = 64, max_wait_ms: float = 2.0,
-                 bgr: bool = True, size: int = 256, device="cuda", run_batch: Optional[Callable] = None):
+                 bgr: bool = True, size: int = 256, device="cuda", want_mask: bool = True, want_png: bool = False,
+                 run_batch: Optional[Callable] = None):
         if max_batch < 1:
             raise ValueError("max_batch must be >= 1")
         self.max_batch, self.max_wait = int(max_batch), float(max_wait_ms) / 1e3
-        self._run = run_batch if run_batch is not None else _gpu_runner(model, intrinsics, depth_scale, bgr, size, device)
+        self._run = run_batch if run_batch is not None else _gpu_runner(model, intrinsics, depth_scale, bgr, size, device,
+                                                                             want_mask, want_png)
         self._q: "queue.Queue[Optional[_Request]]" = queue.Queue()
         self._closed = False
         self.batches_run, self.frames_run = 0, 0

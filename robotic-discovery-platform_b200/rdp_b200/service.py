@@ -56,6 +56,30 @@ def upsize_mask(mask_small: torch.Tensor, H: int, W: int, *, want_count: bool = 
     return out, cnt
 
 
+def encode_mask_png(final_mask: torch.Tensor, *, to_host: bool = True):
+    """(B,H,W) uint8 -> one PNG per frame (`cv2.imencode('.png', final_mask * 255)`, `server.py:142-143`), encoded on
+    the GPU.  Returns a list of `bytes` (to_host=True: two small copies, lengths then payload) or the device buffer
+    (B, stride) uint8 with the lengths (B,) int32."""
+    import ctypes as C
+    m = _need_cuda_u8(final_mask, "mask batch", 3)
+    B, H, W = m.shape
+    lib = _lib.load()
+    max_png, ws_bytes = C.c_size_t(), C.c_size_t()
+    _lib.check(lib.rdp_post_mask_png_sizes(B, H, W, C.byref(max_png), C.byref(ws_bytes)), "rdp_post_mask_png_sizes")
+    stride = (max_png.value + 3) // 4 * 4
+    png = torch.empty((B, stride), dtype=torch.uint8, device=m.device)
+    nbytes = torch.empty(B, dtype=torch.int32, device=m.device)
+    ws = torch.empty(ws_bytes.value, dtype=torch.uint8, device=m.device)
+    with torch.cuda.device(m.device):
+        _lib.check(lib.rdp_post_mask_png(m.data_ptr(), B, H, W, png.data_ptr(), stride, nbytes.data_ptr(), ws.data_ptr(),
+                                         ws.numel(), torch.cuda.current_stream(m.device).cuda_stream), "rdp_post_mask_png")
+    if not to_host:
+        return png, nbytes
+    n = nbytes.cpu().numpy()
+    host = png[:, :int(n.max())].cpu().numpy()
+    return [host[i, :n[i]].tobytes() for i in range(B)]
+
+
 @dataclass
 class FrameAnalysis:
     curvature: geometry.CurvatureBatch   # mean/max curvature, spline points, status per frame

@@ -129,7 +129,7 @@ def test_micro_batcher_serves_ten_request_threads_like_the_direct_call():
     direct = service.analyze_frames(model, torch.from_numpy(np.stack(bgr)).cuda(),
                                     torch.from_numpy(np.stack([f["depth"] for f in frames])).cuda(), K, scale, bgr=True)
     got = {}
-    with MicroBatcher(model, K, scale, max_batch=16, max_wait_ms=5.0) as mb:
+    with MicroBatcher(model, K, scale, max_batch=16, max_wait_ms=5.0, want_png=True) as mb:
         def worker(t):
             for j in range(per_thread):
                 i = t * per_thread + j
@@ -144,8 +144,56 @@ def test_micro_batcher_serves_ten_request_threads_like_the_direct_call():
     for i, r in got.items():
         assert np.array_equal(r.final_mask, direct.final_mask[i].cpu().numpy())
         assert r.mask_coverage == float(direct.mask_coverage_percent[i])
+        assert np.array_equal(sp.decode_mask_png(r.mask_png), r.final_mask * 255)     # what the client would see
         ok = int(direct.curvature.status[i]) == _lib.FRAME_OK
         assert len(r.curvature_results.spline_points) == (100 if ok else 0)
         if ok:
             assert r.curvature_results.mean_curvature == float(direct.curvature.mean_curvature[i])
             assert r.curvature_results.max_curvature == float(direct.curvature.max_curvature[i])
+
+
+def _png_chunks(data):
+    import struct
+    import zlib
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, out = 8, []
+    while pos < len(data):
+        n, kind = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        assert zlib.crc32(kind + body) == struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])[0], kind
+        out.append((kind, body))
+        pos += 12 + n
+    return out
+
+
+def test_mask_png_from_the_gpu_decodes_to_the_reference_picture():
+    """server.py:142-143 encodes with OpenCV, client.py:111-112 decodes with OpenCV: the decoded picture is the contract."""
+    import zlib
+    rng = np.random.default_rng(4)
+    yy, xx = np.mgrid[0:480, 0:640]
+    band = ((np.sin(xx / 90.0) * 60 + 200 < yy) & (yy < np.sin(xx / 90.0) * 60 + 330)).astype(np.uint8)
+    masks = [band, np.zeros((480, 640), np.uint8), np.ones((480, 640), np.uint8), (rng.random((480, 640)) > 0.5).astype(np.uint8),
+             (rng.random((480, 640)) > 0.999).astype(np.uint8), band * 7]                 # any non-zero value is "set"
+    pngs = service.encode_mask_png(torch.from_numpy(np.stack(masks)).cuda())
+    for m, data in zip(masks, pngs):
+        chunks = _png_chunks(data)                                                        # CRC-32 of every chunk
+        assert [k for k, _ in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+        raw = zlib.decompress(chunks[1][1])                                               # Adler-32 checked by zlib
+        assert len(raw) == 480 * 81
+        want = (m != 0).astype(np.uint8) * 255
+        assert np.array_equal(sp.decode_mask_png(data), want)
+        assert np.array_equal(sp.decode_mask_png(sp.encode_mask_png((m != 0).astype(np.uint8))), want)   # the reference's round trip
+    assert len(pngs[0]) < 4 * len(sp.encode_mask_png(band))                               # run-length coding is effective
+    print("png bytes:", [len(p) for p in pngs], "cv2:", [len(sp.encode_mask_png((m != 0).astype(np.uint8))) for m in masks])
+
+
+@pytest.mark.parametrize("H,W,B", [(1, 1, 1), (3, 5, 2), (97, 131, 3), (33, 2600, 2), (720, 1280, 2), (700, 9, 1)])
+def test_mask_png_other_shapes(H, W, B):
+    rng = np.random.default_rng(H * W)
+    m = (rng.random((B, H, W)) > 0.7).astype(np.uint8)
+    m[0, :, : W // 2] = 1
+    for _ in range(2):                                                                    # buffers are reused across calls
+        pngs = service.encode_mask_png(torch.from_numpy(m).cuda())
+        for i in range(B):
+            _png_chunks(pngs[i])
+            assert np.array_equal(sp.decode_mask_png(pngs[i]).reshape(H, W), m[i] * 255)

@@ -153,7 +153,7 @@ def server_shaped():
             print(json.dumps(out[-1]), file=sys.stderr)
         # N2: ten request threads (server.py:172) with host frames, results back on the host (mask included)
         n_threads, per_thread = 10, 64
-        with MicroBatcher(model, K, scale, max_batch=64, max_wait_ms=2.0, bgr=False) as mb:
+        with MicroBatcher(model, K, scale, max_batch=64, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True) as mb:
             def worker(t):
                 for j in range(per_thread):
                     f = frames[(t + j) % 8]
@@ -167,7 +167,7 @@ def server_shaped():
                     t.join()
                 dt = time.perf_counter() - t0
             out.append({"config": f"S2: MicroBatcher, 10 request threads x {per_thread} frames {W}x{H} from host memory, "
-                                  "mask + curvature back on the host (wall clock)",
+                                  "PNG mask (encoded on the GPU) + curvature back on the host (wall clock)",
                         "frames_per_s": n_threads * per_thread / dt, "batches": mb.batches_run, "frames": mb.frames_run,
                         "mean_batch": mb.frames_run / max(1, mb.batches_run),
                         "dispatcher_seconds": {k: round(v, 4) for k, v in mb._run.seconds.items()}, "wall_seconds_last_pass": dt})

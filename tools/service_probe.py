@@ -52,6 +52,18 @@ def main():
                               status=np.bincount(g.status.cpu().numpy(), minlength=6).tolist(),
                               knots=sorted(set(g.n_knots.cpu().numpy().tolist())),
                               coverage=round(float(r.mask_coverage_percent.mean()), 2))))
+        t_png = timed(lambda: service.encode_mask_png(r.final_mask, to_host=False))
+        import time
+        import cv2
+        fm = r.final_mask.cpu().numpy()
+        t0 = time.perf_counter()
+        for i in range(8):
+            cv2.imencode(".png", fm[i] * 255)
+        t_cv = (time.perf_counter() - t0) / 8 * 1e3
+        pngs = service.encode_mask_png(r.final_mask)
+        print(json.dumps(dict(png_gpu_ms_per_batch=round(t_png, 4), png_gpu_us_per_frame=round(t_png / B * 1e3, 2),
+                              png_cv2_ms_per_frame_one_core=round(t_cv, 3), png_bytes_mean=int(np.mean([len(p) for p in pngs])),
+                              cv2_bytes_first=len(cv2.imencode(".png", fm[0] * 255)[1]))))
         pre_bytes = B * (H * W * 3 + 3 * 256 * 256 * 4)
         post_bytes = B * (256 * 256 + H * W)
         print(json.dumps(dict(H=H, W=W, B=B, pre_ms=round(t_pre, 4), pre_GBs=round(pre_bytes / t_pre / 1e6, 1),
