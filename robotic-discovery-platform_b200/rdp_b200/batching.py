@@ -31,14 +31,37 @@ class FrameResult:
 
 @dataclass
 class _Request:
-    color: np.ndarray
-    depth: np.ndarray
+    color: object                        # the frame, or a _Staged slot when the runner stages on the request thread
+    depth: object
     future: Future
     key: tuple
 
 
-def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, want_mask: bool, want_png: bool) -> Callable:
-    """The default `run_batch`: stacked host frames -> list of FrameResult through the CUDA loop body."""
+class _Staged:
+    """A frame already copied into a pinned slot by its request thread."""
+    __slots__ = ("pool", "slot", "shape")
+
+    def __init__(self, pool, slot, shape):
+        self.pool, self.slot, self.shape = pool, slot, shape
+
+
+class _PinnedPool:
+    def __init__(self, n: int, cshape, dshape, depth_dtype):
+        import torch
+        self.color = torch.empty((n,) + tuple(cshape), dtype=torch.uint8).pin_memory()
+        self.depth = torch.empty((n,) + tuple(dshape), dtype=depth_dtype).pin_memory()
+        self.color_np, self.depth_np = self.color.numpy(), self.depth.numpy()
+        self.free: "queue.Queue[int]" = queue.Queue()
+        for i in range(n):
+            self.free.put(i)
+
+
+def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, want_mask: bool, want_png: bool,
+                max_batch: int) -> Callable:
+    """The default `run_batch`: staged host frames -> list of FrameResult through the CUDA loop body.
+
+    `run.stage(color, depth)` is called by the request thread itself: it copies the frame into a pinned slot (the
+    copy releases the GIL, so ten request threads stage in parallel and the dispatcher only issues the H2D copies)."""
     import torch
 
     from pkg.geometry_utils import _to_result
@@ -46,39 +69,52 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, wa
     from . import service
 
     dev = torch.device(device)
-    staging = {}
+    pools, pools_lock = {}, threading.Lock()
 
-    def run(colors: List[np.ndarray], depths: List[np.ndarray]) -> List[FrameResult]:
+    def stage(color: np.ndarray, depth: np.ndarray) -> _Staged:
+        key = (color.shape, depth.shape, depth.dtype.str)
+        with pools_lock:
+            pool = pools.get(key)
+            if pool is None:  # bounded: one pool per camera format; a full pool makes request threads wait their turn
+                pool = pools[key] = _PinnedPool(2 * max_batch + 16, color.shape, depth.shape, torch.from_numpy(depth[:0]).dtype)
+        slot = pool.free.get()
+        pool.color_np[slot][...] = color
+        pool.depth_np[slot][...] = depth
+        return _Staged(pool, slot, color.shape)
+
+    def run(colors: List[_Staged], depths) -> List[FrameResult]:
         t0 = time.perf_counter()
-        B = len(colors)
-        key = (B, colors[0].shape, depths[0].shape, depths[0].dtype)
-        if key not in staging:  # pinned staging buffers per batch shape (bounded: B <= max_batch, few camera formats)
-            staging[key] = (torch.empty((B,) + colors[0].shape, dtype=torch.uint8).pin_memory(),
-                            torch.empty((B,) + depths[0].shape, dtype=torch.from_numpy(depths[0][:0]).dtype).pin_memory())
-        hc, hd = staging[key]
-        for i in range(B):
-            hc[i].numpy()[...] = colors[i]
-            hd[i].numpy()[...] = depths[i]
-        t1 = time.perf_counter()
-        with torch.cuda.device(dev):
-            r = service.analyze_frames(model, hc.to(dev, non_blocking=True), hd.to(dev, non_blocking=True), intrinsics,
-                                       depth_scale, size=size, bgr=bgr)
-            status = r.curvature.status.cpu().numpy()
-            mean, mx = r.curvature.mean_curvature.cpu().numpy(), r.curvature.max_curvature.cpu().numpy()
-            pts = r.curvature.spline_points.cpu().numpy()
-            cov = r.mask_coverage_percent.cpu().numpy()
-            pngs = service.encode_mask_png(r.final_mask) if want_png else [None] * B   # a few KB per frame instead of H*W
-            masks = r.final_mask.cpu().numpy() if want_mask else [None] * B
+        B, pool = len(colors), colors[0].pool
+        try:
+            with torch.cuda.device(dev):
+                dc = torch.empty((B,) + tuple(pool.color.shape[1:]), dtype=torch.uint8, device=dev)
+                dd = torch.empty((B,) + tuple(pool.depth.shape[1:]), dtype=pool.depth.dtype, device=dev)
+                for i, c in enumerate(colors):
+                    dc[i].copy_(pool.color[c.slot], non_blocking=True)
+                    dd[i].copy_(pool.depth[c.slot], non_blocking=True)
+                t1 = time.perf_counter()
+                r = service.analyze_frames(model, dc, dd, intrinsics, depth_scale, size=size, bgr=bgr)
+                status = r.curvature.status.cpu().numpy()       # (synchronises: the H2D copies are done from here on)
+                mean, mx = r.curvature.mean_curvature.cpu().numpy(), r.curvature.max_curvature.cpu().numpy()
+                pts = r.curvature.spline_points.cpu().numpy()
+                cov = r.mask_coverage_percent.cpu().numpy()
+                pngs = service.encode_mask_png(r.final_mask) if want_png else [None] * B   # a few KB per frame, not H*W
+                masks = r.final_mask.cpu().numpy() if want_mask else [None] * B
+        finally:
+            torch.cuda.synchronize(dev)
+            for c in colors:
+                pool.free.put(c.slot)
         t2 = time.perf_counter()
         out = [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B, pngs[i])
                for i in range(B)]
         t3 = time.perf_counter()
-        run.seconds["stage"] += t1 - t0
+        run.seconds["issue_h2d"] += t1 - t0
         run.seconds["gpu_and_copies"] += t2 - t1
         run.seconds["unpack"] += t3 - t2
         return out
 
-    run.seconds = {"stage": 0.0, "gpu_and_copies": 0.0, "unpack": 0.0}   # where the dispatcher's time went (diagnostics)
+    run.stage = stage
+    run.seconds = {"issue_h2d": 0.0, "gpu_and_copies": 0.0, "unpack": 0.0}   # where the dispatcher's time went (diagnostics)
     return run
 
 
@@ -92,7 +128,7 @@ class MicroBatcher:
             raise ValueError("max_batch must be >= 1")
         self.max_batch, self.max_wait = int(max_batch), float(max_wait_ms) / 1e3
         self._run = run_batch if run_batch is not None else _gpu_runner(model, intrinsics, depth_scale, bgr, size, device,
-                                                                             want_mask, want_png)
+                                                                             want_mask, want_png, self.max_batch)
         self._q: "queue.Queue[Optional[_Request]]" = queue.Queue()
         self._closed = False
         self.batches_run, self.frames_run = 0, 0
@@ -107,8 +143,11 @@ class MicroBatcher:
         if color.ndim != 3 or color.dtype != np.uint8 or depth.shape != color.shape[:2]:
             raise ValueError(f"expected (H,W,C) uint8 colour and (H,W) depth, got {color.shape} {color.dtype} / {depth.shape}")
         fut: Future = Future()
-        # frames of different camera formats cannot share a batch
-        self._q.put(_Request(color, depth, fut, (color.shape, depth.dtype.str)))
+        key = (color.shape, depth.dtype.str)          # frames of different camera formats cannot share a batch
+        stage = getattr(self._run, "stage", None)
+        if stage is not None:                         # copy into pinned memory here, on the request thread
+            color, depth = stage(color, depth), None
+        self._q.put(_Request(color, depth, fut, key))
         return fut
 
     def analyze(self, color_image: np.ndarray, depth_image: np.ndarray, timeout: Optional[float] = None) -> FrameResult:

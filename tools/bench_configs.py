@@ -153,7 +153,8 @@ def server_shaped():
             print(json.dumps(out[-1]), file=sys.stderr)
         # N2: ten request threads (server.py:172) with host frames, results back on the host (mask included)
         n_threads, per_thread = 10, 64
-        with MicroBatcher(model, K, scale, max_batch=64, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True) as mb:
+        # max_batch = the servicer's worker count: a batch holding every outstanding request goes at once, without max_wait
+        with MicroBatcher(model, K, scale, max_batch=n_threads, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True) as mb:
             def worker(t):
                 for j in range(per_thread):
                     f = frames[(t + j) % 8]
