@@ -922,7 +922,9 @@ __device__ __forceinline__ void window_rotate_in(double (&Rw)[5][5], double (&zw
 // final once interval i is done.  Inputs are prefetched into L1 a few intervals ahead: they were written by other
 // threads (or, for the back substitution, by this one: stores do not allocate in L1).
 // (No __restrict__/const-cache loads: every input was written earlier in this kernel.)
-template <bool PEN>
+// DIAG_ONLY: only the triangle is wanted (FITPACK's first smoothing parameter needs sum(diag R)): the right-hand sides
+// are not rotated and nothing is solved.
+template <bool PEN, bool DIAG_ONLY = false>
 __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
                                               double* R, double* z, double* c) {
   double Rw[5][5], zw[5][3];
@@ -1003,7 +1005,8 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
 #pragma unroll
           for (int e = st + 1; e <= q; ++e) rota(cs[q], sn[q], h[q][e], Rw[4 - q + st][e - st]);
 #pragma unroll
-          for (int d = 0; d < 3; ++d) rota(cs[q], sn[q], x[q][d], zw[4 - q + st][d]);
+          for (int d = 0; d < 3; ++d)
+            if (!DIAG_ONLY) rota(cs[q], sn[q], x[q][d], zw[4 - q + st][d]);
         }
     }
   };
@@ -1049,6 +1052,7 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
 #pragma unroll
     for (int d = 0; d < 3; ++d) z[(size_t)(nrint - 1 + r) * 3 + d] = zw[r][d];
   }
+  if (DIAG_ONLY) return;
   // fpback: c_i = (z_i - sum_e R[i][e] c_{i+e}) / R[i][0]; the newest coefficient enters last (shortest chain).
   // Entries of R past the last column were never touched and are zero.
   double c1[3] = {0.0, 0.0, 0.0}, c2[3] = {0.0, 0.0, 0.0}, c3[3] = {0.0, 0.0, 0.0}, c4[3] = {0.0, 0.0, 0.0};
@@ -1754,7 +1758,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       }
     }
     if (!band_R_valid) {  // FITPACK's first p needs the diagonal of the banded triangle of the last least-squares fit
-      if (tid == 0) band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
+      if (tid == 0) band_merge_solve<false, true>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
       __syncthreads();
     }
     lap(tm_merge);
