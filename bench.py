@@ -388,6 +388,8 @@ def run_b200(args):
                          "survey_bytes_per_frame": geometry_bytes_per_frame(P, n_points)},
         "launch_ms": {n: round(float(v), 4) for n, v in zip(names, unet_ms)},
     }
+    if rank == 0 and world == 1:
+        line["server_shaped"] = time_server_shaped(model, dev_rgb[0], dev_depth[0], K, scale, B, H, W)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = time_cpu_reference(H, W, budget_s=args.cpu_budget)
     elif rank == 0:
@@ -401,6 +403,34 @@ def run_b200(args):
 
 
 _REAL_STDOUT = None
+
+
+def time_server_shaped(model, rgb, depth, K, scale, B, H, W, reps=5):
+    """Secondary figure (not the headline metric): the reference server's own loop body on the same frames - resize to
+    256x256, U-Net, nearest up-size, curvature at camera resolution, PNG of the mask (`server.py:120-143`)."""
+    import torch
+
+    from rdp_b200 import service
+
+    def step():
+        r = service.analyze_frames(model, rgb, depth, K, scale)
+        service.encode_mask_png(r.final_mask, to_host=False)
+        return r
+
+    for _ in range(3):
+        r = step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        r = step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / reps
+    return {"value": B / ms * 1e3, "unit": "frames/s", "ms_per_step": ms, "frames_ok": int((r.curvature.status == 0).sum()),
+            "knots_min": int(r.curvature.n_knots.min()), "knots_max": int(r.curvature.n_knots.max()),
+            "workload": f"{B} frames {W}x{H}: rdp_pre_resize -> UNet 256x256 -> rdp_post_mask_nearest -> rdp_geom_curvature at "
+                        f"{W}x{H} -> rdp_post_mask_png, device-resident inputs"}
 
 
 def emit(line: dict) -> None:
