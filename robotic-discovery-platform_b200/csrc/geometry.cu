@@ -796,7 +796,8 @@ __global__ void __launch_bounds__(FIT_THREADS) k_fit(const Params p) {
 // triangles, interleaved by last column with the smoothing-penalty rows when there are any, into the band - in
 // that order no fill-in ever runs past a row's own last column, so the merge is O(n) instead of FITPACK's O(n^2)
 // smoothing step.  Knot selection (fpknot) works on (residual, point-count, begin) nodes and a flag per data point.
-constexpr int KN_THREADS = 256;
+constexpr int KN_THREADS = 256;  // most threads per CTA (array sizes); the kernel runs with blockDim.x = 256 or 128
+#define KN_NT ((int)blockDim.x)   // threads of this launch: 128 lets two CTAs share an SM when there are more frames than SMs
 constexpr int KN_MAXIT = 20;
 
 // FITPACK's bracket search multiplies and divides p by 0.04 and then compares with the bracket end it started from:
@@ -1121,7 +1122,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
   while ((4 << L) < nrint) ++L;  // every interval index below 4 * 2^L, so each interval has its group; 2^L + 1 >= NB follows
   const int ng0 = 1 << L, nbp = ng0 + 1;
   // ---- level 0: groups from the interval triangles, the penalty rows and the padding ----
-  for (int g = tid; g < ng0; g += KN_THREADS) {
+  for (int g = tid; g < ng0; g += KN_NT) {
     double R[36], Z[8][3];
 #pragma unroll
     for (int q = 0; q < 36; ++q) R[q] = 0.0;
@@ -1172,7 +1173,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
   int ngin = ng0;
   for (int lvl = 0; lvl < L; ++lvl) {
     const int ngout = ngin >> 1;
-    for (int j = tid; j < ngout; j += KN_THREADS) {
+    for (int j = tid; j < ngout; j += KN_NT) {
       double P[4][12], PZ[4][3];
 #pragma unroll
       for (int a = 0; a < 4; ++a) {
@@ -1207,9 +1208,9 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
           }
         }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) cw.scr[(size_t)(k * 11 + e) * KN_THREADS + tid] = h[4 + e];
+        for (int e = 0; e < 8; ++e) cw.scr[(size_t)(k * 11 + e) * KN_NT + tid] = h[4 + e];
 #pragma unroll
-        for (int d = 0; d < 3; ++d) cw.scr[(size_t)(k * 11 + 8 + d) * KN_THREADS + tid] = x[d];
+        for (int d = 0; d < 3; ++d) cw.scr[(size_t)(k * 11 + 8 + d) * KN_NT + tid] = x[d];
       }
       const int b = (2 * j + 1) << lvl;
       {
@@ -1232,9 +1233,9 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
       for (int k = 0; k < 16; ++k) {
         double h[8], x[3];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) h[e] = cw.scr[(size_t)(k * 11 + e) * KN_THREADS + tid];
+        for (int e = 0; e < 8; ++e) h[e] = cw.scr[(size_t)(k * 11 + e) * KN_NT + tid];
 #pragma unroll
-        for (int d = 0; d < 3; ++d) x[d] = cw.scr[(size_t)(k * 11 + 8 + d) * KN_THREADS + tid];
+        for (int d = 0; d < 3; ++d) x[d] = cw.scr[(size_t)(k * 11 + 8 + d) * KN_NT + tid];
         rotate_in_tri8(R, Z, h, x);
       }
 #pragma unroll
@@ -1272,7 +1273,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
   // ---- back substitution down the levels ----
   for (int lvl = L - 1; lvl >= 0; --lvl) {
     const int cnt = 1 << (L - lvl - 1);
-    for (int j = tid; j < cnt; j += KN_THREADS) {
+    for (int j = tid; j < cnt; j += KN_NT) {
       const int b = (2 * j + 1) << lvl, bl = b - (1 << lvl), br = b + (1 << lvl);
       double side[8][3], cb[4][3];
 #pragma unroll
@@ -1304,7 +1305,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
     }
     __syncthreads();
   }
-  for (int i = tid; i < nk1 * 3; i += KN_THREADS) c[i] = cp[i];
+  for (int i = tid; i < nk1 * 3; i += KN_NT) c[i] = cp[i];
   __syncthreads();
 }
 
@@ -1314,7 +1315,7 @@ __device__ __forceinline__ double block_sum1(double v, double* s_red) {
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
   __syncthreads();
   double a = 0.0;
-  for (int w = 0; w < KN_THREADS / 32; ++w) a += s_red[w];
+  for (int w = 0; w < KN_NT / 32; ++w) a += s_red[w];
   return a;
 }
 
@@ -1363,7 +1364,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   {  // normalise the chord-length parameter in place (parcur): u[0] = 0, u[m-1] = 1
     const double total = U[m - 1];
     __syncthreads();
-    for (int i = tid; i < m; i += KN_THREADS) {
+    for (int i = tid; i < m; i += KN_NT) {
       U[i] = i == 0 ? 0.0 : (i == m - 1 ? 1.0 : U[i] / total);
       w.flag[i] = 0;
     }
@@ -1393,7 +1394,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     // (1) task triangles, one thread per task (at most KN_CH consecutive points of one interval).  They depend on the
     // knots only, not on the smoothing parameter: the root find reuses those of the last least-squares fit.
     if (!tri_valid) {
-    for (int k = tid; k < ntasks; k += KN_THREADS) {
+    for (int k = tid; k < ntasks; k += KN_NT) {
       double T[4][4] = {}, Z[4][3] = {};
       const int p0 = w.tbeg[k], p1 = k + 1 < ntasks ? w.tbeg[k + 1] : m;
       for (int it = p0; it < p1; ++it) {
@@ -1425,7 +1426,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
     // (1b) the triangles of one interval share their four columns: pairwise tree reduction down to one per interval
     for (int r = 1; r < max_tasks; r <<= 1) {
-      for (int k = tid; k < ntasks; k += KN_THREADS) {
+      for (int k = tid; k < ntasks; k += KN_NT) {
         const int i = w.tint[k], j = k - w.tfirst[i];
         if ((j & (2 * r - 1)) != 0 || k + r >= w.tfirst[i + 1]) continue;
         double* a = w.tri + (size_t)k * 22;
@@ -1494,7 +1495,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     lap(tm_merge);
     // (3) residuals
     double part = 0.0;
-    for (int it = tid; it < m; it += KN_THREADS) {
+    for (int it = tid; it < m; it += KN_NT) {
       const int l0 = w.lidx[it] - 3;
       double tt = 0.0;
 #pragma unroll
@@ -1518,7 +1519,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     // ---- knot vector, interval of every point and interval starts from the flags (block scan over the points) ----
     tri_valid = false;
     int carry = 0, carry2 = 0;
-    for (int i0 = 0; i0 < m; i0 += KN_THREADS) {
+    for (int i0 = 0; i0 < m; i0 += KN_NT) {
       const int i = i0 + tid;
       const int f = (i < m) ? w.flag[i] : 0;
       const int cut = (i < m) && (f || (i % KN_CH) == 0);  // a triangle task starts here
@@ -1542,7 +1543,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
         woff2 += s_scan2[k];
       }
       int tot = 0, tot2 = 0;
-      for (int k = 0; k < KN_THREADS / 32; ++k) {
+      for (int k = 0; k < KN_NT / 32; ++k) {
         tot += s_scan[k];
         tot2 += s_scan2[k];
       }
@@ -1570,7 +1571,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       s_i[1] = 1;
     }
     __syncthreads();
-    for (int i = tid; i < carry + 1; i += KN_THREADS) {  // most tasks any interval has (block-uniform loop bound below)
+    for (int i = tid; i < carry + 1; i += KN_NT) {  // most tasks any interval has (block-uniform loop bound below)
       const int c = w.tfirst[i + 1] - w.tfirst[i];
       if (c > 1) atomicMax(&s_i[1], c);
     }
@@ -1587,7 +1588,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
     // the last data point (u = 1) belongs to the last interval (FITPACK: l stops at nk1)
     if (tid == 0) w.lidx[m - 1] = nk1 - 1;
-    for (int it = tid; it < m; it += KN_THREADS) {
+    for (int it = tid; it < m; it += KN_NT) {
       if (it == m - 1) continue;
       double h[4];
       bspl3(w.t, U[it], w.lidx[it], h);
@@ -1631,7 +1632,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     fpold = fp;
     ++n_iter;
     // ---- residual per interval; the point sitting on a knot is shared half/half by its two intervals ----
-    for (int i = tid; i < nrint; i += KN_THREADS) {
+    for (int i = tid; i < nrint; i += KN_NT) {
       const int p0 = w.ibegin[i], p1 = i + 1 < nrint ? w.ibegin[i + 1] : m;
       double a = i == 0 ? w.term[p0] : 0.5 * w.term[p0];
       for (int it = p0 + 1; it < p1; ++it) a += w.term[it];
@@ -1654,7 +1655,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       my_beg = 0x7fffffff;
       my_nrd = 0;
       my_idx = -1;
-      for (int i = tid; i < nn; i += KN_THREADS) {
+      for (int i = tid; i < nn; i += KN_NT) {
         const int nr = w.nrd[i];
         if (nr == 0) continue;
         const double v = w.fpint[i];
@@ -1696,7 +1697,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       br = 0;
       bi = -1;
 #pragma unroll
-      for (int k = 0; k < KN_THREADS / 32; ++k) {
+      for (int k = 0; k < KN_NT / 32; ++k) {
         const unsigned long long ok = s_knot_key[buf][k];
         const int4 om = s_knot_meta[buf][k];
         if (ok > bk || (ok == bk && om.x < bb)) {
@@ -1710,7 +1711,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       const double fpmax = __longlong_as_double((long long)bk);
       const int maxpt = br, maxbeg = bb;
       const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
-      const bool own_old = (bi % KN_THREADS) == tid, own_new = (nn % KN_THREADS) == tid;
+      const bool own_old = (bi % KN_NT) == tid, own_new = (nn % KN_NT) == tid;
       if (own_old) {
         w.flag[nrx - 1] = 1;
         w.nrd[bi] = ihalf - 1;
@@ -1726,7 +1727,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       ++nn;
       if (stop == 2) {  // n == nmax: knots as for interpolation, t[4+i] = u[2+i]
         __syncthreads();  // the flag set above by another thread must not land after the rewrite below
-        for (int i = tid; i < m; i += KN_THREADS) w.flag[i] = (i >= 2 && i <= m - 3) ? 1 : 0;
+        for (int i = tid; i < m; i += KN_NT) w.flag[i] = (i >= 2 && i <= m - 3) ? 1 : 0;
         break;
       }
       if (stop == 3) break;
@@ -1738,7 +1739,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
 
   if (smoothing) {
     // ---- Part 2: find p with F(p) = s, F = residual of the spline minimising residual + (1/p) * derivative jumps ----
-    for (int i = tid; i < nrint - 1; i += KN_THREADS) {  // fpdisc
+    for (int i = tid; i < nrint - 1; i += KN_NT) {  // fpdisc
       const double fac = (double)nrint / (w.t[nk1] - w.t[3]);
       const int l = i + 5;  // 1-based knot index k2 + i
       double h[8];
@@ -1763,7 +1764,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     }
     lap(tm_merge);
     double sumdiag = 0.0;
-    for (int i = tid; i < nk1; i += KN_THREADS) sumdiag += w.R[i * 5];
+    for (int i = tid; i < nk1; i += KN_NT) sumdiag += w.R[i * 5];
     sumdiag = block_sum1(sumdiag, s_red);
     double p1 = 0.0, f1 = fp0 - s, p3 = -1.0, f3 = fpms, pp = (double)nk1 / sumdiag;
     bool ich1 = false, ich3 = false;
@@ -1858,7 +1859,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   if (lane == 0) s_best[warp] = kmax_key;
   __syncthreads();
   if (tid == 0) {
-    for (int k = 1; k < KN_THREADS / 32; ++k) kmax_key = s_best[k] > kmax_key ? s_best[k] : kmax_key;
+    for (int k = 1; k < KN_NT / 32; ++k) kmax_key = s_best[k] > kmax_key ? s_best[k] : kmax_key;
     p.out.mean_curvature[b] = kcnt > 0.0 ? ksum / kcnt : 0.0;
     p.out.max_curvature[b] = kcnt > 0.0 ? key_to_double(kmax_key) : 0.0;
     p.out.status[b] = RDP_FRAME_OK;
@@ -2000,7 +2001,15 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
   mark();
   static const int knots_debug = getenv("RDP_DEBUG_KNOTS") ? atoi(getenv("RDP_DEBUG_KNOTS")) : 0;  // phase cycle counts
-  k_fit_knots<<<B, KN_THREADS, 0, stream>>>(p, kn, pl.ecap + 8, knots_debug);  // exits at once for frames that need no extra knots
+  // One CTA per frame and 255 registers per thread: 256 threads fill an SM's register file.  With more frames than SMs,
+  // 128 threads per CTA put two frames on an SM; the parallel phases take longer, the serial chains (most of the time)
+  // do not, so the batch finishes in about one CTA lifetime instead of two.
+  int n_sm = 148, dev_id = 0;
+  RDP_CUDA_TRY(cudaGetDevice(&dev_id));
+  RDP_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev_id));
+  static const int knots_threads_env = getenv("RDP_KNOTS_THREADS") ? atoi(getenv("RDP_KNOTS_THREADS")) : 0;  // 128 or 256 (A/B)
+  const int kn_threads = knots_threads_env == 128 || knots_threads_env == 256 ? knots_threads_env : (B > n_sm ? 128 : KN_THREADS);
+  k_fit_knots<<<B, kn_threads, 0, stream>>>(p, kn, pl.ecap + 8, knots_debug);  // exits at once for frames that need no extra knots
   mark();
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
