@@ -35,7 +35,7 @@ def _to_result(status: int, mean: float, mx: float, pts: np.ndarray) -> Curvatur
     from rdp_b200 import _lib
     if status == _lib.FRAME_OK:
         return CurvatureResult(mean_curvature=float(mean), max_curvature=float(mx),
-                               spline_points=[Point(x=float(p[0]), y=float(p[1]), z=float(p[2])) for p in pts])
+                               spline_points=[Point(x, y, z) for x, y, z in np.asarray(pts, dtype=np.float64).tolist()])
     return CurvatureResult()
 
 

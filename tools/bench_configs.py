@@ -152,7 +152,7 @@ def server_shaped():
                         "geometry_launch_ms": {k: round(v, 4) for k, v in zip(geometry.LAUNCH_NAMES, lm)}})
             print(json.dumps(out[-1]), file=sys.stderr)
         # N2: ten request threads (server.py:172) with host frames, results back on the host (mask included)
-        n_threads, per_thread = 10, 64
+        n_threads, per_thread = int(os.environ.get("RDP_S2_THREADS", 10)), 64   # 10 = the servicer's max_workers
         # max_batch = the servicer's worker count: a batch holding every outstanding request goes at once, without max_wait
         with MicroBatcher(model, K, scale, max_batch=n_threads, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True) as mb:
             def worker(t):
@@ -167,7 +167,7 @@ def server_shaped():
                 for t in threads:
                     t.join()
                 dt = time.perf_counter() - t0
-            out.append({"config": f"S2: MicroBatcher, 10 request threads x {per_thread} frames {W}x{H} from host memory, "
+            out.append({"config": f"S2: MicroBatcher, {n_threads} request threads x {per_thread} frames {W}x{H} from host memory, "
                                   "PNG mask (encoded on the GPU) + curvature back on the host (wall clock)",
                         "frames_per_s": n_threads * per_thread / dt, "batches": mb.batches_run, "frames": mb.frames_run,
                         "mean_batch": mb.frames_run / max(1, mb.batches_run),
