@@ -70,6 +70,7 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, wa
 
     dev = torch.device(device)
     pools, pools_lock = {}, threading.Lock()
+    lane = threading.local()      # every dispatcher lane (thread) issues its batches on a stream of its own
 
     def stage(color: np.ndarray, depth: np.ndarray) -> _Staged:
         key = (color.shape, depth.shape, depth.dtype.str)
@@ -85,8 +86,11 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, wa
     def run(colors: List[_Staged], depths) -> List[FrameResult]:
         t0 = time.perf_counter()
         B, pool = len(colors), colors[0].pool
-        try:
+        if getattr(lane, "stream", None) is None:
             with torch.cuda.device(dev):
+                lane.stream = torch.cuda.Stream()
+        try:
+            with torch.cuda.device(dev), torch.cuda.stream(lane.stream):
                 dc = torch.empty((B,) + tuple(pool.color.shape[1:]), dtype=torch.uint8, device=dev)
                 dd = torch.empty((B,) + tuple(pool.depth.shape[1:]), dtype=pool.depth.dtype, device=dev)
                 for i, c in enumerate(colors):
@@ -101,16 +105,17 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, wa
                 pngs = service.encode_mask_png(r.final_mask) if want_png else [None] * B   # a few KB per frame, not H*W
                 masks = r.final_mask.cpu().numpy() if want_mask else [None] * B
         finally:
-            torch.cuda.synchronize(dev)
+            lane.stream.synchronize()
             for c in colors:
                 pool.free.put(c.slot)
         t2 = time.perf_counter()
         out = [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B, pngs[i])
                for i in range(B)]
         t3 = time.perf_counter()
-        run.seconds["issue_h2d"] += t1 - t0
-        run.seconds["gpu_and_copies"] += t2 - t1
-        run.seconds["unpack"] += t3 - t2
+        with pools_lock:
+            run.seconds["issue_h2d"] += t1 - t0
+            run.seconds["gpu_and_copies"] += t2 - t1
+            run.seconds["unpack"] += t3 - t2
         return out
 
     run.stage = stage
@@ -123,17 +128,21 @@ class MicroBatcher:
 
     def __init__(self, model=None, intrinsics=None, depth_scale=None, *, max_batch: int = 64, max_wait_ms: float = 2.0,
                  bgr: bool = True, size: int = 256, device="cuda", want_mask: bool = True, want_png: bool = False,
-                 run_batch: Optional[Callable] = None):
-        if max_batch < 1:
-            raise ValueError("max_batch must be >= 1")
+                 lanes: int = 1, run_batch: Optional[Callable] = None):
+        """`lanes` dispatcher threads form and run batches independently (each on its own CUDA stream): with many
+        concurrent requests a second lane overlaps one batch's latency-bound spline fits with the next batch's U-Net."""
+        if max_batch < 1 or lanes < 1:
+            raise ValueError("max_batch and lanes must be >= 1")
         self.max_batch, self.max_wait = int(max_batch), float(max_wait_ms) / 1e3
         self._run = run_batch if run_batch is not None else _gpu_runner(model, intrinsics, depth_scale, bgr, size, device,
                                                                              want_mask, want_png, self.max_batch)
         self._q: "queue.Queue[Optional[_Request]]" = queue.Queue()
         self._closed = False
         self.batches_run, self.frames_run = 0, 0
-        self._thread = threading.Thread(target=self._loop, name="rdp-microbatcher", daemon=True)
-        self._thread.start()
+        self._stats_lock = threading.Lock()
+        self._threads = [threading.Thread(target=self._loop, name=f"rdp-microbatcher-{i}", daemon=True) for i in range(lanes)]
+        for t in self._threads:
+            t.start()
 
     # ---- request side ------------------------------------------------------------------------------------
     def submit(self, color_image: np.ndarray, depth_image: np.ndarray) -> Future:
@@ -156,8 +165,10 @@ class MicroBatcher:
     def close(self) -> None:
         if not self._closed:
             self._closed = True
-            self._q.put(None)
-            self._thread.join()
+            for _ in self._threads:        # one stop token per lane; what was accepted before it is still served
+                self._q.put(None)
+            for t in self._threads:
+                t.join()
 
     def __enter__(self):
         return self
@@ -201,7 +212,8 @@ class MicroBatcher:
             for r in batch:
                 r.future.set_exception(e)
             return
-        self.batches_run += 1
-        self.frames_run += len(batch)
+        with self._stats_lock:
+            self.batches_run += 1
+            self.frames_run += len(batch)
         for r, res in zip(batch, results):
             r.future.set_result(res)

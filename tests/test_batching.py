@@ -103,3 +103,36 @@ def test_bad_frames_are_refused_at_submit_and_close_is_final():
     with pytest.raises(RuntimeError):
         mb.submit(*_frame(1))
     mb.close()
+
+
+def test_two_lanes_serve_everything_and_overlap_batches():
+    log, active, peak = [], [0], [0]
+    lock = threading.Lock()
+
+    def run(colors, depths):
+        with lock:
+            active[0] += 1
+            peak[0] = max(peak[0], active[0])
+            log.append(len(colors))
+        time.sleep(0.03)
+        with lock:
+            active[0] -= 1
+        return [FrameResult(None, np.full(c.shape[:2], c[0, 0, 0], np.uint8), float(d[0, 0]), len(colors)) for c, d in zip(colors, depths)]
+
+    with MicroBatcher(run_batch=run, max_batch=4, max_wait_ms=5, lanes=2) as mb:
+        out = {}
+
+        def worker(tag):
+            out[tag] = int(mb.analyze(*_frame(tag)).final_mask[0, 0])
+
+        threads = [threading.Thread(target=worker, args=(t,)) for t in range(1, 41)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(10)
+        pending = [mb.submit(*_frame(t)) for t in range(50, 56)]
+    assert out == {t: t for t in range(1, 41)}
+    assert [int(f.result(1).final_mask[0, 0]) for f in pending] == list(range(50, 56))      # close() drained both lanes
+    assert sum(log) == 46 and max(log) <= 4 and peak[0] == 2                                  # two batches in flight
+    with pytest.raises(ValueError):
+        MicroBatcher(run_batch=run, lanes=0)

@@ -154,7 +154,9 @@ def server_shaped():
         # N2: ten request threads (server.py:172) with host frames, results back on the host (mask included)
         n_threads, per_thread = int(os.environ.get("RDP_S2_THREADS", 10)), 64   # 10 = the servicer's max_workers
         # max_batch = the servicer's worker count: a batch holding every outstanding request goes at once, without max_wait
-        with MicroBatcher(model, K, scale, max_batch=n_threads, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True) as mb:
+        lanes = int(os.environ.get("RDP_S2_LANES", 1))
+        with MicroBatcher(model, K, scale, max_batch=n_threads, max_wait_ms=2.0, bgr=False, want_mask=False, want_png=True,
+                          lanes=lanes) as mb:
             def worker(t):
                 for j in range(per_thread):
                     f = frames[(t + j) % 8]
@@ -169,7 +171,7 @@ def server_shaped():
                 dt = time.perf_counter() - t0
             out.append({"config": f"S2: MicroBatcher, {n_threads} request threads x {per_thread} frames {W}x{H} from host memory, "
                                   "PNG mask (encoded on the GPU) + curvature back on the host (wall clock)",
-                        "frames_per_s": n_threads * per_thread / dt, "batches": mb.batches_run, "frames": mb.frames_run,
+                        "frames_per_s": n_threads * per_thread / dt, "lanes": lanes, "batches": mb.batches_run, "frames": mb.frames_run,
                         "mean_batch": mb.frames_run / max(1, mb.batches_run),
                         "dispatcher_seconds": {k: round(v, 4) for k, v in mb._run.seconds.items()}, "wall_seconds_last_pass": dt})
             print(json.dumps(out[-1]), file=sys.stderr)
