@@ -197,3 +197,28 @@ def test_mask_png_other_shapes(H, W, B):
         for i in range(B):
             _png_chunks(pngs[i])
             assert np.array_equal(sp.decode_mask_png(pngs[i]).reshape(H, W), m[i] * 255)
+
+
+def test_png_entry_point_refuses_bad_buffers():
+    import ctypes as C
+    lib = _lib.load()
+    B, H, W = 1, 16, 24
+    max_png, ws_bytes = C.c_size_t(), C.c_size_t()
+    _lib.check(lib.rdp_post_mask_png_sizes(B, H, W, C.byref(max_png), C.byref(ws_bytes)), "sizes")
+    assert max_png.value >= 43 + 20 and ws_bytes.value > 0
+    m = torch.zeros((B, H, W), dtype=torch.uint8, device="cuda")
+    png = torch.empty((B, max_png.value + 8), dtype=torch.uint8, device="cuda")
+    n = torch.empty(B, dtype=torch.int32, device="cuda")
+    ws = torch.empty(ws_bytes.value, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    ok_stride = (max_png.value + 3) // 4 * 4
+    assert lib.rdp_post_mask_png(m.data_ptr(), B, H, W, png.data_ptr(), 32, n.data_ptr(), ws.data_ptr(), ws.numel(), stream) == -1
+    assert b"png_stride" in lib.rdp_last_error()
+    assert lib.rdp_post_mask_png(m.data_ptr(), B, H, W, png.data_ptr(), ok_stride, n.data_ptr(), ws.data_ptr(), 16, stream) == -4
+    assert lib.rdp_post_mask_png(m.data_ptr(), B, H, W, None, ok_stride, n.data_ptr(), ws.data_ptr(), ws.numel(), stream) == -1
+    assert lib.rdp_post_mask_png_sizes(0, H, W, C.byref(max_png), C.byref(ws_bytes)) == -1
+    assert lib.rdp_pre_resize(m.data_ptr(), 1, 4, 4, 9, 2, 2, 0, png.data_ptr(), stream) == -2           # 9 channels
+    assert lib.rdp_post_mask_nearest(None, 1, 4, 4, 8, 8, png.data_ptr(), None, stream) == -1
+    assert lib.rdp_post_mask_png(m.data_ptr(), B, H, W, png.data_ptr(), ok_stride, n.data_ptr(), ws.data_ptr(), ws.numel(), stream) == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(sp.decode_mask_png(png[0, :int(n[0])].cpu().numpy().tobytes()), np.zeros((H, W), np.uint8))
