@@ -180,3 +180,25 @@ def test_full_size_batch_properties():
     assert torch.equal(valid, r.n_points)
     for i in range(4):
         _check_frame(r, i, frames[i])
+
+
+def test_more_knot_frames_than_sms_use_the_small_cta_and_agree(manifest):
+    """With more frames than SMs k_fit_knots runs 128-thread CTAs (two frames per SM): same knots, same curvature."""
+    from rdp_b200 import geometry
+    names = ["geom_f32_480x640_f552_knots136", "geom_f32_480x640_f555_knots167", "geom_f32_480x640_f552_knots12"]
+    metas = [manifest["cases"][n] for n in names]
+    frames = [synth.make_frame(v["seed"], v["H"], v["W"], v["fill"], v["depth"]) for v in metas]
+    n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+    B = n_sm + 12
+    masks = torch.from_numpy(np.stack([frames[i % 3]["mask_gt"] for i in range(B)])).cuda()
+    depth = torch.from_numpy(np.stack([frames[i % 3]["depth"] for i in range(B)])).cuda()
+    r = geometry.curvature_batch(masks, depth, frames[0]["K"], frames[0]["depth_scale"])
+    one = [geometry.curvature_batch(masks[i:i + 1], depth[i:i + 1], frames[0]["K"], frames[0]["depth_scale"]) for i in range(3)]
+    torch.cuda.synchronize()
+    assert int((r.status == 0).sum()) == B
+    for i in range(B):
+        v, o = metas[i % 3], one[i % 3]
+        assert int(r.n_knots[i]) == v["n_knots"] == int(o.n_knots[0])
+        for got, single, ref in ((float(r.mean_curvature[i]), float(o.mean_curvature[0]), v["mean_curvature"]),
+                                 (float(r.max_curvature[i]), float(o.max_curvature[0]), v["max_curvature"])):
+            assert abs(got - single) <= 1e-9 * abs(single) and abs(got - ref) <= 1e-8 * abs(ref)
