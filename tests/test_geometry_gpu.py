@@ -202,3 +202,20 @@ def test_more_knot_frames_than_sms_use_the_small_cta_and_agree(manifest):
         for got, single, ref in ((float(r.mean_curvature[i]), float(o.mean_curvature[0]), v["mean_curvature"]),
                                  (float(r.max_curvature[i]), float(o.max_curvature[0]), v["max_curvature"])):
             assert abs(got - single) <= 1e-9 * abs(single) and abs(got - ref) <= 1e-8 * abs(ref)
+
+
+@pytest.mark.parametrize("H,W,amp", [(64, 96, 300.0), (64, 96, 3000.0), (96, 128, 3000.0)])
+def test_interpolation_knots_regime(H, W, amp):
+    """Depth noise so large that FITPACK runs out of knots to add (n = nmax = m + 4: one knot per data point, the
+    least-squares spline interpolates, fp = 0 < s) and then smooths back up to fp = s."""
+    f = synth.make_frame(40, H, W, 0.5, "f32")
+    rng = np.random.default_rng(int(amp) + H)
+    f["depth"] = (f["depth"] * (1.0 + amp * rng.random((H, W)))).astype(np.float32)
+    o = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
+    assert o.status == gp.OK and o.n_knots == o.n_edge + 4            # the oracle is in the regime this test is about
+    r = _run([f])
+    assert int(r.status[0]) == 0 and int(r.n_edge[0]) == o.n_edge
+    assert int(r.n_knots[0]) == o.n_knots and int(r.fit_ier[0]) == o.ier
+    assert abs(float(r.fit_residual[0]) - o.fp) <= 1e-6 * o.fp
+    assert abs(float(r.mean_curvature[0]) - o.mean_curvature) <= 1e-6 * o.mean_curvature
+    assert abs(float(r.max_curvature[0]) - o.max_curvature) <= 1e-6 * o.max_curvature
