@@ -1606,7 +1606,10 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     if ((debug & 2) && tid == 0 && band_R_valid) {
       double sd = 0.0;
       for (int i = 0; i < nk1; ++i) sd += w.R[i * 5];
-      printf("  frame %d lsq n %d fp %.17g sumdiag %.17g\n", b, n, fp, sd);
+      double tk = 0.0, dmin = 1e300;
+      for (int i = 0; i < n; ++i) tk += w.t[i] * (double)(i + 1);
+      for (int i = 0; i < nk1; ++i) dmin = fmin(dmin, w.R[i * 5]);
+      printf("  frame %d lsq n %d fp %.17g sumdiag %.17g knot checksum %.17g min diag %.3g\n", b, n, fp, sd, tk, dmin);
     }
     if (n == 8) {
       ier = -2;
