@@ -6,7 +6,7 @@ sys.path[:0] = ['/root/repo', '/root/repo/robotic-discovery-platform_b200']
 from pkg.segmentation_model import UNet
 from rdp_b200 import synth
 
-B,H,W=64,480,640
+B,H,W=int(os.environ.get('B',64)),int(os.environ.get('H',480)),int(os.environ.get('W',640))
 model = UNet(3,1); model.load_state_dict(synth.make_state_dict(2, planted=True)); model=model.cuda().eval()
 base=[synth.make_frame(5000+i,H,W,0.15,"u16") for i in range(8)]
 rgb=torch.from_numpy(np.stack([base[i%8]["rgb"] for i in range(B)])).cuda()
