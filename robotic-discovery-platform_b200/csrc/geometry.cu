@@ -925,9 +925,12 @@ __device__ __forceinline__ void window_rotate_in(double (&Rw)[5][5], double (&zw
 // (No __restrict__/const-cache loads: every input was written earlier in this kernel.)
 // DIAG_ONLY: only the triangle is wanted (FITPACK's first smoothing parameter needs sum(diag R)): the right-hand sides
 // are not rotated and nothing is solved.
+// rem_out (may be null): sum of squares of what is left of the right-hand sides once their rows have been rotated in -
+// FITPACK's own fp of the least-squares stage (fppara accumulates it the same way), see solve().
 template <bool PEN, bool DIAG_ONLY = false>
 __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
-                                              double* R, double* z, double* c) {
+                                              double* R, double* z, double* c, double* rem_out = nullptr) {
+  double rem = 0.0;
   double Rw[5][5], zw[5][3];
 #pragma unroll
   for (int r = 0; r < 5; ++r) {
@@ -1010,6 +1013,10 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
             if (!DIAG_ONLY) rota(cs[q], sn[q], x[q][d], zw[4 - q + st][d]);
         }
     }
+    if (!DIAG_ONLY) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) rem += x[q][0] * x[q][0] + x[q][1] * x[q][1] + x[q][2] * x[q][2];
+    }
   };
   int t_next = tfirst[0], t_next2 = nrint > 1 ? tfirst[1] : 0;
   for (int i = 0; i < nrint; ++i) {  // window row r = band row i - 1 + r
@@ -1053,6 +1060,7 @@ __device__ __noinline__ void band_merge_solve(const double* tri, const int* tfir
 #pragma unroll
     for (int d = 0; d < 3; ++d) z[(size_t)(nrint - 1 + r) * 3 + d] = zw[r][d];
   }
+  if (rem_out) *rem_out = rem;
   if (DIAG_ONLY) return;
   // fpback: c_i = (z_i - sum_e R[i][e] c_{i+e}) / R[i][0]; the newest coefficient enters last (shortest chain).
   // Entries of R past the last column were never touched and are zero.
@@ -1113,10 +1121,12 @@ __device__ __forceinline__ void rotate_in_tri8(double (&R)[36], double (&Z)[8][3
   }
 }
 
+// Returns this thread's share of the sum of squares of the right-hand-side remainders (see band_merge_solve).
 template <bool PEN>
-__device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
-                                      CrWs cw, double* c) {
+__device__ __noinline__ double cr_solve(const double* tri, const int* tfirst, const double* D, double pinv, int nrint,
+                                        CrWs cw, double* c) {
   const int tid = threadIdx.x;
+  double rem = 0.0;
   const int nk1 = nrint + 3;
   int L = 1;
   while ((4 << L) < nrint) ++L;  // every interval index below 4 * 2^L, so each interval has its group; 2^L + 1 >= NB follows
@@ -1154,6 +1164,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
           x[0] = x[1] = x[2] = 0.0;
         }
         rotate_in_tri8(R, Z, h, x);
+        rem += x[0] * x[0] + x[1] * x[1] + x[2] * x[2];
       }
     }
 #pragma unroll
@@ -1237,6 +1248,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
 #pragma unroll
         for (int d = 0; d < 3; ++d) x[d] = cw.scr[(size_t)(k * 11 + 8 + d) * KN_NT + tid];
         rotate_in_tri8(R, Z, h, x);
+        rem += x[0] * x[0] + x[1] * x[1] + x[2] * x[2];
       }
 #pragma unroll
       for (int q = 0; q < 36; ++q) Gout[(size_t)q * ngout + j] = R[q];
@@ -1307,6 +1319,7 @@ __device__ __noinline__ void cr_solve(const double* tri, const int* tfirst, cons
   }
   for (int i = tid; i < nk1 * 3; i += KN_NT) c[i] = cp[i];
   __syncthreads();
+  return rem;
 }
 
 __device__ __forceinline__ double block_sum1(double v, double* s_red) {
@@ -1391,6 +1404,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   auto solve = [&](double pinv) -> double {
     lap(tm_setup);
     ++n_solve;
+    double rem_acc = 0.0;  // this thread's share of sum(remainder^2) over every right-hand side rotated in below
     // (1) task triangles, one thread per task (at most KN_CH consecutive points of one interval).  They depend on the
     // knots only, not on the smoothing parameter: the root find reuses those of the last least-squares fit.
     if (!tri_valid) {
@@ -1410,6 +1424,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
           for (int e = 0; e < 4; ++e)
             if (e > r) rota(cs, sn, h[e], T[r][e]);
         }
+        rem_acc += x[0] * x[0] + x[1] * x[1] + x[2] * x[2];
       }
       double* o = w.tri + (size_t)k * 22;
       int q = 0;
@@ -1462,6 +1477,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
             for (int e = 0; e < 4; ++e)
               if (e > pc) rota(cs, sn, h[e], T[pc][e]);
           }
+          rem_acc += x[0] * x[0] + x[1] * x[1] + x[2] * x[2];
         }
         q = 0;
 #pragma unroll
@@ -1482,12 +1498,14 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     // (2) merge into the band, penalty rows interleaved by last column; back substitution
     if (nrint >= KN_CR_MIN && !no_cr) {
       if (pinv > 0.0) cr_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, cw, w.c);
-      else cr_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, cw, w.c);
+      else rem_acc += cr_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, cw, w.c);
       band_R_valid = false;
     } else {
       if (tid == 0) {
+        double rem_sweep = 0.0;
         if (pinv > 0.0) band_merge_solve<true>(w.tri, w.tfirst, w.D, pinv, nrint, w.R, w.z, w.c);
-        else band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c);
+        else band_merge_solve<false>(w.tri, w.tfirst, w.D, 0.0, nrint, w.R, w.z, w.c, &rem_sweep);
+        rem_acc += rem_sweep;
       }
       band_R_valid = true;
       __syncthreads();
@@ -1511,6 +1529,13 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     }
     const double total = block_sum1(part, s_red);
     lap(tm_res);
+    // Least-squares stage: FITPACK's fp is what the rotations leave of the right-hand sides (fppara adds the squared
+    // remainder of every data row it has rotated in), not the residual of the evaluated spline.  The two agree unless
+    // the triangle is numerically singular (more B-splines than data near an end: pivots of 1e-23 seen) - then the
+    // coefficients are meaningless, the evaluated residual explodes, and FITPACK carries on with the rotation-based
+    // value.  Orthogonal transformations preserve it, so the sum over the tasks, the trees and the solver is the same
+    // number.  The smoothing stage evaluates the spline, here as there.
+    if (pinv == 0.0) return block_sum1(rem_acc, s_red);
     return total;
   };
 
