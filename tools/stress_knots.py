@@ -17,14 +17,16 @@ from rdp_b200 import geometry, synth  # noqa: E402
 
 def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 48
+    plain = "--plain" in sys.argv        # ground-truth masks (mostly the 8-knot cubic regime) instead of staircase edges
     rng = np.random.default_rng(123)
     H, W = 240, 320
     frames = []
     for i in range(n):
         fill = float(rng.uniform(0.15, 0.6))
         f = synth.make_frame(1000 + i, H, W, fill, "u16" if i % 2 else "f32")
-        small = f["mask_gt"][::3, ::3] if i % 3 else f["mask_gt"][::2, ::2]          # what a low-resolution U-Net would give
-        f["mask_gt"] = np.ascontiguousarray(sp.upsize_mask_np(small, H, W))
+        if not plain:
+            small = f["mask_gt"][::3, ::3] if i % 3 else f["mask_gt"][::2, ::2]      # what a low-resolution U-Net would give
+            f["mask_gt"] = np.ascontiguousarray(sp.upsize_mask_np(small, H, W))
         frames.append(f)
     groups = {}
     for i, f in enumerate(frames):
@@ -48,6 +50,8 @@ def main():
         if o.status != gp.OK:
             continue
         hist.append(nk)
+        if o.n_knots != nk:
+            continue
         rel = max(abs(mean - o.mean_curvature) / o.mean_curvature, abs(mx - o.max_curvature) / o.max_curvature)
         worst = max(worst, rel if rel < 1e-4 else 0.0)
         if rel > 1e-6:
