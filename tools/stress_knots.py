@@ -19,7 +19,7 @@ def main():
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 48
     plain = "--plain" in sys.argv        # ground-truth masks (mostly the 8-knot cubic regime) instead of staircase edges
     rng = np.random.default_rng(123)
-    H, W = 240, 320
+    H, W = int(os.environ.get("H", 240)), int(os.environ.get("W", 320))
     frames = []
     for i in range(n):
         fill = float(rng.uniform(0.15, 0.6))

@@ -15,7 +15,7 @@ from rdp_b200 import synth  # noqa: E402
 def frame(i, n=512):
     rng = np.random.default_rng(123)
     fills = [float(rng.uniform(0.15, 0.6)) for _ in range(n)]
-    H, W = 240, 320
+    H, W = int(os.environ.get("H", 240)), int(os.environ.get("W", 320))
     f = synth.make_frame(1000 + i, H, W, fills[i], "u16" if i % 2 else "f32")
     small = f["mask_gt"][::3, ::3] if i % 3 else f["mask_gt"][::2, ::2]
     f["mask_gt"] = np.ascontiguousarray(sp.upsize_mask_np(small, H, W))
