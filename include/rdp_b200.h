@@ -178,7 +178,7 @@ int rdp_geom_deproject_static(const uint8_t* mask, const void* depth, int depth_
  * horizontal pass first, weights normalised per output index - in one pass, fp32.
  *   rgb_nhwc [B][H][W][C] uint8 (device), C in 1..8      out_nchw [B][C][out_h][out_w] fp32 (device)
  *   flags: 0 or RDP_PRE_SWAP_RB
- * One launch, no workspace.  Agreement with torchvision: a few fp32 ulp (the tests hold it to 2e-6 absolute). */
+ * One launch, no workspace.  Agreement with torchvision: a few fp32 ulp (the tests hold it to 1e-6 absolute). */
 #define RDP_PRE_SWAP_RB 1 /* input is BGR (cv2.imdecode): also does cv2.cvtColor(.., COLOR_BGR2RGB), server.py:120 */
 int rdp_pre_resize(const uint8_t* rgb_nhwc, int B, int H, int W, int C, int out_h, int out_w, int flags,
                    float* out_nchw, void* stream);

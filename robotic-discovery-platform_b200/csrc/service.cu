@@ -13,14 +13,16 @@ struct AaAxis {
   float scale, support, invscale;
   int in_size;
 };
+// Every step is rounded to fp32 as ATen rounds it: with the compiler free to contract, (j + lo) - scale * (i + 0.5)
+// becomes one fma on the unrounded centre, which at coordinates of several hundred shifts a weight by 1e-5.
 __device__ __forceinline__ void aa_window(const AaAxis& a, int i, int& lo, int& n, float& center) {
-  center = a.scale * ((float)i + 0.5f);
-  lo = max(0, (int)(center - a.support + 0.5f));
-  n = min(a.in_size, (int)(center + a.support + 0.5f)) - lo;
+  center = __fmul_rn(a.scale, __fadd_rn((float)i, 0.5f));
+  lo = max(0, (int)__fadd_rn(__fsub_rn(center, a.support), 0.5f));
+  n = min(a.in_size, (int)__fadd_rn(__fadd_rn(center, a.support), 0.5f)) - lo;
 }
 __device__ __forceinline__ float aa_weight(const AaAxis& a, int j, int lo, float center) {
-  const float x = ((float)(j + lo) - center + 0.5f) * a.invscale;
-  const float w = 1.0f - fabsf(x);
+  const float x = __fmul_rn(__fadd_rn(__fsub_rn((float)(j + lo), center), 0.5f), a.invscale);
+  const float w = __fsub_rn(1.0f, fabsf(x));
   return w > 0.f ? w : 0.f;
 }
 

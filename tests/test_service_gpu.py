@@ -16,7 +16,7 @@ from rdp_b200 import _lib, service, synth
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
-RESIZE_ATOL = 2e-6     # fp32, values in [0,1]; the kernel sums the taps in a different order from ATen
+RESIZE_ATOL = 1e-6     # fp32, values in [0,1]; the kernel sums the taps in a different order from ATen (6e-7 seen over 150 random shapes)
 
 
 def _cases():
