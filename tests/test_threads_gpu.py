@@ -53,3 +53,41 @@ def test_concurrent_callers_share_one_model():
         assert np.array_equal(m0, m1)
         assert r0.mean_curvature == r1.mean_curvature and r0.max_curvature == r1.max_curvature
         assert len(r1.spline_points) == 100
+
+
+def test_frame_pipeline_returns_what_the_direct_call_returns():
+    """Three streams, two slots, shared workspaces: every micro-batch's host-side results, in submission order, equal the
+    direct forward_mask + curvature_batch call on the same frames - also when slots are reused many times."""
+    import numpy as np
+    import torch
+
+    from pkg.segmentation_model import UNet
+    from rdp_b200 import geometry, synth
+    from rdp_b200.pipeline import FramePipeline
+    B, H, W, n_batches = 4, 96, 128, 7
+    model = UNet(3, 1).eval()
+    model.load_state_dict(synth.make_state_dict(2, planted=True))
+    model = model.cuda()
+    frames = [synth.make_frame(700 + i, H, W, 0.25 + 0.05 * (i % 4), "u16") for i in range(B * n_batches)]
+    K, scale = frames[0]["K"], frames[0]["depth_scale"]
+    rgb = [torch.from_numpy(np.stack([f["rgb"] for f in frames[b * B:(b + 1) * B]])).pin_memory() for b in range(n_batches)]
+    dep = [torch.from_numpy(np.stack([f["depth"] for f in frames[b * B:(b + 1) * B]])).pin_memory() for b in range(n_batches)]
+    pipe = FramePipeline(model, K, scale, B, H, W, slots=2)
+    got = []
+    for b in range(n_batches):
+        if pipe.in_flight == 2:
+            got.append(pipe.collect())
+        pipe.submit(rgb[b], dep[b])
+    while pipe.in_flight:
+        got.append(pipe.collect())
+    assert len(got) == n_batches
+    for b in range(n_batches):
+        mask, _, _ = model.forward_mask(rgb[b].cuda())
+        r = geometry.curvature_batch(mask[:, 0], dep[b].cuda(), K, scale)
+        assert np.array_equal(got[b]["status"], r.status.cpu().numpy())
+        assert np.array_equal(got[b]["mean"], r.mean_curvature.cpu().numpy())
+        assert np.array_equal(got[b]["max"], r.max_curvature.cpu().numpy())
+        assert np.array_equal(got[b]["points"], r.spline_points.cpu().numpy())
+    assert any((g["status"] == 0).any() for g in got)
+    with pytest.raises(RuntimeError):            # a third submit without a collect would overwrite uncollected results
+        pipe.submit(rgb[0], dep[0]); pipe.submit(rgb[1], dep[1]); pipe.submit(rgb[2], dep[2])
