@@ -109,3 +109,35 @@ def analyze_frames(model, color_u8: torch.Tensor, depth: torch.Tensor, intrinsic
     # through its reciprocal, which rounds differently
     coverage = cnt.to(torch.float64) / torch.full_like(cnt, H * W, dtype=torch.float64) * 100.0
     return FrameAnalysis(curv, final_mask, coverage, x, mask_small)
+
+
+class StreamRing:
+    """Round-robin CUDA streams for back-to-back batches of the server-shaped step.
+
+    The spline fits of a batch are a latency chain on one CTA per frame (64 frames leave more than half of the SMs idle
+    for about half of the step); issued on alternating streams, that tail overlaps the next batch's U-Net:
+    640x480, 64 frames: 9.5 -> 7.3 ms per batch with two streams; 32 frames: 7.3 -> 4.0 ms with three.
+
+        ring = StreamRing(2)
+        for rgb, depth in batches:
+            with ring.next():
+                r = analyze_frames(model, rgb, depth, K, scale)     # inputs must already be visible to that stream
+        ring.synchronize()
+    """
+
+    def __init__(self, n: int = 2, device=None):
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        with torch.cuda.device(self.device):
+            self.streams = [torch.cuda.Stream(self.device) for _ in range(max(1, int(n)))]
+        self._i = 0
+
+    def next(self):
+        s = self.streams[self._i % len(self.streams)]
+        self._i += 1
+        s.wait_stream(torch.cuda.current_stream(self.device))      # what the caller queued so far (its inputs) comes first
+        return torch.cuda.stream(s)
+
+    def synchronize(self) -> None:
+        for s in self.streams:
+            torch.cuda.current_stream(self.device).wait_stream(s)
+            s.synchronize()

@@ -222,3 +222,29 @@ def test_png_entry_point_refuses_bad_buffers():
     assert lib.rdp_post_mask_png(m.data_ptr(), B, H, W, png.data_ptr(), ok_stride, n.data_ptr(), ws.data_ptr(), ws.numel(), stream) == 0
     torch.cuda.synchronize()
     assert np.array_equal(sp.decode_mask_png(png[0, :int(n[0])].cpu().numpy().tobytes()), np.zeros((H, W), np.uint8))
+
+
+def test_stream_ring_gives_the_same_results_as_one_stream():
+    from pkg.segmentation_model import UNet
+    H, W, B = 240, 320, 6
+    model = UNet(3, 1).eval()
+    model.load_state_dict(synth.make_state_dict(5, planted=True))
+    model = model.cuda()
+    batches = []
+    for k in range(5):
+        frames = [synth.make_frame(400 + 10 * k + i, H, W, 0.30, "u16") for i in range(B)]
+        batches.append((torch.from_numpy(np.stack([f["rgb"] for f in frames])).cuda(),
+                        torch.from_numpy(np.stack([f["depth"] for f in frames])).cuda(), frames[0]["K"], frames[0]["depth_scale"]))
+    single = [service.analyze_frames(model, *b) for b in batches]
+    torch.cuda.synchronize()
+    ring = service.StreamRing(3)
+    ringed = []
+    for b in batches:
+        with ring.next():
+            ringed.append(service.analyze_frames(model, *b))
+    ring.synchronize()
+    for a, c in zip(single, ringed):
+        assert torch.equal(a.final_mask, c.final_mask) and torch.equal(a.mask_coverage_percent, c.mask_coverage_percent)
+        assert torch.equal(a.curvature.status, c.curvature.status) and torch.equal(a.curvature.n_knots, c.curvature.n_knots)
+        assert torch.equal(a.curvature.mean_curvature, c.curvature.mean_curvature)
+        assert torch.equal(a.curvature.spline_points, c.curvature.spline_points)
