@@ -27,6 +27,7 @@ __device__ __forceinline__ float aa_weight(const AaAxis& a, int j, int lo, float
 }
 
 constexpr int MAX_C = 8;
+constexpr int AA_TAPS = 32;  // horizontal taps kept per thread (a 15x reduction); wider windows recompute them
 
 __global__ void __launch_bounds__(256) k_resize_aa(const uint8_t* __restrict__ in, int B, int H, int W, int C, int OH, int OW,
                                                    AaAxis ay, AaAxis ax, int swap_rb, float* __restrict__ out) {
@@ -40,6 +41,11 @@ __global__ void __launch_bounds__(256) k_resize_aa(const uint8_t* __restrict__ i
   float sumx = 0.f, sumy = 0.f;
   for (int j = 0; j < nx; ++j) sumx += aa_weight(ax, j, x0, cx);
   for (int j = 0; j < ny; ++j) sumy += aa_weight(ay, j, y0, cy);
+  // the normalised horizontal weights are the same for every source row: one division per tap, not one per tap and row
+  float wxs[AA_TAPS];
+  const bool cached = nx <= AA_TAPS;
+  if (cached)
+    for (int j = 0; j < nx; ++j) wxs[j] = aa_weight(ax, j, x0, cx) / sumx;
   float acc[MAX_C];
 #pragma unroll
   for (int c = 0; c < MAX_C; ++c) acc[c] = 0.f;
@@ -50,10 +56,10 @@ __global__ void __launch_bounds__(256) k_resize_aa(const uint8_t* __restrict__ i
 #pragma unroll
     for (int c = 0; c < MAX_C; ++c) h[c] = 0.f;
     for (int jx = 0; jx < nx; ++jx) {
-      const float wx = aa_weight(ax, jx, x0, cx) / sumx;
+      const float wx = cached ? wxs[jx] : aa_weight(ax, jx, x0, cx) / sumx;
 #pragma unroll
       for (int c = 0; c < MAX_C; ++c)
-        if (c < C) h[c] += wx * (__fdiv_rn((float)row[jx * C + c], 255.0f));  // ToTensor: uint8 / 255
+        if (c < C) h[c] += wx * (__fdiv_rn((float)row[jx * C + c], 255.0f));  // ToTensor: uint8 / 255 (a shared-memory table of the 256 quotients was slower)
     }
 #pragma unroll
     for (int c = 0; c < MAX_C; ++c) acc[c] += wy * h[c];
