@@ -1628,13 +1628,19 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     __syncthreads();
 
     fp = solve(0.0);
-    if ((debug & 2) && tid == 0 && band_R_valid) {
-      double sd = 0.0;
-      for (int i = 0; i < nk1; ++i) sd += w.R[i * 5];
-      double tk = 0.0, dmin = 1e300;
+    if ((debug & 2) && tid == 0) {
+      double sd = 0.0, tk = 0.0, dmin = 1e300, ck = 0.0;
       for (int i = 0; i < n; ++i) tk += w.t[i] * (double)(i + 1);
-      for (int i = 0; i < nk1; ++i) dmin = fmin(dmin, w.R[i * 5]);
-      printf("  frame %d lsq n %d fp %.17g sumdiag %.17g knot checksum %.17g min diag %.3g\n", b, n, fp, sd, tk, dmin);
+      for (int i = 0; i < nk1 * 3; ++i) ck += w.c[i] * (double)(1 + i % 5);
+      if (band_R_valid) {
+        for (int i = 0; i < nk1; ++i) {
+          sd += w.R[i * 5];
+          dmin = fmin(dmin, w.R[i * 5]);
+        }
+        printf("  frame %d lsq n %d fp %.17g sumdiag %.17g knot checksum %.17g min diag %.3g coefficient checksum %.17g\n", b, n, fp, sd, tk, dmin, ck);
+      } else {
+        printf("  frame %d lsq n %d fp %.17g (cyclic reduction) knot checksum %.17g coefficient checksum %.17g\n", b, n, fp, tk, ck);
+      }
     }
     if (n == 8) {
       ier = -2;
@@ -1739,6 +1745,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
       const double fpmax = __longlong_as_double((long long)bk);
       const int maxpt = br, maxbeg = bb;
       const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
+      if ((debug & 16) && tid == 0) printf("  frame %d n %d split %d: node %d begin %d points %d residual %.17g -> knot at point %d\n", b, n, l, bi, maxbeg, maxpt, fpmax, nrx - 1);
       const bool own_old = (bi % KN_NT) == tid, own_new = (nn % KN_NT) == tid;
       if (own_old) {
         w.flag[nrx - 1] = 1;

@@ -12,7 +12,7 @@ from oracle import service_port as sp  # noqa: E402
 from rdp_b200 import synth  # noqa: E402
 
 
-def frame(i, n=512):
+def frame(i, n=int(os.environ.get("N", 512))):
     rng = np.random.default_rng(123)
     fills = [float(rng.uniform(0.15, 0.6)) for _ in range(n)]
     H, W = int(os.environ.get("H", 240)), int(os.environ.get("W", 320))
