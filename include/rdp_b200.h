@@ -44,11 +44,13 @@ extern "C" {
 #define RDP_DEPTH_U16 0 /* z = (double)d * scale                     (uint16 image * Python float) */
 #define RDP_DEPTH_F32 1 /* z = (double)(float)(d * (float)scale)     (float32 image * Python float) */
 #define RDP_DEPTH_F32_WIDE 2 /* z = (double)d * scale                (float32 image * numpy float64 scalar) */
+#define RDP_DEPTH_F64 3 /* z = d * scale, d a double                  (float64 image; other integer dtypes widened by the host) */
 
 /* U-Net input formats */
 #define RDP_IN_RGB_U8_NHWC 0 /* (B,H,W,C) uint8, scaled by 1/255 on load (ToTensor, server.py:108) */
 #define RDP_IN_F32_NCHW 1    /* (B,C,H,W) float32, the tensor the reference module receives (server.py:121) */
-/* OR into in_fmt: also keep the last conv's activation in the workspace (only rdp_unet_read_activation(17) needs it) */
+/* OR into in_fmt: keep every conv's activation in the workspace, each in storage of its own (parity hook:
+ * rdp_unet_read_activation needs it; the workspace must then have the size rdp_unet_workspace_bytes_ex reports) */
 #define RDP_IN_FLAG_KEEP_ACTIVATIONS 0x100
 
 int rdp_abi_version(void);
@@ -80,12 +82,17 @@ typedef struct {
   const float* outc_bias;   /* device fp32 [n_classes] */
 } RdpUnetWeights;
 
-/* Builds an immutable handle (copies the small descriptor, keeps the caller's device pointers). */
+/* Builds an immutable handle (copies the small descriptor, keeps the caller's device pointers).  A handle belongs to
+ * the device that was current when it was created (its weights live there); a process may hold handles on several
+ * devices and call each with its own device current. */
 int rdp_unet_create(const RdpUnetWeights* weights, RdpUnet** out);
 void rdp_unet_destroy(RdpUnet* net);
 
-/* Scratch for activations of one forward call of shape (B,H,W). */
+/* Scratch for activations of one forward call of shape (B,H,W).  Buffers whose lifetimes do not overlap share
+ * storage (8.2 GB for 64 frames of 640x480).  A forward called with RDP_IN_FLAG_KEEP_ACTIVATIONS keeps every layer's
+ * output instead and needs the larger size rdp_unet_workspace_bytes_ex(net, RDP_IN_FLAG_KEEP_ACTIVATIONS, ...) gives. */
 int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W, size_t* bytes);
+int rdp_unet_workspace_bytes_ex(const RdpUnet* net, int in_fmt_flags, int B, int H, int W, size_t* bytes);
 
 /* logits: fp32 (B, n_classes, H, W) or NULL.  mask: uint8 (B, n_classes, H, W) in {0,1} or NULL; it is
  * [sigmoidf(logit) > 0.5f] evaluated in fp32 like the server does.  At least one of them must be non-NULL. */
@@ -102,7 +109,8 @@ int rdp_unet_forward_profiled(const RdpUnet* net, const void* input, int in_fmt,
                               uint8_t* mask, void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);
 
 /* Debug / parity hook: copy of an intermediate activation as fp32 NCHW.  `index` = 0..17 (conv outputs in the
- * order of RdpUnetWeights.conv).  Must be called after rdp_unet_forward on the same workspace and stream. */
+ * order of RdpUnetWeights.conv).  Must be called after an rdp_unet_forward with RDP_IN_FLAG_KEEP_ACTIVATIONS on the
+ * same workspace and stream. */
 int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,
                              float* out_nchw, void* stream);
 
@@ -123,7 +131,19 @@ typedef struct {
   int32_t* bin_counts;     /* [B][50] points per x-bin                        (NULL allowed) */
   int32_t* n_knots;        /* [B] knots of the fitted spline (8 = single cubic)  (NULL allowed) */
   int32_t* fit_ier;        /* [B] FITPACK's ier: -2, 0, or 1/2/3 (warnings)     (NULL allowed) */
+  int32_t* fit_flags;      /* [B] RDP_FIT_FLAG_* bits, 0 for the single-cubic regime (NULL allowed; ABI version 2) */
 } RdpCurvatureOut;
+
+/* fit_flags: decisions inside FITPACK's knot-insertion regime (splprep, geometry_utils.py:78) that were taken on a
+ * margin smaller than the rounding noise of the least-squares solves.  FITPACK itself (scipy) takes the same
+ * decisions on the same margins, so on a flagged frame two correct implementations - or scipy on two machines - may
+ * place a knot differently and report curvatures that differ by far more than 1e-3; an
+ * unflagged frame follows scipy's knot sequence exactly. */
+#define RDP_FIT_FLAG_KNOT_TIE 1    /* fpknot: largest and second-largest interval residual within ~1e-9 relative
+                                      (and not the bit-identical halves of one split) */
+#define RDP_FIT_FLAG_BRACKET_TIE 2 /* smoothing root find: (p/0.04)*0.04 compared with p, an exact-arithmetic
+                                      equality FITPACK decides by the last bit; resolved here as exact arithmetic does */
+#define RDP_FIT_FLAG_NPLUS_TIE 4   /* the number of knots to add, int(nplus*(fp-s)/(fpold-fp)), sat on an integer */
 
 int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes);
 
@@ -161,8 +181,10 @@ int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int dept
  * are refused with RDP_ERR_UNSUPPORTED.  The array (about 100 KB) is held by every GPU that loads the library
  * until the process exits.  The call itself performs no allocation of any kind.
  *
- * The first call on each device looks up the array's device address; make that first call with the device
- * current and before any stream capture begins.  All calls share the array and each clears what it uses
+ * The first call on each device looks up the array's device address; make that first call before any stream
+ * capture begins.  On EVERY call the device that `stream` belongs to must be the current device (the array is per
+ * device and is found through the current one); a stream of another device is refused with RDP_ERR_BAD_ARGUMENT
+ * before any work is issued.  All calls share the array and each clears what it uses
  * before running, so calls whose GPU work could overlap (different streams, different threads) race: keep them
  * on one stream or wait for one to finish before issuing the next. */
 int rdp_geom_deproject_static(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,

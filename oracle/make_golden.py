@@ -47,6 +47,23 @@ GEOM_CASES = [
     ("geom_u16_480x640_f15_ties", 16, 480, 640, 0.15, "u16"),
     ("geom_u16_240x320_f30_ties", 17, 240, 320, 0.30, "u16"),
 ]
+# Round 2: the knot-insertion regime at HD resolution, and on what the service really sees (uint16 depth; a mask that
+# was up-sized from a low-resolution one, so its edge is a staircase).  Fields as above plus
+#   stair  0 = ground-truth mask, n = mask_gt[::n, ::n] up-sized with OpenCV's INTER_NEAREST rule (server.py:125)
+#   ties   "none"   = tie-free input, the unmodified reference is a deterministic oracle
+#          "stable" = the input has ties (equal x among edge points, equal y at a bin's k-th boundary) and NumPy's
+#                     argpartition / default argsort leave their order unspecified: the reference's own
+#                     code is run with those two calls made deterministic (larger y first, then the smaller pixel
+#                     index; equal x by pixel index - the rule DESIGN.md states), and the unmodified reference's
+#                     result is recorded next to it as `*_unmodified` so the tie-induced gap is on file.
+GEOM_CASES_R2 = [
+    ("geom_f32_720x1280_f48_knots3942", 35, 720, 1280, 0.48, "f32", 0, "none"),
+    ("geom_f32_720x1280_f50_knots5409", 33, 720, 1280, 0.50, "f32", 0, "none"),
+    ("geom_f32_480x640_f15_stair3", 22, 480, 640, 0.15, "f32", 3, "none"),
+    ("geom_u16_480x640_f56_knots_ties", 16, 480, 640, 0.56, "u16", 0, "stable"),
+    ("geom_u16_480x640_f15_stair3_ties", 16, 480, 640, 0.15, "u16", 3, "stable"),
+    ("geom_u16_240x320_f30_stair2_ties", 17, 240, 320, 0.30, "u16", 2, "stable"),
+]
 
 
 def _import_reference():
@@ -64,9 +81,92 @@ def _import_reference():
     return mods["segmentation_model"], mods["geometry_utils"]
 
 
+class _StableNumpy:
+    """`numpy` as the reference module sees it, with the two tie-dependent calls made deterministic.
+
+    `argpartition(y, -k)` (`geometry_utils.py:139`): a full order by (y ascending, index descending) so that the last k
+    entries are the k largest y with ties won by the smaller index, those k then listed by index (= pixel order, the
+    cloud is row-major).  `argsort(x)` (`:74`): stable, so equal x keep that order.  Everything else is NumPy's own."""
+
+    def __init__(self, real):
+        self._np = real
+
+    def __getattr__(self, name):
+        return getattr(self._np, name)
+
+    def argpartition(self, a, kth, *args, **kw):
+        np_ = self._np
+        a = np_.asarray(a)
+        order = np_.lexsort((-np_.arange(a.shape[0]), a))
+        k = -kth if kth < 0 else a.shape[0] - kth
+        order[a.shape[0] - k:] = np_.sort(order[a.shape[0] - k:])
+        return order
+
+    def argsort(self, a, *args, **kw):
+        return self._np.argsort(a, kind="stable")
+
+
+def staircase_mask(mask, n, H, W):
+    """mask[::n, ::n] brought back to (H, W) by cv2.resize(..., INTER_NEAREST), as the server does (`server.py:125`)."""
+    import cv2
+    return np.ascontiguousarray(cv2.resize(np.ascontiguousarray(mask[::n, ::n]), (W, H), interpolation=cv2.INTER_NEAREST))
+
+
+def geometry_record(geo, mask, depth, K, scale):
+    """Everything the tests compare for one frame, from the reference module `geo` (possibly with stable ties)."""
+    from scipy.interpolate import splprep
+    pcd = geo._get_pcd_from_mask(mask, depth, K, scale)
+    edge = geo._find_point_cloud_edge(pcd)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        res = geo.compute_curvature_profile(mask=mask, depth_image=depth, intrinsics=K, depth_scale=scale)
+        srt = edge[np.argsort(edge[:, 0], kind="stable")]
+        (tck, _u), fp, ier, _ = splprep([srt[:, 0], srt[:, 1], srt[:, 2]], s=0.1, k=3, full_output=1)
+    xs = np.sort(edge[:, 0])
+    return pcd, edge, res, tck, float(fp), int(ier), int((np.diff(xs) == 0).sum())
+
+
 def sample_positions(shape, n=48, seed=7):
     rng = np.random.default_rng(seed)
     return tuple(rng.integers(0, s, size=n) for s in shape)
+
+
+def round2_cases(geo, manifest):
+    from rdp_b200 import synth
+    for name, seed, H, W, fill, flavour, stair, ties in GEOM_CASES_R2:
+        f = synth.make_frame(seed, H, W, fill, flavour)
+        mask = staircase_mask(f["mask_gt"], stair, H, W) if stair else f["mask_gt"]
+        depth, K, scale = f["depth"], f["K"], f["depth_scale"]
+        real_np = geo.np
+        unmod = geometry_record(geo, mask, depth, K, scale)
+        if ties == "stable":
+            geo.np = _StableNumpy(real_np)
+            try:
+                pcd, edge, res, tck, fp, ier, x_ties = geometry_record(geo, mask, depth, K, scale)
+            finally:
+                geo.np = real_np
+        else:
+            pcd, edge, res, tck, fp, ier, x_ties = unmod
+            assert x_ties == 0, (name, "is listed as tie-free but has equal x among its edge points", x_ties)
+        rec = dict(
+            n_points=np.int64(pcd.shape[0]),
+            pcd_sha256=np.frombuffer(hashlib.sha256(np.ascontiguousarray(pcd, dtype='<f8').tobytes()).digest(), dtype=np.uint8),
+            edge_sorted=edge[np.lexsort((edge[:, 1], edge[:, 0]))],
+            mean_curvature=np.float64(res.mean_curvature), max_curvature=np.float64(res.max_curvature),
+            spline_points=np.array([[p.x, p.y, p.z] for p in res.spline_points], dtype=np.float64),
+            t=np.asarray(tck[0]), fp=np.float64(fp), ier=np.int64(ier), x_ties=np.int64(x_ties),
+            mean_curvature_unmodified=np.float64(unmod[2].mean_curvature),
+            max_curvature_unmodified=np.float64(unmod[2].max_curvature),
+        )
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **rec)
+        manifest["cases"][name] = dict(kind="geometry", seed=seed, H=H, W=W, fill=fill, depth=flavour, stair=stair, ties=ties,
+                                       n_points=int(pcd.shape[0]), n_edge=int(edge.shape[0]), n_knots=int(len(tck[0])),
+                                       ier=ier, fp=fp, x_ties=x_ties, mean_curvature=float(res.mean_curvature),
+                                       max_curvature=float(res.max_curvature),
+                                       mean_curvature_unmodified=float(unmod[2].mean_curvature),
+                                       max_curvature_unmodified=float(unmod[2].max_curvature))
+        print(name, {k: manifest["cases"][name][k] for k in ("n_points", "n_edge", "n_knots", "ier", "x_ties", "mean_curvature",
+                                                              "max_curvature", "mean_curvature_unmodified")})
 
 
 def main():
@@ -78,6 +178,14 @@ def main():
     seg, geo = _import_reference()
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
+    if "--round2" in sys.argv:      # only the cases added in round 2, merged into the existing manifest
+        with open(os.path.join(OUT, "manifest.json")) as fh:
+            manifest = json.load(fh)
+        assert (manifest["numpy"], manifest["scipy"]) == (np.__version__, scipy.__version__), "library versions changed"
+        round2_cases(geo, manifest)
+        with open(os.path.join(OUT, "manifest.json"), "w") as fh:
+            json.dump(manifest, fh, indent=1, sort_keys=True)
+        return
     manifest = {"torch": torch.__version__, "numpy": np.__version__, "scipy": scipy.__version__, "cases": {}}
 
     # ---------------- U-Net ----------------
@@ -179,6 +287,7 @@ def main():
         degenerate[key] = dict(mean=float(r.mean_curvature), max=float(r.max_curvature), n_spline=len(r.spline_points))
         print("degenerate", key, degenerate[key])
     manifest["degenerate"] = degenerate
+    round2_cases(geo, manifest)
 
     with open(os.path.join(OUT, "manifest.json"), "w") as fh:
         json.dump(manifest, fh, indent=1, sort_keys=True)

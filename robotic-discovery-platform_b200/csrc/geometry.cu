@@ -23,6 +23,13 @@
 
 #include "rdp_common.cuh"
 
+// Development switches are compiled out of the shipped library (see unet.cu): build with -DRDP_DEVELOPMENT to get them.
+#ifdef RDP_DEVELOPMENT
+static inline const char* dev_env(const char* name) { return getenv(name); }
+#else
+static inline const char* dev_env(const char*) { return nullptr; }
+#endif
+
 namespace rdp {
 namespace geom {
 
@@ -87,6 +94,7 @@ struct Params {
 // ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ double depth_to_z(const Params& p, size_t gi) {
   if (p.depth_fmt == RDP_DEPTH_U16) return __dmul_rn((double)((const uint16_t*)p.depth)[gi], p.scale);
+  if (p.depth_fmt == RDP_DEPTH_F64) return __dmul_rn(((const double*)p.depth)[gi], p.scale);
   const float d = ((const float*)p.depth)[gi];
   if (p.depth_fmt == RDP_DEPTH_F32) return (double)__fmul_rn(d, p.scale_f32);
   return __dmul_rn((double)d, p.scale);
@@ -781,6 +789,7 @@ __global__ void __launch_bounds__(FIT_THREADS) k_fit(const Params p) {
     if (p.out.fit_residual) p.out.fit_residual[b] = fp;
     if (p.out.n_knots) p.out.n_knots[b] = 8;
     if (p.out.fit_ier) p.out.fit_ier[b] = status == RDP_FRAME_OK ? -2 : 0;
+    if (p.out.fit_flags) p.out.fit_flags[b] = 0;
   }
 }
 
@@ -807,6 +816,10 @@ constexpr int KN_MAXIT = 20;
 // it, which is also FITPACK's own outcome in the large majority of cases.
 constexpr double KN_TIE_UP = 1.0 + 1e-12, KN_TIE_DOWN = 1.0 - 1e-12;
 constexpr int KN_CH = 16;  // data points per triangle task (an interval with more points is cut into several)
+// Two interval residuals closer than this (in units of the last place: 2^23 ulp is 1-2e-9 relative) cannot be told
+// apart by solves that order their rotations differently: measured noise between the cyclic reduction, the one-thread
+// sweep and FITPACK's row-by-row order is 1e-13 ... 1e-11 relative.
+constexpr unsigned long long KN_NEAR_TIE = 1ull << 23;
 
 struct KnotWs {
   double *t, *q, *term, *fpint, *tri, *R, *z, *c, *D;
@@ -1338,7 +1351,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   __shared__ int s_i[8];
   __shared__ unsigned long long s_best[KN_THREADS / 32];
   __shared__ int s_besti[KN_THREADS / 32];
-  __shared__ unsigned long long s_knot_key[2][KN_THREADS / 32];
+  __shared__ unsigned long long s_knot_key[2][KN_THREADS / 32], s_knot_key2[2][KN_THREADS / 32];
   __shared__ int4 s_knot_meta[2][KN_THREADS / 32];
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (p.out.status[b] != RDP_FRAME_NEEDS_KNOTS) return;
@@ -1399,6 +1412,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
   };
   double fp = 0.0, fp0 = 0.0, fpold = 0.0, fpms = 0.0;
   bool smoothing = false, finished = false;
+  int fit_flags = 0;  // RDP_FIT_FLAG_*: decisions of this fit that rounding noise could have taken the other way
 
   // ---- one least-squares (pinv = 0) or smoothing (pinv > 0) solve on the current knots: fills w.c, returns fp ----
   auto solve = [&](double pinv) -> double {
@@ -1657,7 +1671,11 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     if (n == nest) { ier = 1; finished = true; break; }
     if (ier == 0) {
       int npl1 = nplus * 2;
-      if (fpold - fp > acc) npl1 = (int)((double)nplus * fpms / (fpold - fp));
+      if (fpold - fp > acc) {
+        const double raw = (double)nplus * fpms / (fpold - fp);
+        npl1 = (int)raw;
+        if (fabs(raw - rint(raw)) <= 1e-9 * fabs(raw)) fit_flags |= RDP_FIT_FLAG_NPLUS_TIE;  // truncation on an integer's edge
+      }
       nplus = min(nplus * 2, max(npl1, max(nplus / 2, 1)));
     } else {
       nplus = 1;
@@ -1684,10 +1702,14 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     int nn = nrint;
     unsigned long long my_key = 0;  // residual as an integer (positive doubles order as their bit patterns); 0 = nothing
     int my_beg = 0x7fffffff, my_nrd = 0, my_idx = -1;
+    // The runner-up (key and point count only) rides along: when it is within KN_NEAR_TIE of the winner without being
+    // its bit-identical twin, the choice of interval hangs on rounding noise and the frame is flagged (fit_flags).
+    unsigned long long my_key2 = 0;
+    int my_nrd2 = 0;
     auto rescan = [&]() {
-      my_key = 0;
+      my_key = my_key2 = 0;
       my_beg = 0x7fffffff;
-      my_nrd = 0;
+      my_nrd = my_nrd2 = 0;
       my_idx = -1;
       for (int i = tid; i < nn; i += KN_NT) {
         const int nr = w.nrd[i];
@@ -1697,51 +1719,68 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
         const unsigned long long key = (unsigned long long)__double_as_longlong(v);
         const int nb = w.nbeg[i];
         if (key > my_key || (key == my_key && nb < my_beg)) {  // larger residual first, earlier interval on ties
+          my_key2 = my_key;
+          my_nrd2 = my_nrd;
           my_key = key;
           my_beg = nb;
           my_nrd = nr;
           my_idx = i;
+        } else if (key > my_key2) {
+          my_key2 = key;
+          my_nrd2 = nr;
         }
       }
     };
     rescan();
     for (int l = 0; l < nplus; ++l) {
-      unsigned long long bk = my_key;
-      int bb = my_beg, br = my_nrd, bi = my_idx;
+      unsigned long long bk = my_key, bk2 = my_key2;
+      int bb = my_beg, br = my_nrd, bi = my_idx, br2 = my_nrd2;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bk, o);
+        const unsigned long long ok = __shfl_xor_sync(0xffffffffu, bk, o), ok2 = __shfl_xor_sync(0xffffffffu, bk2, o);
         const int ob = __shfl_xor_sync(0xffffffffu, bb, o), orr = __shfl_xor_sync(0xffffffffu, br, o),
-                  oi = __shfl_xor_sync(0xffffffffu, bi, o);
-        if (ok > bk || (ok == bk && ob < bb)) {
+                  oi = __shfl_xor_sync(0xffffffffu, bi, o), orr2 = __shfl_xor_sync(0xffffffffu, br2, o);
+        if (ok > bk || (ok == bk && ob < bb)) {  // the other side wins: its runner-up competes with our winner
+          if (bk > ok2) { bk2 = bk; br2 = br; } else { bk2 = ok2; br2 = orr2; }
           bk = ok;
           bb = ob;
           br = orr;
           bi = oi;
+        } else if (ok > bk2) {
+          bk2 = ok;
+          br2 = orr;
         }
       }
       const int buf = l & 1;
       if (lane == 0) {
         s_knot_key[buf][warp] = bk;
-        s_knot_meta[buf][warp] = make_int4(bb, br, bi, 0);
+        s_knot_meta[buf][warp] = make_int4(bb, br, bi, br2);
+        s_knot_key2[buf][warp] = bk2;
       }
       __syncthreads();
-      bk = 0;
+      bk = bk2 = 0;
       bb = 0x7fffffff;
-      br = 0;
+      br = br2 = 0;
       bi = -1;
 #pragma unroll
       for (int k = 0; k < KN_NT / 32; ++k) {
-        const unsigned long long ok = s_knot_key[buf][k];
+        const unsigned long long ok = s_knot_key[buf][k], ok2 = s_knot_key2[buf][k];
         const int4 om = s_knot_meta[buf][k];
         if (ok > bk || (ok == bk && om.x < bb)) {
+          if (bk > ok2) { bk2 = bk; br2 = br; } else { bk2 = ok2; br2 = om.w; }
           bk = ok;
           bb = om.x;
           br = om.y;
           bi = om.z;
+        } else if (ok > bk2) {
+          bk2 = ok;
+          br2 = om.y;
         }
       }
       if (bi < 0) break;  // nothing left to split (block-uniform: every thread derived the same winner)
+      // bit-identical residuals with equal point counts come from one expression (the halves of an odd split and their
+      // descendants) and resolve by position in every implementation; anything else this close is decided by rounding
+      if (bk2 != 0 && bk - bk2 <= KN_NEAR_TIE && !(bk == bk2 && br == br2)) fit_flags |= RDP_FIT_FLAG_KNOT_TIE;
       const double fpmax = __longlong_as_double((long long)bk);
       const int maxpt = br, maxbeg = bb;
       const int ihalf = maxpt / 2 + 1, nrx = maxbeg + ihalf;
@@ -1815,6 +1854,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
         if ((f2 - f3) <= acc) {
           p3 = p2; f3 = f2;
           pp = pp * 0.04;
+          if (p1 > 0.0 && fabs(pp - p1) <= 1e-12 * p1) fit_flags |= RDP_FIT_FLAG_BRACKET_TIE;
           if (pp <= p1 * KN_TIE_UP) pp = p1 * 0.9 + p2 * 0.1;
           continue;
         }
@@ -1825,6 +1865,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
           p1 = p2; f1 = f2;
           pp = pp / 0.04;
           if (p3 < 0.0) continue;
+          if (fabs(pp - p3) <= 1e-12 * p3) fit_flags |= RDP_FIT_FLAG_BRACKET_TIE;
           if (pp >= p3 * KN_TIE_DOWN) pp = p2 * 0.1 + p3 * 0.9;
           continue;
         }
@@ -1904,6 +1945,7 @@ __global__ void __launch_bounds__(KN_THREADS) k_fit_knots(const Params p, const 
     if (p.out.n_knots) p.out.n_knots[b] = n;
     if (p.out.fit_residual) p.out.fit_residual[b] = fp;
     if (p.out.fit_ier) p.out.fit_ier[b] = ier;
+    if (p.out.fit_flags) p.out.fit_flags[b] = fit_flags;
   }
 }
 
@@ -1991,7 +2033,7 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   RDP_REQUIRE(mask && depth && intrinsics && out && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_geom_curvature: null pointer");
   RDP_REQUIRE(B > 0 && H > 0 && W > 0, RDP_ERR_BAD_ARGUMENT, "rdp_geom_curvature: bad shape %dx%dx%d", B, H, W);
   RDP_REQUIRE((size_t)H * W < (1ull << 31) / 4, RDP_ERR_UNSUPPORTED, "rdp_geom_curvature: frame too large");
-  RDP_REQUIRE(depth_fmt >= RDP_DEPTH_U16 && depth_fmt <= RDP_DEPTH_F32_WIDE, RDP_ERR_BAD_ARGUMENT,
+  RDP_REQUIRE(depth_fmt >= RDP_DEPTH_U16 && depth_fmt <= RDP_DEPTH_F64, RDP_ERR_BAD_ARGUMENT,
               "rdp_geom_curvature: unknown depth format %d", depth_fmt);
   RDP_REQUIRE(out->mean_curvature && out->max_curvature && out->spline_points && out->status, RDP_ERR_BAD_ARGUMENT,
               "rdp_geom_curvature: mean/max/spline_points/status outputs are required");
@@ -2017,7 +2059,7 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   mark();
   RDP_CUDA_TRY(cudaMemsetAsync(workspace, 0, pl.header_bytes, stream));
   mark();
-  const bool vec = (p.P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
+  const bool vec = depth_fmt != RDP_DEPTH_F64 && (p.P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
   const int tiles_total = B * pl.tiles;
   if (vec) k_deproject<true><<<tiles_total, DP_THREADS, 0, stream>>>(p);
   else k_deproject<false><<<tiles_total, DP_THREADS, 0, stream>>>(p);
@@ -2035,14 +2077,14 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
   mark();
-  static const int knots_debug = getenv("RDP_DEBUG_KNOTS") ? atoi(getenv("RDP_DEBUG_KNOTS")) : 0;  // phase cycle counts
+  static const int knots_debug = dev_env("RDP_DEBUG_KNOTS") ? atoi(dev_env("RDP_DEBUG_KNOTS")) : 0;  // phase cycle counts
   // One CTA per frame and 255 registers per thread: 256 threads fill an SM's register file.  With more frames than SMs,
   // 128 threads per CTA put two frames on an SM; the parallel phases take longer, the serial chains (most of the time)
   // do not, so the batch finishes in about one CTA lifetime instead of two.
   int n_sm = 148, dev_id = 0;
   RDP_CUDA_TRY(cudaGetDevice(&dev_id));
   RDP_CUDA_TRY(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev_id));
-  static const int knots_threads_env = getenv("RDP_KNOTS_THREADS") ? atoi(getenv("RDP_KNOTS_THREADS")) : 0;  // 128 or 256 (A/B)
+  static const int knots_threads_env = dev_env("RDP_KNOTS_THREADS") ? atoi(dev_env("RDP_KNOTS_THREADS")) : 0;  // 128 or 256 (A/B)
   const int kn_threads = knots_threads_env == 128 || knots_threads_env == 256 ? knots_threads_env : (B > n_sm ? 128 : KN_THREADS);
   k_fit_knots<<<B, kn_threads, 0, stream>>>(p, kn, pl.ecap + 8, knots_debug);  // exits at once for frames that need no extra knots
   mark();
@@ -2130,7 +2172,7 @@ extern "C" int rdp_geom_deproject_static(const uint8_t* mask, const void* depth,
               "rdp_geom_deproject_static: null pointer");
   RDP_REQUIRE(B > 0 && H > 0 && W > 0, RDP_ERR_BAD_ARGUMENT, "rdp_geom_deproject_static: bad shape %dx%dx%d", B, H, W);
   RDP_REQUIRE((size_t)H * W < (1ull << 31) / 4, RDP_ERR_UNSUPPORTED, "rdp_geom_deproject_static: frame too large");
-  RDP_REQUIRE(depth_fmt >= RDP_DEPTH_U16 && depth_fmt <= RDP_DEPTH_F32_WIDE, RDP_ERR_BAD_ARGUMENT,
+  RDP_REQUIRE(depth_fmt >= RDP_DEPTH_U16 && depth_fmt <= RDP_DEPTH_F64, RDP_ERR_BAD_ARGUMENT,
               "rdp_geom_deproject_static: unknown depth format %d", depth_fmt);
   const int P = H * W;
   const int tiles = (P + TILE_PX - 1) / TILE_PX;
@@ -2139,6 +2181,19 @@ extern "C" int rdp_geom_deproject_static(const uint8_t* mask, const void* depth,
               "%d tiles of 16384 pixels per call); use rdp_geom_curvature with a workspace for larger batches",
               B, tiles, STATIC_MAX_FRAMES, STATIC_MAX_TILES);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  // The scratch address is looked up for the CURRENT device; a stream that belongs to another device would make the
+  // memsets below and the kernels disagree about which GPU's array they touch.  Refuse before anything is issued.
+  if (stream != nullptr && stream != cudaStreamLegacy && stream != cudaStreamPerThread) {
+    int cur = -1, sdev = -1;
+    RDP_CUDA_TRY(cudaGetDevice(&cur));
+    if (cudaStreamGetDevice(stream, &sdev) == cudaSuccess) {
+      RDP_REQUIRE(sdev == cur, RDP_ERR_BAD_ARGUMENT,
+                  "rdp_geom_deproject_static: the stream belongs to device %d but device %d is current; make the stream's "
+                  "device current before every call", sdev, cur);
+    } else {
+      (void)cudaGetLastError();  // older drivers: the check is advisory
+    }
+  }
   void* scratch = nullptr;
   const int rc = static_scratch_address(&scratch);
   if (rc != RDP_OK) return rc;
@@ -2162,7 +2217,7 @@ extern "C" int rdp_geom_deproject_static(const uint8_t* mask, const void* depth,
   p.scale_f32 = (float)depth_scale;
   p.pix = pixel_ids;
   p.out.points_xyz = points_xyz;
-  const bool vec = (P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
+  const bool vec = depth_fmt != RDP_DEPTH_F64 && (P % 16 == 0) && ((uintptr_t)mask % 16 == 0) && ((uintptr_t)depth % 16 == 0);
   if (vec) k_deproject<true><<<B * tiles, DP_THREADS, 0, stream>>>(p);
   else k_deproject<false><<<B * tiles, DP_THREADS, 0, stream>>>(p);
   k_export_counts<<<(B + 63) / 64, 64, 0, stream>>>(p.fs, B, n_points);

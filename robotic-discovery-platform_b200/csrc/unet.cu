@@ -1,20 +1,25 @@
 // U-Net forward on sm_100a: replaces UNet.forward of the reference (pkg/segmentation_model.py:109-120) plus the
 // server's mask rule (services/vision_analysis/server.py:124).
 //
-// Activations live in HBM as NHWC bf16.  Every 3x3 convolution (+ folded eval-BatchNorm + ReLU) is one launch of
-// `k_conv3x3`, an implicit GEMM on the 5th-generation tensor cores:
-//   * M = a 128-pixel spatial patch (tile_h x tile_w) of one frame, N = 64..256 output channels, K = 9 taps x Cin;
-//   * per K-step (one tap, 64 input channels) TMA loads the patch shifted by the tap offset from a 4-D NHWC tensor
-//     map - out-of-bounds pixels are zero-filled by the TMA unit, which *is* the convolution padding - and the
-//     matching 64-wide slice of the packed weights, both with 128-byte swizzle, into a ring of shared-memory stages;
-//   * one thread issues tcgen05.mma (bf16 x bf16 -> fp32) into a TMEM accumulator; two accumulator stages let the
-//     epilogue of tile i overlap the MMAs of tile i+1 (persistent CTAs, static round-robin over tiles);
-//   * four epilogue warps read TMEM (tcgen05.ld), add the BN shift, apply ReLU and store bf16 NHWC; for the last
-//     layer they also apply the 1x1 OutConv, and write fp32 logits and/or the thresholded mask;
+// Activations live in HBM as NHWC bf16.  Every 3x3 convolution (+ folded eval-BatchNorm + ReLU) is one launch of an
+// implicit GEMM on the 5th-generation tensor cores (`k_conv3x3_halo`; `k_conv_first` for inc.0; `k_conv3x3` is the
+// per-tap fallback):
+//   * M = a 128-pixel spatial patch of one frame, N = 64..256 output channels, K = 9 taps x Cin;
+//   * TMA loads one (tile + halo) box per 64 input channels from a 4-D NHWC tensor map - out-of-bounds pixels are
+//     zero-filled by the TMA unit, which *is* the convolution padding - and the 9 taps address it in place through
+//     shifted shared-memory descriptors; weight slices are resident or streamed, all with 128-byte swizzle;
+//   * one elected thread issues tcgen05.mma (bf16 x bf16 -> fp32) into double-buffered TMEM accumulators, so the
+//     epilogue of tile i overlaps the MMAs of tile i+1 (persistent CTAs, static round-robin over tiles);
+//   * epilogue warps read TMEM (tcgen05.ld), add the BN shift, apply ReLU and store bf16 NHWC; MaxPool2d(2) leaves as
+//     a second, pooled output of the same epilogue; the last layer applies the 1x1 OutConv there as well and writes
+//     fp32 logits and/or the thresholded mask;
 //   * skip connections are read in place: the K loop takes its first channel blocks from the skip tensor and the
-//     rest from the upsampled tensor (two tensor maps), so `torch.cat` never materialises.
-// Pooling, bilinear upsampling (align_corners=True, position-dependent weights) and the first layer's im2col are
-// separate bandwidth-bound kernels in this round.
+//     rest from the up-sampled branch, so `torch.cat` never materialises; the bilinear x2 up-sampling
+//     (align_corners=True, position-dependent weights) is done by interpolation warps inside the convolution that
+//     consumes it, straight into the swizzled operand tile;
+//   * inc.0 (3 input channels) gathers its 3x3 neighbourhoods from the uint8 image inside the kernel (no im2col in HBM).
+// Development switches (environment variables that change kernel selection or skip work) exist only in builds with
+// -DRDP_DEVELOPMENT; the shipped library ignores them.
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdarg.h>
@@ -22,10 +27,23 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
+#include <set>
+#include <utility>
 
 #include "rdp_common.cuh"
 #include "sm100_ptx.cuh"
+
+// Development switches are compiled out of the shipped library: an environment variable must never change what a
+// server computes.  Build with -DRDP_DEVELOPMENT (RDP_DEVELOPMENT=1 python rdp_b200/build.py --force) to get them.
+#ifdef RDP_DEVELOPMENT
+#define RDP_DEV(...) __VA_ARGS__
+static inline const char* dev_env(const char* name) { return getenv(name); }
+#else
+#define RDP_DEV(...)
+static inline const char* dev_env(const char*) { return nullptr; }
+#endif
 
 namespace rdp {
 namespace unet {
@@ -397,7 +415,7 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
   const int ncb = p.kb0 + p.kb1;
   uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
   const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
-  long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64(), t0;
+  RDP_DEV(long long w_acc = 0, w_a = 0, w_b = 0, t_begin = clock64(), t0;)
   if (RESIDENT) {
     mbar_wait(w_full, 0);
     tc_fence_after();
@@ -407,15 +425,15 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
 #pragma unroll
     for (int as = 0; as < 2; ++as) {
       if (work < p.total_work) {
-        t0 = clock64();
+        RDP_DEV(t0 = clock64();)
         mbar_wait(&acc_empty[as], aphase ^ 1);
-        w_acc += clock64() - t0;
+        RDP_DEV(w_acc += clock64() - t0;)
         tc_fence_after();
         const uint32_t tmem_acc = BASE0 ? (uint32_t)(as * TILES * BN) : tmem_base + as * TILES * BN;
         for (int cb = 0; cb < ncb; ++cb) {
-          t0 = clock64();
+          RDP_DEV(t0 = clock64();)
           mbar_wait(&full_a[sa], pa);
-          w_a += clock64() - t0;
+          RDP_DEV(w_a += clock64() - t0;)
           tc_fence_after();
           const uint32_t a_lo = a_lo0 + sa * (halo_stride(TILES) >> 4);
           const uint32_t bres_lo = b_lo0 + cb * (9 * B_BLOCK >> 4);
@@ -425,9 +443,9 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
             if (RESIDENT) {
               b_lo = bres_lo + tap * (B_BLOCK >> 4);
             } else {
-              t0 = clock64();
+              RDP_DEV(t0 = clock64();)
               mbar_wait(&full_b[sb], pb);
-              w_b += clock64() - t0;
+              RDP_DEV(w_b += clock64() - t0;)
               tc_fence_after();
               b_lo = b_lo0 + sb * (B_BLOCK >> 4);
             }
@@ -453,9 +471,9 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
     }
     aphase ^= 1;
   }
-  if (p.debug_waits && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
+  RDP_DEV(if (p.debug_waits && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
     printf("  mma thread: total %lld cyc, waiting acc_empty %lld, full_a %lld, full_b %lld (BN %d tiles %d resident %d)\n",
-           clock64() - t_begin, w_acc, w_a, w_b, BN, TILES, (int)RESIDENT);
+           clock64() - t_begin, w_acc, w_a, w_b, BN, TILES, (int)RESIDENT);)
 }
 
 // interpolation warps: 8 where a block's MMA time is short (64-wide layers) or its halo large (super-tiles), else 4
@@ -672,8 +690,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     const int group = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
-    long long epi_wait = 0;
-    const long long epi_begin = clock64();
+    RDP_DEV(long long epi_wait = 0; const long long epi_begin = clock64();)
     int it = 0;
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
       if (EG > 1 && (it % EG) != group) continue;
@@ -684,9 +701,9 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       const int ty = m % p.tiles_y;
       const int n = m / p.tiles_y;
       const int y = ty * 16 + (row >> 3);
-      const long long e0 = clock64();
+      RDP_DEV(const long long e0 = clock64();)
       mbar_wait(&acc_full[as], aphase);
-      epi_wait += clock64() - e0;
+      RDP_DEV(epi_wait += clock64() - e0;)
       tc_fence_after();
 #pragma unroll
       for (int h = 0; h < TILES; ++h) {
@@ -696,8 +713,8 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         epilogue_tile<BN, true>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
       }
     }
-    if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
-      printf("  epilogue warp: total %lld cyc, waiting acc_full %lld\n", clock64() - epi_begin, epi_wait);
+    RDP_DEV(if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
+      printf("  epilogue warp: total %lld cyc, waiting acc_full %lld\n", clock64() - epi_begin, epi_wait);)
   }
 
   tc_fence_before();
@@ -845,16 +862,15 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
       const uint64_t db = make_sw128_desc(smem_u32(smem_b));
       uint32_t as = 0, aphase = 0;
       int it = 0;
-      long long w_acc = 0, w_a = 0, t_begin = clock64(), t0;
+      RDP_DEV(long long w_acc = 0, w_a = 0, t_begin = clock64(), t0;)
       for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
         const int stage = it % FIRST_STAGES;
         const uint32_t phase = (uint32_t)(it / FIRST_STAGES) & 1u;
-        t0 = clock64();
+        RDP_DEV(t0 = clock64();)
         mbar_wait(&acc_empty[as], aphase ^ 1);
-        w_acc += clock64() - t0;
-        t0 = clock64();
+        RDP_DEV(w_acc += clock64() - t0; t0 = clock64();)
         mbar_wait(&a_full[stage], phase);
-        w_a += clock64() - t0;
+        RDP_DEV(w_a += clock64() - t0;)
         tc_fence_after();
         const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * A_STAGE_BYTES));
 #pragma unroll
@@ -863,9 +879,9 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
         tc_commit(&acc_full[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      if (p.debug_waits && blockIdx.x == 0)
+      RDP_DEV(if (p.debug_waits && blockIdx.x == 0)
         printf("first layer mma thread: total %lld cyc, waiting acc_empty (epilogue) %lld, a_full (producers) %lld\n",
-               clock64() - t_begin, w_acc, w_a);
+               clock64() - t_begin, w_acc, w_a);)
     }
   } else {
     // ================= epilogue: TMEM -> shift, ReLU, bf16 -> swizzled smem tile -> one TMA store =================
@@ -1171,12 +1187,26 @@ static int log2_exact(int v) {  // shift for a power of two, -1 otherwise
 using namespace rdp;
 using namespace rdp::unet;
 
+// Encoded tensor maps of one (workspace, shape) pair, in the order forward_impl asks for them.
+struct MapSet {
+  const void* ws = nullptr;
+  int B = 0, H = 0, W = 0, keep = 0, n = 0;
+  unsigned long long stamp = 0;
+  CUtensorMap maps[40];
+};
+constexpr int MAP_CACHE_ENTRIES = 8;
+
 struct RdpUnet {
   RdpUnetWeights w;
   CUtensorMap wmap[18];
   int bn[18];
   int cin_pad[18];
   int num_sms;
+  // The handle's parameters never change after creation; this cache of activation tensor maps (about 40
+  // cuTensorMapEncodeTiled calls per forward otherwise) is the only mutable part and has its own lock.
+  mutable std::mutex map_mu;
+  mutable unsigned long long map_clock = 0;
+  mutable MapSet map_cache[MAP_CACHE_ENTRIES];
 };
 
 namespace {
@@ -1193,29 +1223,85 @@ struct Buffers {
 
 const int kConvLevel[18] = {0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
 
-Buffers carve_unet(const RdpUnet* net, void* ws, int B, int H, int W) {
+// keep_all: every buffer has its own storage (rdp_unet_read_activation can then read any layer afterwards).
+// Otherwise buffers whose lifetimes do not overlap share storage.  Time runs in half steps: conv i launches at 2i, the
+// stand-alone up-sampling kernel of Up block j at 2(10+2j)-1, the im2col fallback at -1; a buffer lives from the launch
+// that writes it to the last launch that reads it, and two buffers may share bytes only if those closed intervals are
+// disjoint.  Largest first, lowest free offset: x1 (live from inc.3 to up4.0) ends up at the bottom, and the peak is
+// x1 + up4's two inputs + its output, about 30 % of the keep_all size.
+Buffers carve_unet(const RdpUnet* net, void* ws, int B, int H, int W, bool keep_all) {
   Buffers b;
   b.lv[0] = {H, W};
   for (int i = 1; i < 5; ++i) b.lv[i] = {b.lv[i - 1].H / 2, b.lv[i - 1].W / 2};
-  Carver c(ws);
   auto px = [&](int l) { return (size_t)B * b.lv[l].H * b.lv[l].W; };
-  b.col = c.take<__nv_bfloat16>(px(0) * 64);
-  for (int i = 0; i < 18; ++i) b.act[i] = c.take<__nv_bfloat16>(px(kConvLevel[i]) * net->w.conv[i].cout);
-  for (int i = 0; i < 4; ++i) b.pool[i] = c.take<__nv_bfloat16>(px(i + 1) * net->w.conv[2 * i + 1].cout);
+  struct Span { size_t bytes, off; int t0, t1; __nv_bfloat16** slot; };
+  Span sp[27];
+  int n = 0;
+  auto add = [&](__nv_bfloat16** slot, size_t elems, int t0, int t1) { sp[n++] = {align_up(elems * 2, 256), 0, t0, t1, slot}; };
+  add(&b.col, px(0) * 64, -1, 0);
+  static const int last_read[18] = {2, 32, 6, 28, 10, 24, 14, 20, 18, 20, 22, 24, 26, 28, 30, 32, 34, 35};
+  for (int i = 0; i < 18; ++i) add(&b.act[i], px(kConvLevel[i]) * net->w.conv[i].cout, 2 * i, last_read[i]);
+  for (int i = 0; i < 4; ++i) add(&b.pool[i], px(i + 1) * net->w.conv[2 * i + 1].cout, 2 * (2 * i + 1), 2 * (2 * i + 2));
   // up[j] feeds conv 10+2j: channels = cout of the layer below (conv 9+2j), spatial = skip level 3-j
-  for (int j = 0; j < 4; ++j) b.up[j] = c.take<__nv_bfloat16>(px(3 - j) * net->w.conv[9 + 2 * j].cout);
-  b.bytes = c.total();
+  for (int j = 0; j < 4; ++j) add(&b.up[j], px(3 - j) * net->w.conv[9 + 2 * j].cout, 2 * (10 + 2 * j) - 1, 2 * (10 + 2 * j));
+  size_t total = 0;
+  if (keep_all) {
+    for (int i = 0; i < n; ++i) {
+      sp[i].off = total;
+      total += sp[i].bytes;
+    }
+  } else {
+    int order[27];
+    for (int i = 0; i < n; ++i) order[i] = i;
+    std::stable_sort(order, order + n, [&](int a, int c) { return sp[a].bytes > sp[c].bytes; });
+    bool placed[27] = {};
+    for (int oi = 0; oi < n; ++oi) {
+      Span& cur = sp[order[oi]];
+      size_t off = 0;
+      for (bool moved = true; moved;) {  // lowest offset not overlapping a placed buffer that is live at the same time
+        moved = false;
+        for (int k = 0; k < n; ++k) {
+          const Span& o = sp[k];
+          if (!placed[k] || o.t1 < cur.t0 || cur.t1 < o.t0) continue;
+          if (off < o.off + o.bytes && o.off < off + cur.bytes) {
+            off = o.off + o.bytes;
+            moved = true;
+          }
+        }
+      }
+      cur.off = off;
+      placed[order[oi]] = true;
+      total = std::max(total, off + cur.bytes);
+    }
+  }
+  for (int i = 0; i < n; ++i) *sp[i].slot = ws ? reinterpret_cast<__nv_bfloat16*>(static_cast<char*>(ws) + sp[i].off) : nullptr;
+  b.bytes = total;
   return b;
 }
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a property of the (kernel, device) pair: a process that drives several
+// GPUs (threads instead of one process per GPU) needs it set on each of them, and two first calls may race.
+int ensure_dyn_smem(const void* kernel, int bytes) {
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  int dev = 0;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> guard(mu);
+  if (done.count({kernel, dev})) return RDP_OK;
+  RDP_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+  done.insert({kernel, dev});
+  return RDP_OK;
+}
+#define RDP_TRY_RC(expr)            \
+  do {                              \
+    const int _rc = (expr);         \
+    if (_rc != RDP_OK) return _rc;  \
+  } while (0)
 
 template <int BN>
 int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms,
                    cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ConvCfg<BN>::SMEM_BYTES));
-    attr_set = true;
-  }
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3<BN>), (int)ConvCfg<BN>::SMEM_BYTES));
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
   k_conv3x3<BN><<<grid, CONV_THREADS, ConvCfg<BN>::SMEM_BYTES, stream>>>(s0, s1, wm, p);
   return RDP_OK;
@@ -1224,11 +1310,7 @@ int launch_conv_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorM
 template <int C, bool U8>
 int launch_conv_first_t(const CUtensorMap& wm, const CUtensorMap& om, const ConvParams& p, const void* in, int num_sms,
                         cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv_first<C, U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, FIRST_SMEM));
-    attr_set = true;
-  }
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv_first<C, U8>), FIRST_SMEM));
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
   k_conv_first<C, U8><<<grid, FIRST_THREADS, FIRST_SMEM, stream>>>(wm, om, p, in);
   return RDP_OK;
@@ -1251,11 +1333,7 @@ int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const CUtensorMap& 
 template <int BN, bool RESIDENT, bool INTERP, int TILES>
 int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p,
                        const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_conv3x3_halo<BN, RESIDENT, INTERP, TILES>, cudaFuncAttributeMaxDynamicSharedMemorySize, HALO_SMEM_TOTAL));
-    attr_set = true;
-  }
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3_halo<BN, RESIDENT, INTERP, TILES>), HALO_SMEM_TOTAL));
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
   k_conv3x3_halo<BN, RESIDENT, INTERP, TILES><<<grid, conv_threads(INTERP, BN, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
   return RDP_OK;
@@ -1263,7 +1341,7 @@ int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUten
 
 // Super-tiles (two 8x16 tiles per work item) pay off where weights stream from L2 and two accumulator pairs fit TMEM.
 inline int halo_tiles_for(int bn, int n_tiles, int ncb, bool interp) {
-  static const int env = getenv("RDP_HALO_TILES") ? atoi(getenv("RDP_HALO_TILES")) : 0;
+  static const int env = dev_env("RDP_HALO_TILES") ? atoi(dev_env("RDP_HALO_TILES")) : 0;
   if (env == 1) return 1;
   const int budget = HALO_SMEM_TOTAL - 1024 - HALO_BAR_BYTES - aux_bytes(bn * n_tiles, false) - (interp ? patch_stride(1) : 0);
   const bool resident = n_tiles == 1 && 9 * ncb * bn * BLOCK_K * 2 + 3 * halo_stride(1) <= budget;
@@ -1278,7 +1356,7 @@ int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtenso
   // everything but the rings: alignment slack, barriers, epilogue constants, one source-patch stage when fused
   const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(p.cout, p.head_w != nullptr) + (p.low ? patch_stride(tiles) : 0);
   int budget = HALO_SMEM_TOTAL - fixed;
-  static const int env_sa = getenv("RDP_HALO_SA") ? atoi(getenv("RDP_HALO_SA")) : 0;
+  static const int env_sa = dev_env("RDP_HALO_SA") ? atoi(dev_env("RDP_HALO_SA")) : 0;
   HaloCfg cfg{};
   cfg.sl = 1;
   const int w_bytes = 9 * ncb * b_block;
@@ -1356,11 +1434,15 @@ extern "C" void rdp_unet_destroy(RdpUnet* net) { delete net; }
 
 extern "C" int rdp_unet_launch_count(const RdpUnet*) { return 1 + 18 + 4 + 4; }
 
-extern "C" int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W, size_t* bytes) {
+extern "C" int rdp_unet_workspace_bytes_ex(const RdpUnet* net, int in_fmt_flags, int B, int H, int W, size_t* bytes) {
   RDP_REQUIRE(net && bytes, RDP_ERR_BAD_ARGUMENT, "rdp_unet_workspace_bytes: null argument");
   RDP_REQUIRE(B > 0 && H >= 16 && W >= 16, RDP_ERR_BAD_ARGUMENT, "rdp_unet_workspace_bytes: bad shape %dx%dx%d (H, W >= 16)", B, H, W);
-  *bytes = carve_unet(net, nullptr, B, H, W).bytes;
+  *bytes = carve_unet(net, nullptr, B, H, W, (in_fmt_flags & RDP_IN_FLAG_KEEP_ACTIVATIONS) != 0).bytes;
   return RDP_OK;
+}
+
+extern "C" int rdp_unet_workspace_bytes(const RdpUnet* net, int B, int H, int W, size_t* bytes) {
+  return rdp_unet_workspace_bytes_ex(net, 0, B, H, W, bytes);
 }
 
 static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B, int H, int W, float* logits,
@@ -1372,19 +1454,45 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   RDP_REQUIRE(in_fmt == RDP_IN_RGB_U8_NHWC || in_fmt == RDP_IN_F32_NCHW, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: unknown input format %d", in_fmt);
   RDP_REQUIRE(B > 0 && H >= 16 && W >= 16, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: bad shape %dx%dx%d (H, W >= 16)", B, H, W);
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const Buffers buf = carve_unet(net, workspace, B, H, W);
+  const Buffers buf = carve_unet(net, workspace, B, H, W, keep_all);
   RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_forward: workspace %zu < required %zu bytes", workspace_bytes, buf.bytes);
   RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_forward: workspace must be 256-byte aligned");
 
-  static const bool debug_waits = getenv("RDP_DEBUG_WAITS") != nullptr;  // development aid, see ConvParams::debug_waits
-  static const bool debug_nohead = getenv("RDP_DEBUG_NOHEAD") != nullptr;    // timing experiments only
-  static const bool debug_nostore = getenv("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
-  static const bool no_fuse_pool = getenv("RDP_NO_FUSE_POOL") != nullptr;  // development switch: separate pooling kernel
-  static const bool fuse_up4 = getenv("RDP_FUSE_UP4") != nullptr;  // development switch: fuse up4's upsample as well
-  static const bool no_fuse_up = getenv("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
-  static const bool force_v1 = getenv("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
+  // Activation tensor maps depend on the workspace address and the shape only: encode them once per (workspace, shape)
+  // and replay them, in call order, on later forwards (the batch-1 server loop calls with the same pair every frame).
+  MapSet maps;
+  bool maps_cached = false;
+  {
+    std::lock_guard<std::mutex> guard(net->map_mu);
+    for (MapSet& e : net->map_cache)
+      if (e.n > 0 && e.ws == workspace && e.B == B && e.H == H && e.W == W && e.keep == (int)keep_all) {
+        e.stamp = ++net->map_clock;
+        maps = e;
+        maps_cached = true;
+        break;
+      }
+  }
+  int map_cursor = 0;
+  // returns the next map of the sequence: replayed when cached, otherwise built by `make` and recorded
+  auto next_map = [&](const CUtensorMap** out, auto make) -> int {
+    if (map_cursor >= (int)(sizeof(maps.maps) / sizeof(maps.maps[0]))) {
+      set_error("rdp_unet_forward: tensor-map table overflow");
+      return RDP_ERR_CUDA;
+    }
+    CUtensorMap* m = &maps.maps[map_cursor++];
+    *out = m;
+    return maps_cached ? RDP_OK : make(m);
+  };
+
+  static const bool debug_waits = dev_env("RDP_DEBUG_WAITS") != nullptr;  // development aid, see ConvParams::debug_waits
+  static const bool debug_nohead = dev_env("RDP_DEBUG_NOHEAD") != nullptr;    // timing experiments only
+  static const bool debug_nostore = dev_env("RDP_DEBUG_NOSTORE") != nullptr;  // timing experiments only: results are garbage
+  static const bool no_fuse_pool = dev_env("RDP_NO_FUSE_POOL") != nullptr;  // development switch: separate pooling kernel
+  static const bool fuse_up4 = dev_env("RDP_FUSE_UP4") != nullptr;  // development switch: fuse up4's upsample as well
+  static const bool no_fuse_up = dev_env("RDP_NO_FUSE_UP") != nullptr;  // development switch: separate upsample kernel
+  static const bool force_v1 = dev_env("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
-  static const char* sel_env = getenv("RDP_CONV_SEL");
+  static const char* sel_env = dev_env("RDP_CONV_SEL");
   const char* sel = (sel_env && strlen(sel_env) == 18) ? sel_env : "1hhhhhhhhhhhhhhhhh";
   auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
   int n_marks = 0;
@@ -1409,10 +1517,10 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.out = debug_nostore ? nullptr : buf.act[0];
     int rc = RDP_OK;
     mark();  // (slot of the im2col launch)
-    CUtensorMap omap;
-    rc = make_act_map(&omap, buf.act[0], B, H, W, 64, p.tile_w, p.tile_h);
+    const CUtensorMap* omap = nullptr;
+    rc = next_map(&omap, [&](CUtensorMap* m) { return make_act_map(m, buf.act[0], B, H, W, 64, p.tile_w, p.tile_h); });
     if (rc != RDP_OK) return rc;
-    if (launch_conv_first(net->w.n_channels, in_fmt == RDP_IN_RGB_U8_NHWC, net->wmap[0], omap, p, input, net->num_sms, stream, &rc)) {
+    if (launch_conv_first(net->w.n_channels, in_fmt == RDP_IN_RGB_U8_NHWC, net->wmap[0], *omap, p, input, net->num_sms, stream, &rc)) {
       if (rc != RDP_OK) return rc;
       first_fused = true;
       mark();
@@ -1466,13 +1574,16 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       p.ry = 2 * low->h > 1 ? (float)(low->h - 1) / (float)(2 * low->h - 1) : 0.f;
       p.rx = 2 * low->w > 1 ? (float)(low->w - 1) / (float)(2 * low->w - 1) : 0.f;
     }
-    CUtensorMap m0, m1;
+    const CUtensorMap *pm0 = nullptr, *pm1 = nullptr;
     const int box_w = halo ? halo_w(tiles) : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
-    int rc = make_act_map(&m0, src0, B, L.H, L.W, c0, box_w, box_h);
+    int rc = next_map(&pm0, [&](CUtensorMap* m) { return make_act_map(m, src0, B, L.H, L.W, c0, box_w, box_h); });
     if (rc != RDP_OK) return rc;
-    if (low) rc = make_act_map(&m1, low->ptr, B, low->h, low->w, c1, patch_w(tiles), PATCH_H, /*swizzle=*/false);
-    else rc = make_act_map(&m1, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
+    rc = next_map(&pm1, [&](CUtensorMap* m) {
+      if (low) return make_act_map(m, low->ptr, B, low->h, low->w, c1, patch_w(tiles), PATCH_H, /*swizzle=*/false);
+      return make_act_map(m, src1 ? src1 : src0, B, L.H, L.W, src1 ? c1 : c0, box_w, box_h);
+    });
     if (rc != RDP_OK) return rc;
+    const CUtensorMap &m0 = *pm0, &m1 = *pm1;
     if (halo) {
       switch (net->bn[i]) {
         case 64: rc = launch_conv_halo<64>(m0, m1, net->wmap[i], p, tiles, net->num_sms, stream); break;
@@ -1530,7 +1641,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       const LowSrc low{buf.act[low_i], Ll.H, Ll.W, dy / 2, dx / 2};
       RDP_TRY(conv(10 + 2 * j, buf.act[skip_i], Cs, nullptr, Cl, 9, &low));
     } else {
-      static const bool ups_v1 = getenv("RDP_UPSAMPLE_V1") != nullptr;  // the one-output-per-thread kernel (A/B, cross-check)
+      static const bool ups_v1 = dev_env("RDP_UPSAMPLE_V1") != nullptr;  // the one-output-per-thread kernel (A/B, cross-check)
       const int sh = log2_exact(C8);
       if (ups_v1 || sh < 0 || C8 > 256) {
         k_upsample2x<<<dim3((Ls.W * C8 + 255) / 256, Ls.H, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, sh, Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
@@ -1548,6 +1659,22 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   }
 #undef RDP_TRY
   RDP_CUDA_TRY(cudaGetLastError());
+  if (!maps_cached) {  // remember this (workspace, shape): least recently used entry goes
+    maps.ws = workspace; maps.B = B; maps.H = H; maps.W = W; maps.keep = (int)keep_all; maps.n = map_cursor;
+    std::lock_guard<std::mutex> guard(net->map_mu);
+    MapSet* victim = nullptr;
+    for (MapSet& e : net->map_cache)  // another thread may have stored the same key meanwhile
+      if (e.n > 0 && e.ws == workspace && e.B == B && e.H == H && e.W == W && e.keep == (int)keep_all) victim = &e;
+    for (MapSet& e : net->map_cache)
+      if (!victim && e.n == 0) victim = &e;
+    if (!victim) {
+      victim = &net->map_cache[0];
+      for (MapSet& e : net->map_cache)
+        if (e.stamp < victim->stamp) victim = &e;
+    }
+    maps.stamp = ++net->map_clock;
+    *victim = maps;
+  }
   return RDP_OK;
 }
 
@@ -1576,7 +1703,7 @@ extern "C" int rdp_unet_forward_profiled(const RdpUnet* net, const void* input, 
 extern "C" int rdp_unet_read_activation(const RdpUnet* net, int index, int B, int H, int W, const void* workspace,
                                         float* out_nchw, void* stream_) {
   RDP_REQUIRE(net && workspace && out_nchw && index >= 0 && index < 18, RDP_ERR_BAD_ARGUMENT, "rdp_unet_read_activation: bad argument");
-  const Buffers buf = carve_unet(net, const_cast<void*>(workspace), B, H, W);
+  const Buffers buf = carve_unet(net, const_cast<void*>(workspace), B, H, W, /*keep_all=*/true);
   const Level L = buf.lv[kConvLevel[index]];
   const int C = net->w.conv[index].cout;
   const size_t total = (size_t)B * C * L.H * L.W;

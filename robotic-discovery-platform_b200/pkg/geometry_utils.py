@@ -59,9 +59,16 @@ def compute_curvature_profiles(masks, depth_images, intrinsics, depth_scale) -> 
 
     if not torch.cuda.is_available():
         raise RuntimeError("compute_curvature_profile (rdp_b200) has no CPU path and no CUDA device is visible")
+    # `depth_image[v, u] * depth_scale` (`geometry_utils.py:105`) is computed in NumPy's promoted type: uint16 and float32
+    # images have kernels of their own; every other dtype (float64, signed or wider integers) promotes to float64, so it
+    # is widened to float64 on the host - exact for the integers, negative values stay negative and are dropped by z > 0.
+    if not isinstance(depth_images, torch.Tensor):
+        depth_images = np.asarray(depth_images)
+        if depth_images.dtype not in (np.uint16, np.float32):
+            depth_images = depth_images.astype(np.float64)
     m, d = to_dev(masks, True), to_dev(depth_images, False)
-    if d.dtype not in (torch.uint16, torch.float32):
-        d = d.to(torch.float32) if d.dtype.is_floating_point else d.to(torch.uint16)
+    if d.dtype not in (torch.uint16, torch.float32, torch.float64):
+        d = d.to(torch.float64)
     fmt = geometry.depth_format(d.dtype, depth_scale)
     r = geometry.curvature_batch(m, d, np.asarray(intrinsics, dtype=np.float64), depth_scale, depth_fmt=fmt)
     status = r.status.cpu().numpy()
@@ -71,7 +78,7 @@ def compute_curvature_profiles(masks, depth_images, intrinsics, depth_scale) -> 
 
 def compute_curvature_profile(mask: np.ndarray, depth_image: np.ndarray, intrinsics: np.ndarray,
                               depth_scale: float) -> CurvatureResult:
-    """mask (H,W) any dtype tested `> 0`, depth (H,W) uint16 or float32, K (3,3), scale -> `CurvatureResult`."""
+    """mask (H,W) any dtype tested `> 0`, depth (H,W) of any real dtype, K (3,3), scale -> `CurvatureResult`."""
     mask = np.asarray(mask)
     depth_image = np.asarray(depth_image)
     if mask.ndim != 2 or depth_image.shape != mask.shape:

@@ -8,8 +8,8 @@ Same class tree and parameter names as the reference (`pkg/segmentation_model.py
 
 The modules only *hold* parameters.  `UNet.forward` folds BatchNorm into bf16 weights (lazily, and again whenever a
 parameter changes) and runs the hand-written CUDA path; it needs `model.eval()` and a CUDA input, like the server
-provides (`server.py:83,121-123`).  Training-mode forward, CPU tensors and `bilinear=False` (which raises in the
-reference as well) raise instead of silently running something else.
+provides (`server.py:83,121-123`).  Training-mode forward and CPU tensors raise instead of silently running
+something else; `bilinear=False` constructs like the reference and raises in `forward` as it does there.
 """
 from __future__ import annotations
 
@@ -52,10 +52,14 @@ class Up(_ParameterHolder):
 
     def __init__(self, in_channels, out_channels, bilinear=True):
         super().__init__()
-        if not bilinear:
-            raise NotImplementedError("bilinear=False is not runnable in the reference either (channel mismatch in Up.forward)")
-        self.up = nn.Upsample(scale_factor=2, mode="bilinear", align_corners=True)
-        self.conv = DoubleConv(in_channels, out_channels, in_channels // 2)
+        if bilinear:
+            self.up = nn.Upsample(scale_factor=2, mode="bilinear", align_corners=True)
+            self.conv = DoubleConv(in_channels, out_channels, in_channels // 2)
+        else:
+            # Constructs like the reference (`segmentation_model.py:63-66`), so such a checkpoint still loads; its
+            # forward cannot run there either (the DoubleConv expects in_channels // 2, the concat has in_channels).
+            self.up = nn.ConvTranspose2d(in_channels, in_channels // 2, kernel_size=2, stride=2)
+            self.conv = DoubleConv(in_channels // 2, out_channels)
 
 
 class OutConv(_ParameterHolder):
@@ -76,10 +80,11 @@ class UNet(nn.Module):
         self.down1 = Down(64, 128)
         self.down2 = Down(128, 256)
         self.down3 = Down(256, 512)
-        self.down4 = Down(512, 512)
-        self.up1 = Up(1024, 256, bilinear)
-        self.up2 = Up(512, 128, bilinear)
-        self.up3 = Up(256, 64, bilinear)
+        factor = 2 if bilinear else 1
+        self.down4 = Down(512, 1024 // factor)
+        self.up1 = Up(1024, 512 // factor, bilinear)
+        self.up2 = Up(512, 256 // factor, bilinear)
+        self.up3 = Up(256, 128 // factor, bilinear)
         self.up4 = Up(128, 64, bilinear)
         self.outc = OutConv(64, n_classes)
 
@@ -109,7 +114,9 @@ class UNet(nn.Module):
         if self.training:
             raise RuntimeError("UNet (rdp_b200) runs inference only: call model.eval() first (server.py:83)")
         if not getattr(self, "bilinear", True):
-            raise NotImplementedError("bilinear=False is not runnable in the reference either")
+            # the reference raises here too, from up1's first convolution (`segmentation_model.py:65,75`)
+            raise RuntimeError("UNet(bilinear=False): Up.forward concatenates 1024 channels into a DoubleConv built for 512 "
+                               "(expected input to have 512 channels, but got 1024 channels instead)")
         if not x.is_cuda:
             raise RuntimeError("UNet (rdp_b200) has no CPU path: move the model and the input to a CUDA device")
 

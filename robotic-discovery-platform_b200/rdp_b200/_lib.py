@@ -10,13 +10,15 @@ LIB_PATH = os.path.join(os.path.dirname(HERE), "lib", "librdp_b200.so")
 
 OK = 0
 FRAME_OK, FRAME_TOO_FEW_POINTS, FRAME_DEGENERATE_BINS, FRAME_TOO_FEW_EDGE, FRAME_FIT_INVALID, FRAME_NEEDS_KNOTS = range(6)
-DEPTH_U16, DEPTH_F32, DEPTH_F32_WIDE = 0, 1, 2
+DEPTH_U16, DEPTH_F32, DEPTH_F32_WIDE, DEPTH_F64 = 0, 1, 2, 3
 IN_RGB_U8_NHWC, IN_F32_NCHW = 0, 1
 IN_FLAG_KEEP_ACTIVATIONS = 0x100
+FIT_FLAG_KNOT_TIE, FIT_FLAG_BRACKET_TIE, FIT_FLAG_NPLUS_TIE = 1, 2, 4
+ABI_VERSION = 2
 
 EXPORTS = [
     "rdp_abi_version", "rdp_last_error",
-    "rdp_unet_create", "rdp_unet_destroy", "rdp_unet_workspace_bytes", "rdp_unet_forward", "rdp_unet_launch_count",
+    "rdp_unet_create", "rdp_unet_destroy", "rdp_unet_workspace_bytes", "rdp_unet_workspace_bytes_ex", "rdp_unet_forward", "rdp_unet_launch_count",
     "rdp_unet_read_activation", "rdp_unet_forward_profiled",
     "rdp_geom_workspace_bytes", "rdp_geom_curvature", "rdp_geom_launch_count", "rdp_geom_curvature_profiled",
     "rdp_geom_deproject_static",
@@ -37,7 +39,7 @@ class CurvatureOut(C.Structure):
     _fields_ = [("mean_curvature", C.c_void_p), ("max_curvature", C.c_void_p), ("spline_points", C.c_void_p),
                 ("status", C.c_void_p), ("n_points", C.c_void_p), ("n_edge", C.c_void_p), ("fit_residual", C.c_void_p),
                 ("points_xyz", C.c_void_p), ("edge_pixels", C.c_void_p), ("bin_counts", C.c_void_p),
-                ("n_knots", C.c_void_p), ("fit_ier", C.c_void_p)]
+                ("n_knots", C.c_void_p), ("fit_ier", C.c_void_p), ("fit_flags", C.c_void_p)]
 
 
 class RdpError(RuntimeError):
@@ -61,11 +63,16 @@ def load() -> C.CDLL:
                            "(or rdp_b200/build.py); rdp_b200 has no CPU fallback")
         lib = C.CDLL(LIB_PATH)
         lib.rdp_abi_version.restype = C.c_int
+        if lib.rdp_abi_version() != ABI_VERSION:
+            raise RdpError(f"{LIB_PATH} has ABI version {lib.rdp_abi_version()}, this package needs {ABI_VERSION}: rebuild it "
+                           "(python __graft_entry__.py)")
         lib.rdp_last_error.restype = C.c_char_p
         lib.rdp_unet_create.argtypes = [C.POINTER(UnetWeights), C.POINTER(C.c_void_p)]
         lib.rdp_unet_destroy.argtypes = [C.c_void_p]
         lib.rdp_unet_destroy.restype = None
         lib.rdp_unet_workspace_bytes.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+        lib.rdp_unet_workspace_bytes_ex.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_size_t)]
+        lib.rdp_unet_workspace_bytes_ex.restype = C.c_int
         lib.rdp_unet_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                          C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
         lib.rdp_unet_launch_count.argtypes = [C.c_void_p]

@@ -105,9 +105,13 @@ def _gpu_runner(model, intrinsics, depth_scale, bgr: bool, size: int, device, wa
                 pngs = service.encode_mask_png(r.final_mask) if want_png else [None] * B   # a few KB per frame, not H*W
                 masks = r.final_mask.cpu().numpy() if want_mask else [None] * B
         finally:
-            lane.stream.synchronize()
-            for c in colors:
-                pool.free.put(c.slot)
+            # The slots must go back whatever happens: after a CUDA error the synchronize raises again, and a pool that
+            # never refills would leave every later request thread blocked in stage().
+            try:
+                lane.stream.synchronize()
+            finally:
+                for c in colors:
+                    pool.free.put(c.slot)
         t2 = time.perf_counter()
         out = [FrameResult(_to_result(int(status[i]), mean[i], mx[i], pts[i]), masks[i], float(cov[i]), B, pngs[i])
                for i in range(B)]
@@ -138,6 +142,7 @@ class MicroBatcher:
                                                                              want_mask, want_png, self.max_batch)
         self._q: "queue.Queue[Optional[_Request]]" = queue.Queue()
         self._closed = False
+        self._gate = threading.Lock()      # orders submit()'s enqueue against close()'s stop tokens
         self.batches_run, self.frames_run = 0, 0
         self._stats_lock = threading.Lock()
         self._threads = [threading.Thread(target=self._loop, name=f"rdp-microbatcher-{i}", daemon=True) for i in range(lanes)]
@@ -156,19 +161,26 @@ class MicroBatcher:
         stage = getattr(self._run, "stage", None)
         if stage is not None:                         # copy into pinned memory here, on the request thread
             color, depth = stage(color, depth), None
-        self._q.put(_Request(color, depth, fut, key))
+        with self._gate:                              # a request is either queued before the stop tokens or refused
+            if self._closed:
+                if stage is not None:
+                    color.pool.free.put(color.slot)
+                raise RuntimeError("MicroBatcher is closed")
+            self._q.put(_Request(color, depth, fut, key))
         return fut
 
     def analyze(self, color_image: np.ndarray, depth_image: np.ndarray, timeout: Optional[float] = None) -> FrameResult:
         return self.submit(color_image, depth_image).result(timeout)
 
     def close(self) -> None:
-        if not self._closed:
+        with self._gate:
+            if self._closed:
+                return
             self._closed = True
             for _ in self._threads:        # one stop token per lane; what was accepted before it is still served
                 self._q.put(None)
-            for t in self._threads:
-                t.join()
+        for t in self._threads:
+            t.join()
 
     def __enter__(self):
         return self

@@ -33,6 +33,7 @@ def _stale(target: str, deps) -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
+    """RDP_DEVELOPMENT=1 in the environment (with --force) compiles the development switches in (-DRDP_DEVELOPMENT)."""
     os.makedirs(LIB_DIR, exist_ok=True)
     os.makedirs(BUILD_DIR, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
@@ -45,7 +46,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(BUILD_DIR, src.replace(".cu", ".o"))
         objs.append(o)
         if force or _stale(o, [s] + headers):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o]
+            cmd = [nvcc, *NVCC_FLAGS, *(["-DRDP_DEVELOPMENT"] if os.environ.get("RDP_DEVELOPMENT") else []), "-c", s, "-o", o]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)

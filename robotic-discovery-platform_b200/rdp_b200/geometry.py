@@ -1,7 +1,7 @@
 """Batched curvature profile on the GPU through the C ABI (`rdp_geom_curvature`).
 
 Replaces `compute_curvature_profile` and its helpers (reference `pkg/geometry_utils.py:42-162`) for device tensors:
-masks (B,H,W) uint8, depth (B,H,W) uint16 | float32.  No CPU fallback.
+masks (B,H,W) uint8, depth (B,H,W) uint16 | float32 | float64.  No CPU fallback.
 """
 from __future__ import annotations
 
@@ -29,6 +29,7 @@ class CurvatureBatch:
     fit_residual: torch.Tensor     # (B,) f64
     n_knots: torch.Tensor = None   # (B,) i32, 8 = single cubic (FITPACK ier=-2), more = knot insertion + smoothing
     fit_ier: torch.Tensor = None   # (B,) i32, FITPACK's ier
+    fit_flags: torch.Tensor = None  # (B,) i32, rdp_b200._lib.FIT_FLAG_*: the fit took a decision inside rounding noise
     points_xyz: torch.Tensor | None = None    # (B,H*W,3) f32, first n_points rows valid
     edge_pixels: torch.Tensor | None = None   # (B,ecap) u32 as int32 view, first n_edge valid
     bin_counts: torch.Tensor | None = None    # (B,50) i32
@@ -41,7 +42,11 @@ def depth_format(depth_dtype, depth_scale) -> int:
         return _lib.DEPTH_U16
     if depth_dtype in (torch.float32, np.dtype(np.float32)):
         # Python float (weak scalar) keeps float32; a NumPy float64 scalar promotes the product to float64
-        return _lib.DEPTH_F32_WIDE if isinstance(depth_scale, np.floating) and not isinstance(depth_scale, np.float32) else _lib.DEPTH_F32
+        # (so does a 0-d float64 ndarray, which is what `np.load(...)['depth_scale']` gives, server.py:94-96)
+        wide = isinstance(depth_scale, (np.ndarray, np.generic)) and np.asarray(depth_scale).dtype == np.float64
+        return _lib.DEPTH_F32_WIDE if wide else _lib.DEPTH_F32
+    if depth_dtype in (torch.float64, np.dtype(np.float64)):
+        return _lib.DEPTH_F64
     raise _lib.RdpError(f"unsupported depth dtype {depth_dtype}")
 
 
@@ -80,6 +85,7 @@ def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_
             fit_residual=torch.empty(B, dtype=torch.float64, device=dev),
             n_knots=torch.zeros(B, dtype=torch.int32, device=dev),
             fit_ier=torch.zeros(B, dtype=torch.int32, device=dev),
+            fit_flags=torch.zeros(B, dtype=torch.int32, device=dev),
             workspace=workspace,
         )
         out = _lib.CurvatureOut()
@@ -88,6 +94,7 @@ def curvature_batch(masks: torch.Tensor, depth: torch.Tensor, intrinsics, depth_
         out.n_points, out.n_edge = res.n_points.data_ptr(), res.n_edge.data_ptr()
         out.fit_residual = res.fit_residual.data_ptr()
         out.n_knots, out.fit_ier = res.n_knots.data_ptr(), res.fit_ier.data_ptr()
+        out.fit_flags = res.fit_flags.data_ptr()
         if want_points:
             res.points_xyz = torch.empty((B, H * W, 3), dtype=torch.float32, device=dev)
             out.points_xyz = res.points_xyz.data_ptr()

@@ -73,13 +73,15 @@ class UnetEngine:
     def launches_per_forward(self) -> int:
         return self.lib.rdp_unet_launch_count(self._handle)
 
-    def workspace_bytes(self, B: int, H: int, W: int) -> int:
+    def workspace_bytes(self, B: int, H: int, W: int, keep_activations: bool = False) -> int:
+        """Bytes one forward needs: buffers with disjoint lifetimes share storage unless every activation is kept."""
         n = C.c_size_t()
-        _lib.check(self.lib.rdp_unet_workspace_bytes(self._handle, B, H, W, C.byref(n)), "rdp_unet_workspace_bytes")
+        flags = _lib.IN_FLAG_KEEP_ACTIVATIONS if keep_activations else 0
+        _lib.check(self.lib.rdp_unet_workspace_bytes_ex(self._handle, flags, B, H, W, C.byref(n)), "rdp_unet_workspace_bytes_ex")
         return n.value
 
-    def new_workspace(self, B: int, H: int, W: int) -> torch.Tensor:
-        return torch.empty(self.workspace_bytes(B, H, W), dtype=torch.uint8, device=self.device)
+    def new_workspace(self, B: int, H: int, W: int, keep_activations: bool = False) -> torch.Tensor:
+        return torch.empty(self.workspace_bytes(B, H, W, keep_activations), dtype=torch.uint8, device=self.device)
 
     LAUNCH_NAMES = (["im2col", "conv inc.0", "conv inc.3"]
                     + [f"{k} down{d}{s}" for d in range(1, 5) for k, s in (("maxpool", ""), ("conv", ".0"), ("conv", ".3"))]
@@ -103,7 +105,7 @@ class UnetEngine:
         if keep_activations:        # parity hook: read_activation(17) needs the last layer's output stored
             fmt |= _lib.IN_FLAG_KEEP_ACTIVATIONS
         with torch.cuda.device(self.device):
-            need = self.workspace_bytes(B, H, W)
+            need = self.workspace_bytes(B, H, W, keep_activations)
             if workspace is None or workspace.numel() < need:
                 workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
             logits = torch.empty((B, self.n_classes, H, W), dtype=torch.float32, device=self.device) if want_logits else None

@@ -19,6 +19,16 @@ def _run(frames, **kw):
     return r
 
 
+def _golden_frame(meta):
+    """The frame a golden case was generated from (round-2 cases may carry a staircase-edged mask, `stair`)."""
+    f = synth.make_frame(meta["seed"], meta["H"], meta["W"], meta["fill"], meta["depth"])
+    if meta.get("stair"):
+        from oracle import service_port as sp
+        n = meta["stair"]
+        f["mask_gt"] = np.ascontiguousarray(sp.upsize_mask_np(np.ascontiguousarray(f["mask_gt"][::n, ::n]), meta["H"], meta["W"]))
+    return f
+
+
 def _check_frame(r, i, f, curv_rtol=1e-9):
     o = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
     n = int(r.n_points[i])
@@ -83,24 +93,42 @@ def test_knot_insertion_regime_matches_reference(manifest, golden):
     """FITPACK's general branch (fp of the 8-knot cubic > s): knot count, ier and curvature vs the reference's values.
 
     The bar is 1e-3 relative (north_star); the kernel reproduces FITPACK's knot sequence exactly, so a far tighter
-    bound holds, including on the thousands-of-knots frame that SURVEY 0.6 expected to be chaotic.
+    bound holds - on the thousands-of-knots frames that SURVEY 0.6 expected to be chaotic (640x480 with 2039 knots,
+    1280x720 with 3942 and 5409), on staircase-edged (service-shaped) masks, and on uint16 depth, where the value on
+    file is the reference's own code run with its tie-dependent NumPy calls made deterministic (`ties: stable`,
+    `oracle/make_golden.py`).  A frame whose fit took a decision inside rounding noise says so in `fit_flags`; only
+    such a frame may leave the reference's knot sequence, and it is reported.
     """
-    from rdp_b200 import geometry
     cases = [(k, v) for k, v in manifest["cases"].items() if v["kind"] == "geometry" and v["n_knots"] != 8]
-    assert len(cases) >= 4
-    frames = [synth.make_frame(v["seed"], v["H"], v["W"], v["fill"], v["depth"]) for _, v in cases]
-    r = _run(frames)
-    for i, (name, meta) in enumerate(cases):
-        g = golden(name)
-        assert int(r.status[i]) == 0, name
-        rel_mean = abs(float(r.mean_curvature[i]) - meta["mean_curvature"]) / meta["mean_curvature"]
-        rel_max = abs(float(r.max_curvature[i]) - meta["max_curvature"]) / meta["max_curvature"]
-        print(f"{name}: knots {int(r.n_knots[i])} (ref {meta['n_knots']}), ier {int(r.fit_ier[i])}, "
-              f"rel err mean {rel_mean:.2e} max {rel_max:.2e}")
-        assert int(r.n_knots[i]) == meta["n_knots"] and int(r.fit_ier[i]) == meta["ier"], name
-        tight = 1e-8 if meta["n_knots"] <= 500 else 1e-6
-        assert rel_mean <= tight and rel_max <= tight, name
-        np.testing.assert_allclose(r.spline_points[i].cpu().numpy(), g["spline_points"], rtol=0, atol=1e-8)
+    assert len(cases) >= 10
+    assert any(v["H"] == 720 for _, v in cases) and any(v["depth"] == "u16" for _, v in cases)
+    flagged = []
+    for shape_key in sorted({(v["H"], v["W"], v["depth"]) for _, v in cases}):
+        group = [(k, v) for k, v in cases if (v["H"], v["W"], v["depth"]) == shape_key]
+        frames = [_golden_frame(v) for _, v in group]
+        r = _run(frames)
+        for i, (name, meta) in enumerate(group):
+            g = golden(name)
+            assert int(r.status[i]) == 0, name
+            assert int(r.n_points[i]) == meta["n_points"] and int(r.n_edge[i]) == meta["n_edge"], name
+            rel_mean = abs(float(r.mean_curvature[i]) - meta["mean_curvature"]) / meta["mean_curvature"]
+            rel_max = abs(float(r.max_curvature[i]) - meta["max_curvature"]) / meta["max_curvature"]
+            flags = int(r.fit_flags[i])
+            print(f"{name}: knots {int(r.n_knots[i])} (ref {meta['n_knots']}), ier {int(r.fit_ier[i])}, fit_flags {flags}, "
+                  f"rel err mean {rel_mean:.2e} max {rel_max:.2e}")
+            tight = 1e-8 if meta["n_knots"] <= 500 else 1e-6
+            exact = (int(r.n_knots[i]) == meta["n_knots"] and int(r.fit_ier[i]) == meta["ier"]
+                     and rel_mean <= tight and rel_max <= tight)
+            if flags == 0:
+                assert exact, name
+                np.testing.assert_allclose(r.spline_points[i].cpu().numpy(), g["spline_points"], rtol=0, atol=1e-8)
+            elif not exact:
+                flagged.append(name)
+    # the tie-free float-depth frames of round 1 must stay exact whatever their flags say
+    for name in ("geom_f32_480x640_f552_knots136", "geom_f32_480x640_f555_knots167", "geom_f32_480x640_f60_knots2039"):
+        assert name not in flagged, name
+    print("frames that left the reference's knot sequence with fit_flags set:", flagged if flagged else "none")
+    assert len(flagged) <= 2, flagged
 
 
 def test_degenerate_and_mixed_batch():
@@ -145,6 +173,35 @@ def test_numpy_promotion_modes():
     _check_frame(_run([f]), 0, f)                       # float32 * python float -> float32 product
     f2 = dict(f); f2["depth_scale"] = np.float64(0.5)
     _check_frame(_run([f2]), 0, f2)                     # float32 * numpy float64 -> float64 product
+
+
+def test_depth_dtypes_follow_numpy_promotion():
+    """`depth_image[v, u] * depth_scale` (`geometry_utils.py:105`) in the image's own dtype: float64 stays float64,
+    signed and wider integers promote to float64 and negative readings are dropped by `z > 0` (they must not wrap
+    into large positive depths); a 0-d float64 ndarray scale (`np.load(...)['depth_scale']`) promotes float32 depth."""
+    from pkg.geometry_utils import compute_curvature_profile
+    f = synth.make_frame(45, 120, 160, 0.3, "u16")
+    mask, K = f["mask_gt"], f["K"]
+    d16 = f["depth"]
+    want = gp.curvature_profile(mask, d16, K, 0.001)
+    assert want.status == gp.OK
+    for dt in (np.int16, np.int32, np.uint32, np.int64, np.float64):
+        d = d16.astype(dt)
+        if np.issubdtype(dt, np.signedinteger):
+            d[::7, ::5] = -5                      # invalid readings: dropped, like the zeros
+        o = gp.curvature_profile(mask, d, K, 0.001)
+        got = compute_curvature_profile(mask=mask, depth_image=d, intrinsics=K, depth_scale=0.001)
+        assert o.status == gp.OK and len(got.spline_points) == 100, dt
+        assert abs(got.mean_curvature - o.mean_curvature) <= 1e-9 * o.mean_curvature, dt
+        assert abs(got.max_curvature - o.max_curvature) <= 1e-9 * o.max_curvature, dt
+    f32 = synth.make_frame(46, 120, 160, 0.3, "f32")
+    f32["depth"] = (f32["depth"] * 2).astype(np.float32)
+    d64 = f32["depth"].astype(np.float64) * 1.0000001        # values float32 cannot hold
+    o = gp.curvature_profile(f32["mask_gt"], d64, K, 0.5)
+    got = compute_curvature_profile(mask=f32["mask_gt"], depth_image=d64, intrinsics=K, depth_scale=0.5)
+    assert abs(got.mean_curvature - o.mean_curvature) <= 1e-9 * o.mean_curvature
+    f3 = dict(f32); f3["depth_scale"] = np.asarray(0.5)        # 0-d float64 array
+    _check_frame(_run([f3]), 0, f3)
 
 
 def test_large_bin_uses_global_paths():

@@ -9,7 +9,16 @@ from rdp_b200 import synth
 
 
 def _frame(meta):
-    return synth.make_frame(meta["seed"], meta["H"], meta["W"], meta["fill"], meta["depth"])
+    """The frame a golden case was generated from (round-2 cases may carry a staircase-edged mask, `stair`)."""
+    f = synth.make_frame(meta["seed"], meta["H"], meta["W"], meta["fill"], meta["depth"])
+    if meta.get("stair"):
+        from oracle import service_port as sp
+        n = meta["stair"]
+        f["mask_gt"] = np.ascontiguousarray(sp.upsize_mask_np(np.ascontiguousarray(f["mask_gt"][::n, ::n]), meta["H"], meta["W"]))
+    return f
+
+
+PORT_FIT_MAX_KNOTS = 2500   # the pure-Python FITPACK port needs minutes beyond this; such cases use scipy's fit here
 
 
 def _geom_cases(manifest, flavour=None, branch=None):
@@ -32,7 +41,8 @@ def test_deprojection_is_bit_exact(manifest, golden):
         g, f = golden(name), _frame(meta)
         pcd, pix = gp.deproject(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
         assert pcd.shape[0] == int(g["n_points"]) == meta["n_points"], name
-        assert np.array_equal(pcd[:64], g["pcd_head"]) and np.array_equal(pcd[-64:], g["pcd_tail"]), name
+        if "pcd_head" in g:
+            assert np.array_equal(pcd[:64], g["pcd_head"]) and np.array_equal(pcd[-64:], g["pcd_tail"]), name
         digest = hashlib.sha256(np.ascontiguousarray(pcd, dtype='<f8').tobytes()).digest()
         assert np.array_equal(np.frombuffer(digest, dtype=np.uint8), g["pcd_sha256"]), name
         assert np.all(np.diff(pix) > 0)            # row-major order
@@ -86,7 +96,8 @@ def test_curvature_branch_b(manifest, golden):
     assert cases
     for name, meta in cases:
         g, f = golden(name), _frame(meta)
-        r = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
+        fit = "port" if meta["n_knots"] <= PORT_FIT_MAX_KNOTS else "scipy"
+        r = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"], fit=fit)
         assert r.n_knots == meta["n_knots"] and np.array_equal(r.tck[0], g["t"]), name
         assert abs(r.mean_curvature - float(g["mean_curvature"])) <= 1e-6 * abs(float(g["mean_curvature"]))
         assert abs(r.max_curvature - float(g["max_curvature"])) <= 1e-6 * abs(float(g["max_curvature"]))
@@ -94,12 +105,35 @@ def test_curvature_branch_b(manifest, golden):
 
 def test_ties_move_curvature_less_than_reported_gap(manifest, golden):
     """With ties the port's explicit tie-break need not equal the reference's pick; record the tie-induced gap."""
-    for name, meta in _geom_cases(manifest, flavour="u16"):
+    for name, meta in _geom_cases(manifest, flavour="u16", branch="A"):
         g, f = golden(name), _frame(meta)
         r = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"])
         assert r.status == gp.OK
         rel = abs(r.mean_curvature - float(g["mean_curvature"])) / abs(float(g["mean_curvature"]))
         assert rel < 5e-2, (name, rel)            # SURVEY 0.5: 8e-4 .. 2.7e-2 observed
+
+
+def test_stable_tie_break_reproduces_the_reference_run_with_the_same_rule(manifest, golden):
+    """uint16 depth in the knot-insertion regime: the reference's own code, run with argpartition/argsort made
+    deterministic by the documented rule (`oracle/make_golden.py: _StableNumpy`), against the oracle's explicit
+    tie-break: the same edge points in the same order, hence the same knots and curvature, bit for bit.  The unmodified
+    reference's value is on file beside it: with ties its curvature moves by 5 % ... 150 % in this regime."""
+    cases = [(k, v) for k, v in _geom_cases(manifest, flavour="u16", branch="B") if v.get("ties") == "stable"]
+    assert len(cases) >= 3
+    for name, meta in cases:
+        g, f = golden(name), _frame(meta)
+        r = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"], fit="scipy")
+        assert r.status == gp.OK and r.n_edge == meta["n_edge"] and r.n_knots == meta["n_knots"], name
+        assert np.array_equal(r.tck[0], g["t"]), name
+        assert r.mean_curvature == float(g["mean_curvature"]) and r.max_curvature == float(g["max_curvature"]), name
+        gap = abs(float(g["mean_curvature_unmodified"]) - float(g["mean_curvature"])) / float(g["mean_curvature"])
+        print(f"{name}: tie-induced gap of the unmodified reference {gap:.3f}")
+    # and the sequential FITPACK port follows scipy on the smallest of them (5-8 s per frame in pure Python)
+    name, meta = min(cases, key=lambda kv: kv[1]["n_knots"])
+    g, f = golden(name), _frame(meta)
+    r = gp.curvature_profile(f["mask_gt"], f["depth"], f["K"], f["depth_scale"], fit="port")
+    assert r.n_knots == meta["n_knots"] and np.array_equal(r.tck[0], g["t"]), name
+    assert abs(r.mean_curvature - float(g["mean_curvature"])) <= 1e-6 * float(g["mean_curvature"])
 
 
 def test_degenerate_inputs_give_empty_results(manifest):
