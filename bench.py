@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the vision hot path: U-Net forward + curvature profile on 640x480 RGB-D frames (BASELINE.json).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config c2|c3|c4|c5]
 
 A step is one pass of the hot path over one batch of synthetic frames: `UNet.forward_mask` (18 tensor-core convs
 + fused head) followed by `curvature_batch` (deprojection ... curvature).  Workload = BASELINE.json `configs[1]`:
@@ -12,7 +12,17 @@ One JSON line on stdout (rank 0).  Besides the contract keys it carries
   roofline_hbm  HBM roofline of the geometry streaming kernel (`k_deproject`)
   cpu_baseline  the oracle port of the reference (PyTorch-CPU fp32 U-Net + NumPy/SciPy geometry) on this host
   e2e           the same metric through the public API from pinned HOST buffers (H2D + compute + D2H per step)
-`--impl reference` times only that CPU port, on a bounded sample per step.
+  cudnn_reference  (c2, measurement only) the reference U-Net's own PyTorch ops on the same GPU through cuDNN: fp32 as
+                shipped and bf16 autocast + channels_last - the kernels the hand-written convolutions have to beat
+  latency_b1    (c2) ms per frame of the server's unchanged call pattern at batch 1 (`server.py:121-130`)
+`--impl reference` times the reference's own modules (oracle/_ref, else the oracle port) on the host cores, on a
+bounded sample per step.
+
+`--config` selects the BASELINE.json configuration (default c2 = configs[1], the one the metric is quoted on):
+  c3  configs[2]: U-Net + curvature at 1280x720, batch 32
+  c4  configs[3]: geometry only, 640x480 and 1280x720, mask fill 5-60 %, batch 256; `roofline` is the stage-level HBM
+      fraction against SURVEY 8(d)'s bytes P*(3+24*fill)
+  c5  configs[4]: 65,536 frames streamed from pinned host memory through FramePipeline, sharded over the ranks
 """
 from __future__ import annotations
 
@@ -154,11 +164,67 @@ def use_all_host_threads():
     return torch.get_num_threads()
 
 
-def cpu_reference_frames(sd, frames, K, scale):
-    """Reference path as shipped: fp32 U-Net on all host threads, server mask rule, then per-frame geometry."""
+_REF_MODULES = None
+
+
+def reference_modules():
+    """The UNMODIFIED reference modules (`pkg/segmentation_model.py`, `pkg/geometry_utils.py`) from the git-ignored
+    oracle/_ref/ that oracle/make_ref.sh fills in the authoring container, loaded under private names (our drop-in
+    mirror owns the name `pkg`).  None when that directory did not travel: the oracle port stands in."""
+    global _REF_MODULES
+    if _REF_MODULES is None:
+        import importlib.util
+        base = os.path.join(ROOT, "oracle", "_ref", "pkg")
+        mods = []
+        for name in ("segmentation_model", "geometry_utils"):
+            path = os.path.join(base, name + ".py")
+            if not os.path.exists(path):
+                mods = None
+                break
+            spec = importlib.util.spec_from_file_location(f"_rdp_ref_{name}", path)
+            m = importlib.util.module_from_spec(spec)
+            sys.modules[spec.name] = m
+            spec.loader.exec_module(m)
+            mods.append(m)
+        _REF_MODULES = tuple(mods) if mods else ()
+    return _REF_MODULES or None
+
+
+def reference_kind():
+    return "reference" if reference_modules() else "port"
+
+
+def reference_unet(sd, device="cpu"):
+    """The reference's `UNet(3, 1)` with the benchmark's weights, eval mode (`server.py:82-83`), or None."""
+    mods = reference_modules()
+    if not mods:
+        return None
+    model = mods[0].UNet(3, 1)
+    model.load_state_dict(sd)
+    return model.to(device).eval()
+
+
+def cpu_reference_frames(sd, frames, K, scale, model=None):
+    """Reference path as shipped (`server.py:121-130`): fp32 U-Net on all host threads, the server's mask rule, then
+    `compute_curvature_profile` per frame - the reference's own modules when oracle/_ref is there, else the port."""
+    import warnings
+
     import torch
-    from oracle import geometry_port, unet_port
+    mods = reference_modules()
     n = 0
+    if mods:
+        model = model if model is not None else reference_unet(sd)
+        for f in frames:
+            x = torch.from_numpy(f["rgb"]).permute(2, 0, 1).float().div(255.0).unsqueeze(0)       # ToTensor
+            with torch.no_grad():
+                out = model(x)
+                mask = (torch.sigmoid(out) > 0.5).squeeze(0).cpu().numpy().transpose(1, 2, 0).astype(np.uint8)
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                mods[1].compute_curvature_profile(depth_image=f["depth"], mask=mask[:, :, 0], intrinsics=K, depth_scale=scale)
+            n += 1
+        return n
+    from oracle import geometry_port, unet_port
     for f in frames:
         logits = unet_port.unet_forward(sd, unet_port.rgb_u8_to_input(f["rgb"][None]))
         mask = unet_port.mask_from_logits(logits)[0, 0].numpy()
@@ -167,26 +233,65 @@ def cpu_reference_frames(sd, frames, K, scale):
     return n
 
 
-def time_cpu_reference(H, W, budget_s=15.0, max_frames=64):
+def _all_cores_worker(args):
+    seed, H, W = args
+    import torch
+    torch.set_num_threads(1)
+    from rdp_b200 import synth
+    sd = synth.make_state_dict(WEIGHT_SEED, planted=True)
+    model = reference_unet(sd)
+    f = synth.make_frame(seed, H, W, FILL, "u16")
+    cpu_reference_frames(sd, [f], f["K"], f["depth_scale"], model)          # warm-up
+    t0 = time.perf_counter()
+    cpu_reference_frames(sd, [f], f["K"], f["depth_scale"], model)
+    return time.perf_counter() - t0
+
+
+def time_cpu_all_cores(H, W):
+    """BASELINE.md 4.4's throughput-oriented variant: one single-threaded worker per host core, one frame each."""
+    import concurrent.futures
+    import multiprocessing
+    n = os.cpu_count() or 1
+    try:
+        n = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        pass
+    t0 = time.perf_counter()
+    with concurrent.futures.ProcessPoolExecutor(max_workers=n, mp_context=multiprocessing.get_context("spawn")) as ex:
+        per = list(ex.map(_all_cores_worker, [(4000 + i, H, W) for i in range(n)]))
+    # steady state: every worker turns out one frame per `t` seconds
+    return {"value": sum(1.0 / t for t in per), "unit": UNIT, "workers": n, "threads_per_worker": 1,
+            "seconds_per_frame_per_worker": statistics.median(per), "wall_s": time.perf_counter() - t0}
+
+
+def time_cpu_reference(H, W, budget_s=15.0, max_frames=64, all_cores=False):
     import torch
     from rdp_b200 import synth
     use_all_host_threads()
     sd = synth.make_state_dict(WEIGHT_SEED, planted=True)
     frames = [synth.make_frame(1000 + i, H, W, FILL, "u16") for i in range(2)]
     K, scale = frames[0]["K"], frames[0]["depth_scale"]
-    cpu_reference_frames(sd, frames[:1], K, scale)                 # warm-up (oneDNN primitive creation)
+    model = reference_unet(sd)
+    cpu_reference_frames(sd, frames[:1], K, scale, model)          # warm-up (oneDNN primitive creation)
     t0 = time.perf_counter()
-    cpu_reference_frames(sd, frames[1:2], K, scale)
+    cpu_reference_frames(sd, frames[1:2], K, scale, model)
     per_frame = time.perf_counter() - t0
     n = int(max(2, min(max_frames, budget_s / max(per_frame, 1e-3))))
     frames = [synth.make_frame(2000 + i, H, W, FILL, "u16") for i in range(n)]
     t0 = time.perf_counter()
-    cpu_reference_frames(sd, frames, K, scale)
+    cpu_reference_frames(sd, frames, K, scale, model)
     dt = time.perf_counter() - t0
-    return {"value": n / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-            "host_cpus": os.cpu_count(),
-            "sample": f"{n} frames {W}x{H} (fill {FILL}, u16 depth), oracle port: torch-CPU fp32 U-Net on "
-                      f"{torch.get_num_threads()} threads + NumPy/SciPy geometry, {dt:.1f} s"}
+    what = ("the reference's own modules (oracle/_ref)" if reference_modules() else "oracle port")
+    out = {"value": n / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": reference_kind(),
+           "host_cpus": os.cpu_count(),
+           "sample": f"{n} frames {W}x{H} (fill {FILL}, u16 depth), {what}: torch-CPU fp32 U-Net on "
+                     f"{torch.get_num_threads()} threads + NumPy/SciPy geometry, {dt:.1f} s"}
+    if all_cores:
+        try:
+            out["all_cores"] = time_cpu_all_cores(H, W)
+        except Exception as e:  # a measurement extra must not cost the line
+            out["all_cores"] = {"error": repr(e)}
+    return out
 
 
 def run_reference(args):
@@ -202,28 +307,129 @@ def run_reference(args):
     per_step = args.ref_frames
     frames = [synth.make_frame(3000 + i, H, W, FILL, "u16") for i in range(per_step)]
     K, scale = frames[0]["K"], frames[0]["depth_scale"]
+    model = reference_unet(sd)
     for _ in range(args.warmup):
-        cpu_reference_frames(sd, frames[:1], K, scale)
+        cpu_reference_frames(sd, frames[:1], K, scale, model)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        cpu_reference_frames(sd, frames, K, scale)
+        cpu_reference_frames(sd, frames, K, scale, model)
     dt = time.perf_counter() - t0
     value = per_step * args.steps / dt
-    sample = (f"{per_step} frames per step x {args.steps} steps, {W}x{H}, oracle port of the reference on "
-              f"{torch.get_num_threads()} threads")
+    what = "the reference's own modules (oracle/_ref)" if reference_modules() else "oracle port of the reference"
+    sample = f"{per_step} frames per step x {args.steps} steps, {W}x{H}, {what} on {torch.get_num_threads()} threads"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
-        "config": {"workload": f"configs[1] sample: UNet+curvature {W}x{H}, {per_step} frames/step on host CPU",
+        "config": {"workload": f"{args.config_name} sample: UNet+curvature {W}x{H}, {per_step} frames/step on host CPU",
                    "height": H, "width": W, "fill": FILL},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": reference_kind(),
                          "host_cpus": os.cpu_count(), "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
     return 0
+
+
+# --------------------------------------------------------------------------------------------------------------
+# measurement-only legs of the c2 line
+# --------------------------------------------------------------------------------------------------------------
+def time_cudnn_reference(sd, rgb_u8, flops_per_frame, reps=3):
+    """"the reference's Blackwell kernel" is whatever PyTorch/cuDNN runs for the unmodified `UNet` on
+    this GPU.  Measurement only - nothing of it is on the product path: the reference module itself (oracle/_ref, else the
+    oracle's functional restatement of the same torch ops) on CUDA, same batch, same event timing, fp32 as shipped
+    (`server.py:57,121-123`) and bf16 autocast + channels_last (the strongest stock variant)."""
+    import torch
+    from oracle import unet_port
+    dev = rgb_u8.device
+    B = rgb_u8.shape[0]
+    x = rgb_u8.permute(0, 3, 1, 2).float().div(255.0).contiguous()
+    model = reference_unet(sd, dev)
+    sd_dev = None if model is not None else {k: v.to(dev) for k, v in sd.items()}
+    torch.backends.cudnn.benchmark = True
+    out = {"what": ("the reference's own nn.Module (oracle/_ref)" if model is not None else "oracle/unet_port.py (the same torch ops)")
+                   + " on CUDA through PyTorch/cuDNN, measurement only", "batch": B,
+           "torch": torch.__version__, "cudnn": torch.backends.cudnn.version()}
+
+    def fwd(inp):
+        return model(inp) if model is not None else unet_port.unet_forward(sd_dev, inp)
+
+    def timed(fn):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize(dev)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(dev)
+        return e0.elapsed_time(e1) / reps
+
+    variants = {}
+    try:
+        torch.backends.cudnn.allow_tf32 = False
+        torch.backends.cuda.matmul.allow_tf32 = False
+        with torch.no_grad():
+            variants["fp32_as_shipped"] = timed(lambda: fwd(x))
+            torch.backends.cudnn.allow_tf32 = True
+            variants["fp32_tf32_allowed"] = timed(lambda: fwd(x))
+            torch.backends.cudnn.allow_tf32 = False
+            if model is not None:
+                model_cl = model.to(memory_format=torch.channels_last)
+                xcl = x.contiguous(memory_format=torch.channels_last)
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    variants["bf16_autocast_channels_last"] = timed(lambda: model_cl(xcl))
+            else:
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    variants["bf16_autocast"] = timed(lambda: fwd(x))
+    except Exception as e:  # out of memory on a smaller GPU etc.: report, do not lose the line
+        out["error"] = repr(e)
+    for k, ms in variants.items():
+        out[k] = {"ms_per_batch": ms, "frames_per_s": B / ms * 1e3, "tflops": B * flops_per_frame / (ms * 1e-3) / 1e12}
+    del model, x
+    torch.cuda.empty_cache()
+    return out
+
+
+def time_latency_b1(model, frame, K, scale, reps=30):
+    """The production call pattern, unchanged (`server.py:121-130`): one 256x256 frame through `model(x)`, the server's
+    `sigmoid > 0.5` + `.cpu()`, `cv2.resize(INTER_NEAREST)` back to camera size, `compute_curvature_profile` on NumPy
+    arrays.  Milliseconds per frame, wall clock around the whole body (it ends on the host)."""
+    import cv2
+    import torch
+    from pkg.geometry_utils import compute_curvature_profile
+    dev = next(model.parameters()).device
+    H, W = frame["depth"].shape
+    small = cv2.resize(frame["rgb"], (256, 256), interpolation=cv2.INTER_AREA)
+    x_host = torch.from_numpy(small).permute(2, 0, 1).float().div(255.0).unsqueeze(0)
+
+    def body():
+        t = [time.perf_counter()]
+        input_tensor = x_host.to(dev)
+        with torch.no_grad():
+            output = model(input_tensor)
+            mask_resized = (torch.sigmoid(output) > 0.5).squeeze(0).cpu().numpy().transpose(1, 2, 0).astype(np.uint8)
+        t.append(time.perf_counter())
+        final_mask = cv2.resize(mask_resized, (W, H), interpolation=cv2.INTER_NEAREST)
+        t.append(time.perf_counter())
+        res = compute_curvature_profile(depth_image=frame["depth"], mask=final_mask, intrinsics=K, depth_scale=scale)
+        t.append(time.perf_counter())
+        return res, t
+
+    for _ in range(5):
+        res, _ = body()
+    parts = []
+    for _ in range(reps):
+        res, t = body()
+        parts.append([1e3 * (t[i + 1] - t[i]) for i in range(3)] + [1e3 * (t[3] - t[0])])
+    med = np.median(np.array(parts), axis=0)
+    return {"ms_per_frame": float(med[3]), "unet_and_mask_to_host_ms": float(med[0]), "cv2_resize_ms": float(med[1]),
+            "compute_curvature_profile_ms": float(med[2]), "frames_per_s_one_thread": 1e3 / float(med[3]),
+            "result_points": len(res.spline_points), "reps": reps,
+            "how": "wall clock, median; model((1,3,256,256)) -> sigmoid>0.5 -> .cpu() -> cv2.resize NEAREST -> "
+                   f"compute_curvature_profile at {W}x{H} on NumPy arrays (server.py:121-130 unchanged)"}
 
 
 # --------------------------------------------------------------------------------------------------------------
@@ -305,14 +511,14 @@ def run_b200(args):
     # ---- timed region 2: end to end from pinned host buffers through the public API ----
     # FramePipeline = the per-GPU stream pipeline a user runs: H2D of micro-batch i+1 and D2H of i-1 overlap compute of i
     from rdp_b200.pipeline import FramePipeline
-    pipe = FramePipeline(model, K, scale, B, H, W, depth_dtype=dev_depth[0].dtype, slots=2, device=dev)
+    pipe = FramePipeline(model, K, scale, B, H, W, depth_dtype=dev_depth[0].dtype, slots=args.slots, device=dev)
     pipe.submit(host_rgb[0], host_depth[0])
     pipe.collect()
     barrier()
     s_in, _, s_out = pipe.events()
     e0.record(s_in)
     for i in range(args.steps):
-        if pipe.in_flight == 2:
+        if pipe.in_flight == args.slots:
             pipe.collect(copy=False)
         pipe.submit(host_rgb[i % RING], host_depth[i % RING])
     while pipe.in_flight:
@@ -353,16 +559,17 @@ def run_b200(args):
     dp_bytes = B * (3.0 * P + 4.0 * n_points)
     step_ms_prof = float(unet_ms.sum() + geom_ms.sum())
     ncu = load_traffic() if (B, H, W) == (64, 480, 640) else None   # the capture was taken on this workload
+    l2_note_gb = unet_ws.numel() / 1e9
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"configs[1]: UNet+curvature {W}x{H}, batch {B} per GPU, bf16 storage / fp32 accumulate",
+        "config": {"workload": f"{args.config_name}: UNet+curvature {W}x{H}, batch {B} per GPU, bf16 storage / fp32 accumulate",
                    "batch_per_gpu": B, "height": H, "width": W, "fill": FILL, "depth": "u16",
                    "weights": f"seeded random init (seed {WEIGHT_SEED}) with a planted colour path so that masks follow the object",
                    "parallelism": f"frames sharded over {world} GPU(s), no collective",
-                   "l2": f"ring of {RING} input batches ({RING * B * P * 5 / 1e6:.0f} MB) and {unet_ws.numel() / 1e9:.1f} GB of "
+                   "l2": f"ring of {RING} input batches ({RING * B * P * 5 / 1e6:.0f} MB) and {l2_note_gb:.1f} GB of "
                          "activations per step, both larger than the 126 MB L2",
                    "frames_ok": int((status == 0).sum()), "mean_points_per_frame": n_points},
         "clocks": clocks,
@@ -370,7 +577,7 @@ def run_b200(args):
                 "ms_per_step": ms_e2e / args.steps,
                 "frames_ok_last_batch": e2e_ok,
                 "how": "rdp_b200.pipeline.FramePipeline: pinned host rgb u8 + depth u16 -> H2D -> UNet.forward_mask -> "
-                       "curvature_batch -> D2H of mean/max/status/points, three streams, two slots"},
+                       f"curvature_batch -> D2H of mean/max/status/points, three streams, {args.slots} slots"},
         "gpu_launches": int((eng.launches_per_forward + len(geometry.LAUNCH_NAMES) - 1) * args.steps),
         "roofline": {"bound": "tensor", "kernel": "k_conv3x3 (18 launches per step)", "achieved": conv_tflops,
                      "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": conv_tflops / peaks["tflops"],
@@ -385,15 +592,223 @@ def run_b200(args):
                          "traffic": ncu["deproject_dram_bytes_per_launch"] if ncu else None, "algorithmic_bytes": dp_bytes,
                          "ms": dp_ms, "geometry_ms_per_step": float(geom_ms.sum()),
                          "geometry_launch_ms": {n: round(float(v), 4) for n, v in zip(geometry.LAUNCH_NAMES, geom_ms)},
-                         "survey_bytes_per_frame": geometry_bytes_per_frame(P, n_points)},
+                         "survey_bytes_per_frame": geometry_bytes_per_frame(P, n_points),
+                         "stage": {"what": "all geometry launches of a step against SURVEY 8(d)'s bytes P*(3+24*fill)",
+                                   "achieved": B * geometry_bytes_per_frame(P, n_points) / (float(geom_ms.sum()) * 1e-3) / 1e9,
+                                   "frac": B * geometry_bytes_per_frame(P, n_points) / (float(geom_ms.sum()) * 1e-3) / 1e9 / peaks["hbm_gbs"]}},
         "launch_ms": {n: round(float(v), 4) for n, v in zip(names, unet_ms)},
     }
-    if rank == 0 and world == 1:
+    if rank == 0 and world == 1 and args.config == "c2":
         line["server_shaped"] = time_server_shaped(model, dev_rgb[0], dev_depth[0], K, scale, B, H, W)
+        line["latency_b1"] = time_latency_b1(model, base[0], K, scale)
+        if not args.no_cudnn:
+            del unet_ws, geom_ws, pipe          # room for the fp32 reference's activations
+            torch.cuda.empty_cache()
+            line["cudnn_reference"] = time_cudnn_reference(sd, dev_rgb[0], sum(flops))
+            best = max((v["frames_per_s"] for v in line["cudnn_reference"].values() if isinstance(v, dict)), default=None)
+            if best:
+                line["cudnn_reference"]["our_unet_frames_per_s"] = B / (float(unet_ms.sum()) * 1e-3)
+                line["cudnn_reference"]["ours_over_best_cudnn"] = B / (float(unet_ms.sum()) * 1e-3) / best
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = time_cpu_reference(H, W, budget_s=args.cpu_budget)
+        line["cpu_baseline"] = time_cpu_reference(H, W, budget_s=args.cpu_budget, all_cores=(args.config == "c2"))
     elif rank == 0:
         line["cpu_baseline"] = None
+    if rank == 0:
+        emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def _dist_setup():
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 arm has no CPU fallback; use --impl reference for the CPU port)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    return world, rank, local_rank, dev
+
+
+def _max_ms(ms, world, dev):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    return ms
+
+
+def run_c4(args):
+    """configs[3]: geometry only - deprojection, binned edge, spline curvature - at 640x480 and 1280x720, mask fill
+    5-60 %, batch 256.  A step is one pass of `curvature_batch` over each of the 16 (resolution, fill) batches."""
+    import torch
+    import torch.distributed as dist
+
+    from rdp_b200 import _lib, geometry, synth
+    world, rank, local_rank, dev = _dist_setup()
+    _lib.load()
+    B = args.batch
+    peaks = load_peaks()
+    fills = (0.05, 0.10, 0.15, 0.20, 0.30, 0.40, 0.50, 0.60)
+    points = []
+    for (H, W) in ((480, 640), (720, 1280)):
+        K = synth.camera_intrinsics(H, W)
+        gws = torch.empty(geometry.workspace_bytes(B, H, W), dtype=torch.uint8, device=dev)
+        for fill in fills:
+            frames = [synth.make_frame(8000 + 31 * rank + i, H, W, fill, "u16") for i in range(8)]
+            masks = torch.from_numpy(np.stack([frames[i % 8]["mask_gt"] for i in range(B)])).to(dev)
+            depth = torch.from_numpy(np.stack([frames[i % 8]["depth"] for i in range(B)])).to(dev)
+            points.append(dict(H=H, W=W, fill=fill, K=K, masks=masks, depth=depth, gws=gws))
+    for pt in points:
+        for _ in range(args.warmup):
+            r = geometry.curvature_batch(pt["masks"], pt["depth"], pt["K"], 0.001, workspace=pt["gws"])
+        pt["ok"] = int((r.status == 0).sum())
+        pt["n_points"] = float(r.n_points.float().mean())
+        pt["knots"] = (int(r.n_knots.min()), int(r.n_knots.max()))
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(len(points) + 1)]
+    acc = np.zeros(len(points))
+    t_all0, t_all1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_all0.record()
+    for _ in range(args.steps):
+        ev[0].record()
+        for j, pt in enumerate(points):
+            geometry.curvature_batch(pt["masks"], pt["depth"], pt["K"], 0.001, workspace=pt["gws"])
+            ev[j + 1].record()
+        ev[-1].synchronize()
+        acc += np.array([ev[j].elapsed_time(ev[j + 1]) for j in range(len(points))])
+    t_all1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ms = _max_ms(t_all0.elapsed_time(t_all1), world, dev)
+    clocks = sampler.stop()
+    acc /= args.steps
+    rows, bytes_a, ms_a = [], 0.0, 0.0
+    for j, pt in enumerate(points):
+        P = pt["H"] * pt["W"]
+        lm = []
+        geometry.curvature_batch(pt["masks"], pt["depth"], pt["K"], 0.001, workspace=pt["gws"], launch_ms=lm)
+        stage_bytes = B * geometry_bytes_per_frame(P, pt["n_points"])
+        cubic = pt["knots"][1] == 8
+        if cubic:
+            bytes_a += stage_bytes
+            ms_a += acc[j]
+        rows.append({"resolution": f"{pt['W']}x{pt['H']}", "fill": pt["fill"], "ms_per_batch": round(float(acc[j]), 4),
+                     "frames_per_s": B / acc[j] * 1e3, "points_per_frame": pt["n_points"], "frames_ok": pt["ok"],
+                     "knots_min": pt["knots"][0], "knots_max": pt["knots"][1],
+                     "regime": "8-knot cubic (ier=-2)" if cubic else "knot insertion + smoothing (latency-bound fits)",
+                     "stage_gbs": stage_bytes / (acc[j] * 1e-3) / 1e9, "stage_frac_of_hbm": stage_bytes / (acc[j] * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                     "launch_ms": {k: round(v, 4) for k, v in zip(geometry.LAUNCH_NAMES, lm)}})
+    frames_per_step = B * len(points)
+    value = world * frames_per_step * args.steps / (ms * 1e-3)
+    line = {
+        "metric": "geometry-only frames/sec (deprojection + binned edge + spline curvature), 640x480 and 1280x720, fill 5-60 %",
+        "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.config_name}: geometry only, 2 resolutions x 8 fills, batch {B} per point, masks supplied",
+                   "batch_per_point": B, "depth": "u16", "l2": "16 input batches (7.6 GB) rotate through every step, each larger than the 126 MB L2",
+                   "parallelism": f"every rank runs the sweep on its own frames ({world} GPU(s)), no collective"},
+        "clocks": clocks, "gpu_launches": int(len(geometry.LAUNCH_NAMES) - 1) * len(points) * args.steps,
+        "e2e": None,
+        "roofline": {"bound": "hbm", "kernel": "geometry stage (all launches), points in the single-cubic regime",
+                     "achieved": bytes_a / (ms_a * 1e-3) / 1e9 if ms_a else None, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": bytes_a / (ms_a * 1e-3) / 1e9 / peaks["hbm_gbs"] if ms_a else None, "traffic": None,
+                     "algorithmic_bytes": "P*(3+24*fill) per frame (SURVEY 8d): mask+depth read once, fp32 xyz written and read once",
+                     "peak_source": peaks["source"]},
+        "points": rows,
+    }
+    if rank == 0:
+        emit(line)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def run_c5(args):
+    """configs[4]: 65,536 frames of 640x480 streamed from pinned host memory, sharded over the ranks (contiguous blocks,
+    `pipeline.frame_shard`), every rank its own `FramePipeline`; no collective on the data path."""
+    import torch
+    import torch.distributed as dist
+
+    from pkg.segmentation_model import UNet
+    from rdp_b200 import _lib, synth
+    from rdp_b200.pipeline import FramePipeline, frame_shard
+    world, rank, local_rank, dev = _dist_setup()
+    _lib.load()
+    B, H, W = args.batch, args.height, args.width
+    total = args.total_frames if args.steps is None else args.steps * B * world
+    mine = frame_shard(total, world, rank)
+    steps = len(mine) // B
+    model = UNet(3, 1)
+    model.load_state_dict(synth.make_state_dict(WEIGHT_SEED, planted=True))
+    model = model.to(dev).eval()
+    base = [synth.make_frame(9000 + 131 * rank + i, H, W, FILL, "u16") for i in range(32)]
+    ring = max(1, 1024 // B)                 # SURVEY 8(d): a ring of 1,024 distinct frame slots in pinned memory
+    host_rgb = [torch.from_numpy(np.stack([base[(i * 7 + j) % 32]["rgb"] for j in range(B)])).pin_memory() for i in range(ring)]
+    host_depth = [torch.from_numpy(np.stack([base[(i * 7 + j) % 32]["depth"] for j in range(B)])).pin_memory() for i in range(ring)]
+    slots = args.slots
+    pipe = FramePipeline(model, base[0]["K"], 0.001, B, H, W, slots=slots, device=dev)
+    for i in range(max(3, args.warmup)):
+        pipe.submit(host_rgb[i % ring], host_depth[i % ring])
+        pipe.collect()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    s_in, _, s_out = pipe.events()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(s_in)
+    ok = 0
+    for i in range(steps):
+        if pipe.in_flight == slots:
+            ok += int((pipe.collect(copy=False)["status"] == 0).sum())
+        pipe.submit(host_rgb[i % ring], host_depth[i % ring])
+    while pipe.in_flight:
+        ok += int((pipe.collect(copy=False)["status"] == 0).sum())
+    e1.record(s_out)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    ms = _max_ms(e0.elapsed_time(e1), world, dev)
+    clocks = sampler.stop()
+    frames = steps * B * world
+    if world > 1:
+        t = torch.tensor([ok], device=dev)
+        dist.all_reduce(t)
+        ok = int(t.item())
+    value = frames / (ms * 1e-3)
+    eng = model._engine_for(dev)
+    from rdp_b200 import geometry
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": max(3, args.warmup),
+        "ms_per_step": ms / max(1, steps), "higher_is_better": True, "scaling": "strong" if args.steps is None else "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"{args.config_name}: {frames} frames {W}x{H} streamed from pinned host memory, micro-batches of {B}, "
+                               f"{world} GPU(s), {steps} steps per rank", "total_frames": frames, "batch_per_gpu": B, "slots": slots,
+                   "ring": f"{ring * B} distinct frame slots per rank in pinned host memory ({ring * B * H * W * 5 / 1e9:.2f} GB), larger than L2",
+                   "parallelism": f"contiguous frame blocks per rank ({world} ranks), no collective", "frames_ok": ok},
+        "clocks": clocks, "seconds": ms * 1e-3,
+        "gpu_launches": int((eng.launches_per_forward + len(geometry.LAUNCH_NAMES) - 1) * steps),
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": int(pipe.h2d_bytes), "d2h_bytes_per_step": int(pipe.d2h_bytes),
+                "how": "this configuration is end to end by construction: every micro-batch is copied from pinned host memory "
+                       "and its results are copied back inside the timed region"},
+        "roofline": None, "cpu_baseline": None,
+    }
     if rank == 0:
         emit(line)
     if world > 1:
@@ -465,19 +880,37 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=None, help="timed steps (default: 10 for c2, 5 for c3, 3 for c4, the whole stream for c5)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
-    ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--height", type=int, default=480)
-    ap.add_argument("--width", type=int, default=640)
+    ap.add_argument("--config", choices=["c2", "c3", "c4", "c5"], default="c2", help="BASELINE.json configs[1..4]")
+    ap.add_argument("--batch", type=int, default=None)
+    ap.add_argument("--height", type=int, default=None)
+    ap.add_argument("--width", type=int, default=None)
+    ap.add_argument("--total-frames", type=int, default=65536, help="c5: frames in the stream (all ranks together)")
+    ap.add_argument("--slots", type=int, default=3, help="c5: micro-batches in flight per GPU")
+    ap.add_argument("--no-cudnn", action="store_true", help="c2: skip the cuDNN measurement leg")
     ap.add_argument("--ref-frames", type=int, default=4, help="frames per step of the CPU reference arm")
     ap.add_argument("--cpu-budget", type=float, default=15.0, help="seconds of CPU work for the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    defaults = {"c2": (64, 480, 640, 10, "configs[1]"), "c3": (32, 720, 1280, 5, "configs[2]"),
+                "c4": (256, 0, 0, 3, "configs[3]"), "c5": (64, 480, 640, None, "configs[4]")}[args.config]
+    args.batch = defaults[0] if args.batch is None else args.batch
+    args.height = defaults[1] if args.height is None else args.height
+    args.width = defaults[2] if args.width is None else args.width
+    args.config_name = defaults[4]
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else max(args.warmup, 1)
     if args.impl == "reference":
+        if args.config in ("c4", "c5"):          # the CPU arm is defined on the U-Net + curvature step (640x480)
+            args.height, args.width = 480, 640
+        args.steps = 10 if args.steps is None else args.steps
         return run_reference(args)
+    if args.config == "c5":
+        return run_c5(args)
+    args.steps = defaults[3] if args.steps is None else args.steps
+    if args.config == "c4":
+        return run_c4(args)
     return run_b200(args)
 
 
