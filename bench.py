@@ -555,8 +555,8 @@ def run_b200(args):
     conv_tflops = B * sum(flops) / (conv_ms * 1e-3) / 1e12
     per_layer = {names[i]: round(B * flops[j] / (unet_ms[i] * 1e-3) / 1e12, 1) for j, i in enumerate(conv_idx)}
     dp_ms = float(geom_ms[geometry.LAUNCH_NAMES.index("deproject")])
-    # k_deproject's own algorithmic bytes: 3P read, 4N pixel ids written (fp32 xyz only when the caller asks for it)
-    dp_bytes = B * (3.0 * P + 4.0 * n_points)
+    # k_deproject's own algorithmic bytes: 3P read; 4N pixel ids + 16N fp64 x/y keys written (fp32 xyz only on request)
+    dp_bytes = B * (3.0 * P + 20.0 * n_points)
     step_ms_prof = float(unet_ms.sum() + geom_ms.sum())
     ncu = load_traffic() if (B, H, W) == (64, 480, 640) else None   # the capture was taken on this workload
     l2_note_gb = unet_ws.numel() / 1e9

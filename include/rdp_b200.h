@@ -157,8 +157,8 @@ int rdp_geom_curvature(const uint8_t* mask, const void* depth, int depth_fmt, in
 int rdp_geom_launch_count(void);
 
 /* Measurement aid (no counterpart in the reference): as rdp_geom_curvature, with a CUDA event between launches;
- * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, xrange, bin_hist,
- * bin_offsets, scatter, select_sort, fit, fit_knots. */
+ * blocks, then fills launch_ms (HOST, rdp_geom_launch_count entries): memset, deproject, bin_hist, scatter,
+ * select_sort, fit, fit_knots. */
 int rdp_geom_curvature_profiled(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                                 const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
                                 void* workspace, size_t workspace_bytes, void* stream, float* launch_ms);
@@ -224,6 +224,42 @@ int rdp_post_mask_nearest(const uint8_t* mask, int B, int h, int w, int H, int W
 int rdp_post_mask_png_sizes(int B, int H, int W, size_t* max_png_bytes, size_t* workspace_bytes);
 int rdp_post_mask_png(const uint8_t* mask, int B, int H, int W, uint8_t* png, size_t png_stride, int32_t* png_bytes,
                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------------------------ */
+/* Wire-format decoders: replace the two cv2.imdecode calls at the top of the server loop */
+/* (services/vision_analysis/server.py:117-118) for a batch of frames.                                       */
+/* ------------------------------------------------------------------------------------------------------ */
+
+/* per-image status of the decoders */
+#define RDP_DECODE_OK 0
+#define RDP_DECODE_NOT_AN_IMAGE 1     /* signature / SOI missing */
+#define RDP_DECODE_TRUNCATED 2        /* marker or chunk structure broken */
+#define RDP_DECODE_UNSUPPORTED 3      /* JPEG: not baseline 8-bit YCbCr 4:4:4/4:2:2/4:2:0 or grey; PNG: not 8/16-bit grey */
+#define RDP_DECODE_WRONG_SIZE 4       /* the image is not H x W */
+#define RDP_DECODE_CORRUPT 5          /* bad Huffman code / zlib stream */
+#define RDP_DECODE_LENGTH_MISMATCH 6  /* PNG: inflated data shorter or longer than H rows */
+#define RDP_DECODE_BAD_FILTER 7       /* PNG: filter type > 4 */
+
+/* Workspace sizes of the two decoders for a batch of B images of H x W (either pointer may be NULL). */
+int rdp_pre_decode_sizes(int B, int H, int W, size_t* jpeg_workspace_bytes, size_t* png_workspace_bytes);
+
+/* Replaces `cv2.imdecode(np.frombuffer(request.color_image.data, np.uint8), cv2.IMREAD_COLOR)` (server.py:117) for the
+ * JPEGs `cv2.imencode('.jpg', ...)` writes (client.py:65): baseline sequential Huffman JPEG, decoded with libjpeg's
+ * accurate integer inverse DCT, "fancy" chroma up-sampling and fixed-point colour conversion, so the BGR bytes equal
+ * OpenCV's (libjpeg-turbo) bit for bit.
+ *   data     concatenated JPEG files (device)            offsets  [B+1] int64 byte offsets into data (device)
+ *   bgr      [B][H][W][3] uint8 (device)                 status   [B] int32 RDP_DECODE_* (device); a failed image is all zero
+ * Two launches.  A Huffman-coded scan is one serial bit stream: one warp per image, so throughput comes from the batch. */
+int rdp_pre_decode_jpeg(const uint8_t* data, const int64_t* offsets, int B, int H, int W, uint8_t* bgr, int32_t* status,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* Replaces `cv2.imdecode(np.frombuffer(request.depth_image.data, np.uint8), cv2.IMREAD_UNCHANGED)` (server.py:118) for
+ * the PNGs `cv2.imencode('.png', depth_uint16)` writes (client.py:66): non-interlaced 16-bit (or 8-bit) greyscale, any
+ * zlib stream (stored / fixed / dynamic Huffman blocks), all five scan-line filters.
+ *   depth    [B][H][W] uint16 (device; 8-bit images are widened)   status [B] int32 RDP_DECODE_* (device)
+ * Two launches; one warp per image inflates, one CTA per image undoes the filters. */
+int rdp_pre_decode_png16(const uint8_t* data, const int64_t* offsets, int B, int H, int W, uint16_t* depth, int32_t* status,
+                         void* workspace, size_t workspace_bytes, void* stream);
 
 #ifdef __cplusplus
 }

@@ -9,12 +9,14 @@
 //
 // Data layout (HBM): mask u8 [B][P], depth u16|f32 [B][P] (P = H*W), workspace arrays indexed [b][i].
 // Kernels (one launch each per batch, all on the caller's stream, no host sync):
-//   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once, writes 4N (pixel ids) + 12N (fp32 xyz); 16384-pixel tiles
-//   k_xrange       L2/HBM      reads 4N + gathers 2N, writes 16N (fp64 x and y keys), x range by atomics
-//   k_bin_hist     L2/HBM      reads 8N, writes N (bin ids)
-//   k_bin_offsets  tiny        50 bins per frame -> k per bin, offsets, status
+//   k_deproject    HBM-bound   reads 3P (u16) bytes/frame once; writes 4N (pixel ids) + 16N (fp64 x and y as ordered keys,
+//                              computed while the tile's depth is still in L1) + 12N (fp32 xyz, on request); x range by
+//                              one pair of atomics per tile; 16384-pixel tiles, ordered compaction by decoupled look-back
+//   k_bin_hist     L2/HBM      reads 8N, writes N (bin ids); the last block of a frame turns the 50 counts into k per bin,
+//                              offsets and the frame status (no separate launch)
 //   k_scatter      L2/HBM      reads 13N, writes 12N (pixel ids and y keys grouped by bin)
-//   k_select_sort  latency     one CTA per (frame, bin): radix select of the k largest y, bitonic sort by x
+//   k_select_sort  latency     one CTA per (frame, bin): the bin's keys staged in shared memory, radix select of the k
+//                              largest y, bitonic sort by x
 //   k_fit          latency     one CTA per frame: chord-length scan, 4x4 normal equations in fp64, curvature
 #include <stdarg.h>
 
@@ -55,7 +57,7 @@ struct FrameState {
   int n_points;
   int n_edge;
   int status;
-  int pad_;
+  int hist_done;  // blocks of k_bin_hist that have added their counts (the last one finalises the frame)
   int bin_count[NUM_BINS];
   int bin_k[NUM_BINS];
   int bin_off[NUM_BINS + 1];
@@ -78,7 +80,7 @@ struct Params {
   uint32_t* pix;       // [B][P] valid pixel ids, row-major order
   uint8_t* bins;       // [B][P] bin id per valid point
   uint32_t* binned;    // [B][P] pixel ids grouped by bin
-  unsigned long long* xkey_c;  // [B][P] ordered fp64 x key per valid point (compacted order), written by k_xrange
+  unsigned long long* xkey_c;  // [B][P] ordered fp64 x key per valid point (compacted order), written by k_deproject
   unsigned long long* ykey_c;  // [B][P] ordered fp64 y key per valid point (compacted order)
   unsigned long long* ykey_b;  // [B][P] the same, grouped by bin like `binned`
   uint32_t* edge_pix;  // [B][ecap] selected pixel ids, ordered by x
@@ -276,89 +278,63 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
   }
   __syncthreads();
 
-  // cooperative, coalesced emission of the tile's points (the x range and the fp64 keys are k_xrange's job, which keeps
-  // this streaming kernel light; the fp32 cloud is only computed when the caller asked for it)
+  // cooperative, coalesced emission of the tile's points: pixel id, the fp64 x and y as ordered integer keys (what the
+  // binning, the selection and the ordering decide on), the frame's x range, and the fp32 cloud when the caller wants
+  // it.  The depth the keys need was loaded by this CTA a moment ago (L1/L2 hit), so the stage reads HBM once.
   const int total = s_total, base = s_base;
+  const bool keys = p.xkey_c != nullptr;
+  unsigned long long kmax = 0, kmin_inv = 0;
   for (int j = tid; j < total; j += DP_THREADS) {
     const uint32_t px = (uint32_t)(t * TILE_PX) + s_pix[j];
     const size_t o = fbase + base + j;
     p.pix[o] = px;
-    if (p.out.points_xyz) {
+    if (keys || p.out.points_xyz) {
       const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
       const double z = depth_to_z(p, fbase + px);
-      float* dst = p.out.points_xyz + 3 * o;
-      dst[0] = (float)deproject_axis((double)u, p.cx, z, p.fx);
-      dst[1] = (float)deproject_axis((double)v, p.cy, z, p.fy);
-      dst[2] = (float)z;
+      const double x = deproject_axis((double)u, p.cx, z, p.fx), y = deproject_axis((double)v, p.cy, z, p.fy);
+      if (keys) {
+        const unsigned long long k = ordered_key(x);
+        p.xkey_c[o] = k;
+        p.ykey_c[o] = ordered_key(y);
+        kmax = k > kmax ? k : kmax;
+        kmin_inv = ~k > kmin_inv ? ~k : kmin_inv;
+      }
+      if (p.out.points_xyz) {
+        float* dst = p.out.points_xyz + 3 * o;
+        dst[0] = (float)x;
+        dst[1] = (float)y;
+        dst[2] = (float)z;
+      }
+    }
+  }
+  if (keys) {  // x range of the frame (geometry_utils.py:124): block reduction, then one atomic pair per tile
+    __shared__ unsigned long long s_red[2][DP_THREADS / 32];
+    kmax = warp_max(kmax);
+    kmin_inv = warp_max(kmin_inv);
+    if (lane == 0) {
+      s_red[0][warp] = kmax;
+      s_red[1][warp] = kmin_inv;
+    }
+    __syncthreads();
+    if (tid == 0 && total > 0) {
+      for (int w = 1; w < DP_THREADS / 32; ++w) {
+        kmax = s_red[0][w] > kmax ? s_red[0][w] : kmax;
+        kmin_inv = s_red[1][w] > kmin_inv ? s_red[1][w] : kmin_inv;
+      }
+      atomicMax(&p.fs[b].xmax_key, kmax);
+      atomicMax(&p.fs[b].xmin_inv_key, kmin_inv);
     }
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// k_xrange: fp64 x / y keys of the valid points and the frame's x range (geometry_utils.py:114-115,124)
+// k_bin_hist / k_scatter: counting sort of the points by x-bin
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PT_THREADS) k_xrange(const Params p) {
-  __shared__ unsigned long long s_red[2][PT_THREADS / 32];
-  const int b = blockIdx.y;
-  const int n = p.fs[b].n_points, i0 = blockIdx.x * PT_PER_BLOCK;
-  if (i0 >= n) return;
-  const size_t fbase = (size_t)b * p.P;
-  const int i1 = min(n, i0 + PT_PER_BLOCK);
-  unsigned long long kmax = 0, kmin_inv = 0;
-  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
-    const uint32_t px = p.pix[fbase + i];
-    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
-    const double z = depth_to_z(p, fbase + px);
-    const unsigned long long k = ordered_key(deproject_axis((double)u, p.cx, z, p.fx));
-    p.xkey_c[fbase + i] = k;
-    p.ykey_c[fbase + i] = ordered_key(deproject_axis((double)v, p.cy, z, p.fy));  // selection key for k_select_sort
-    kmax = k > kmax ? k : kmax;
-    kmin_inv = ~k > kmin_inv ? ~k : kmin_inv;
-  }
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  kmax = warp_max(kmax);
-  kmin_inv = warp_max(kmin_inv);
-  if (lane == 0) {
-    s_red[0][warp] = kmax;
-    s_red[1][warp] = kmin_inv;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    for (int w = 1; w < PT_THREADS / 32; ++w) {
-      kmax = s_red[0][w] > kmax ? s_red[0][w] : kmax;
-      kmin_inv = s_red[1][w] > kmin_inv ? s_red[1][w] : kmin_inv;
-    }
-    atomicMax(&p.fs[b].xmax_key, kmax);
-    atomicMax(&p.fs[b].xmin_inv_key, kmin_inv);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// k_bin_hist / k_bin_offsets / k_scatter: counting sort of the points by x-bin
-// ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
-  __shared__ int s_hist[NUM_BINS];
-  const int b = blockIdx.y;
-  const FrameState& f = p.fs[b];
-  const int n = f.n_points, i0 = blockIdx.x * PT_PER_BLOCK;
-  double x_min, width;
-  if (i0 >= n || !frame_bins(f, x_min, width)) return;
-  if (threadIdx.x < NUM_BINS) s_hist[threadIdx.x] = 0;
-  __syncthreads();
-  const size_t fbase = (size_t)b * p.P;
-  const int i1 = min(n, i0 + PT_PER_BLOCK);
-  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
-    const int bin = bin_of(key_to_double(p.xkey_c[fbase + i]), x_min, width);
-    p.bins[fbase + i] = (uint8_t)bin;
-    atomicAdd(&s_hist[bin], 1);
-  }
-  __syncthreads();
-  if (threadIdx.x < NUM_BINS && s_hist[threadIdx.x]) atomicAdd(&p.fs[b].bin_count[threadIdx.x], s_hist[threadIdx.x]);
-}
-
-__global__ void k_bin_offsets(const Params p) {
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= p.B) return;
+// (Points arrive in row-major pixel order, so the 32 points of a warp fall into one or two bins; grouping the lanes with
+// match.any before the shared-memory atomic was measured slower than the plain atomic, which the hardware already folds
+// for lanes that hit one address.)
+// k per bin, bin offsets, edge offsets and the frame status from the 50 counts (geometry_utils.py:121-138)
+__device__ void finalize_bins(const Params& p, int b, const volatile int* counts) {
   FrameState& f = p.fs[b];
   double x_min, width;
   int status = RDP_FRAME_OK, off = 0, eoff = 0;
@@ -368,7 +344,7 @@ __global__ void k_bin_offsets(const Params p) {
     status = RDP_FRAME_DEGENERATE_BINS;
   }
   for (int i = 0; i < NUM_BINS; ++i) {
-    const int c = status == RDP_FRAME_OK ? f.bin_count[i] : 0;
+    const int c = status == RDP_FRAME_OK ? counts[i] : 0;
     int k = 0;
     if (c > 0) {
       k = (int)__dmul_rn((double)c, 0.05);  // int(cnt * top_k_percent), geometry_utils.py:138
@@ -386,6 +362,43 @@ __global__ void k_bin_offsets(const Params p) {
   f.n_edge = eoff;
   if (status == RDP_FRAME_OK && eoff < MIN_EDGE) status = RDP_FRAME_TOO_FEW_EDGE;
   f.status = status;
+}
+
+__global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
+  __shared__ int s_hist[NUM_BINS];
+  __shared__ int s_last;
+  const int b = blockIdx.y;
+  FrameState& f = p.fs[b];
+  const int n = f.n_points, i0 = blockIdx.x * PT_PER_BLOCK;
+  double x_min, width;
+  if (!frame_bins(f, x_min, width)) {  // too few points or zero width: nothing to count, block 0 records the status
+    if (blockIdx.x == 0 && threadIdx.x == 0) finalize_bins(p, b, f.bin_count);
+    return;
+  }
+  if (i0 >= n) return;
+  if (threadIdx.x < NUM_BINS) s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const size_t fbase = (size_t)b * p.P;
+  const int i1 = min(n, i0 + PT_PER_BLOCK);
+  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
+    const int bin = bin_of(key_to_double(p.xkey_c[fbase + i]), x_min, width);
+    p.bins[fbase + i] = (uint8_t)bin;
+    atomicAdd(&s_hist[bin], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x < NUM_BINS && s_hist[threadIdx.x]) atomicAdd(&f.bin_count[threadIdx.x], s_hist[threadIdx.x]);
+  // the block that adds its counts last turns them into offsets (what used to be a launch of its own)
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int blocks = (n + PT_PER_BLOCK - 1) / PT_PER_BLOCK;
+    s_last = atomicAdd(&f.hist_done, 1) == blocks - 1;
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    finalize_bins(p, b, f.bin_count);
+  }
 }
 
 __global__ void __launch_bounds__(PT_THREADS) k_scatter(const Params p) {
@@ -430,9 +443,20 @@ __device__ __forceinline__ bool key_has_prefix(unsigned long long yk, uint32_t n
   return (npx >> (32 - 8 * (d - 8))) == (pl >> (32 - 8 * (d - 8)));
 }
 
+// Shared memory of k_select_sort.  A bin of up to SEL_STAGE_CAP points is copied in once (y key + pixel id, 12 bytes a
+// point) and every radix pass, the gather and the sort then stay on chip; its k <= 5 % selected points are sorted in the
+// small arrays.  Larger bins (HD frames, thick bands) keep reading global memory and use the staging area as their
+// SORT_CAP-sized sort buffer instead.  The kernel is a chain of short phases between barriers, so what it needs most is
+// resident CTAs: a 3072-point staging area (39 KB, 5 CTAs per SM) measured 1.7x slower than this one (14 KB, 16 per SM).
+constexpr int SEL_STAGE_CAP = 1024;
+constexpr int SEL_SMALL_SORT = SEL_STAGE_CAP / 20 + 4;   // k = max(1, int(cnt * 0.05)) for cnt <= SEL_STAGE_CAP
+static_assert(SEL_STAGE_CAP * 12 >= SORT_CAP * 12, "the staging area doubles as the large sort buffer");
+
 __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
-  __shared__ unsigned long long s_sk[SORT_CAP];  // x sort keys of the selected points
-  __shared__ uint32_t s_sp[SORT_CAP];            // their pixel ids
+  __shared__ unsigned long long s_stage_key[SEL_STAGE_CAP];   // staged y keys | x sort keys of a large bin
+  __shared__ uint32_t s_stage_pix[SEL_STAGE_CAP];             // staged pixel ids | pixel ids of a large bin's selection
+  __shared__ unsigned long long s_small_key[SEL_SMALL_SORT];  // x sort keys of a staged bin's selection
+  __shared__ uint32_t s_small_pix[SEL_SMALL_SORT];
   __shared__ int s_hist[256];
   __shared__ unsigned long long s_ph, s_mm[2][SEL_THREADS / 32];
   __shared__ uint32_t s_pl;
@@ -444,13 +468,19 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
   const int cnt = f.bin_count[bin], k = f.bin_k[bin];
   if (cnt == 0) return;
   const size_t fbase = (size_t)b * p.P;
+  const bool staged = cnt <= SEL_STAGE_CAP;
   const uint32_t* seg = p.binned + fbase + f.bin_off[bin];              // pixel ids of the bin
   const unsigned long long* ykeys = p.ykey_b + fbase + f.bin_off[bin];  // their ordered fp64 y keys
 
-  // common leading digits of the y keys (they are clustered: a bin spans a few centimetres)
+  // one read of the bin from global memory: stage it (when it fits) and find the leading digits every key shares
+  // (the keys are clustered: a bin spans a few centimetres)
   unsigned long long kmax = 0, kmin_inv = 0;
   for (int i = tid; i < cnt; i += SEL_THREADS) {
     const unsigned long long yk = ykeys[i];
+    if (staged) {
+      s_stage_key[i] = yk;
+      s_stage_pix[i] = seg[i];
+    }
     kmax = yk > kmax ? yk : kmax;
     kmin_inv = ~yk > kmin_inv ? ~yk : kmin_inv;
   }
@@ -476,6 +506,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
     s_nsel = 0;
   }
   __syncthreads();
+  auto key_at = [&](int i) { return staged ? s_stage_key[i] : ykeys[i]; };
+  auto pix_at = [&](int i) { return staged ? s_stage_pix[i] : seg[i]; };
 
   if (!s_done) {
     for (int d = s_start; d < 12; ++d) {
@@ -484,8 +516,8 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
       const unsigned long long ph = s_ph;
       const uint32_t pl = s_pl;
       for (int i = tid; i < cnt; i += SEL_THREADS) {
-        const unsigned long long yk = ykeys[i];
-        const uint32_t npx = d >= 8 ? ~seg[i] : 0u;  // the pixel id only matters once the whole y key is tied
+        const unsigned long long yk = key_at(i);
+        const uint32_t npx = d >= 8 ? ~pix_at(i) : 0u;  // the pixel id only matters once the whole y key is tied
         if (key_has_prefix(yk, npx, d, ph, pl)) atomicAdd(&s_hist[key_digit(yk, npx, d)], 1);
       }
       __syncthreads();
@@ -526,14 +558,14 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
   // gather the selected points with their x sort key
   const unsigned long long th = s_done && k >= cnt ? 0ull : s_ph;
   const uint32_t tl = s_done && k >= cnt ? 0u : s_pl;
-  const bool sort_in_smem = k <= SORT_CAP;
+  const bool sort_in_smem = staged || k <= SORT_CAP;
   const size_t ebase = (size_t)b * p.ecap + f.edge_off[bin];
-  unsigned long long* sk = sort_in_smem ? s_sk : p.edge_key + ebase;
-  uint32_t* sp = sort_in_smem ? s_sp : p.edge_pix + ebase;
+  unsigned long long* sk = staged ? s_small_key : (sort_in_smem ? s_stage_key : p.edge_key + ebase);
+  uint32_t* sp = staged ? s_small_pix : (sort_in_smem ? s_stage_pix : p.edge_pix + ebase);
   for (int i = tid; i < cnt; i += SEL_THREADS) {
-    const unsigned long long yk = ykeys[i];
+    const unsigned long long yk = key_at(i);
     if (yk < th) continue;
-    const uint32_t px = seg[i];
+    const uint32_t px = pix_at(i);
     if (yk > th || ~px >= tl) {
       const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
       const int pos = atomicAdd(&s_nsel, 1);
@@ -2025,7 +2057,7 @@ extern "C" int rdp_geom_workspace_bytes(int B, int H, int W, size_t* bytes) {
   return RDP_OK;
 }
 
-extern "C" int rdp_geom_launch_count(void) { return 9; }
+extern "C" int rdp_geom_launch_count(void) { return 7; }
 
 static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt, int B, int H, int W,
                           const double* intrinsics, double depth_scale, const RdpCurvatureOut* out,
@@ -2065,11 +2097,7 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   else k_deproject<false><<<tiles_total, DP_THREADS, 0, stream>>>(p);
   mark();
   const dim3 pgrid((p.P + PT_PER_BLOCK - 1) / PT_PER_BLOCK, B);
-  k_xrange<<<pgrid, PT_THREADS, 0, stream>>>(p);
-  mark();
   k_bin_hist<<<pgrid, PT_THREADS, 0, stream>>>(p);
-  mark();
-  k_bin_offsets<<<(B + 63) / 64, 64, 0, stream>>>(p);
   mark();
   k_scatter<<<pgrid, PT_THREADS, 0, stream>>>(p);
   mark();

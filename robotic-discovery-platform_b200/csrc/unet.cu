@@ -130,9 +130,11 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // Drains one 128 x BN fp32 accumulator tile: BN shift + ReLU -> bf16 NHWC store; for the last layer also the 1x1
 // OutConv (+ mask rule).  Thread = one pixel (TMEM lane); 32-column chunks, the next chunk's tcgen05.ld is in
 // flight while the current one is processed.
+// acc_empty_bar: local barrier to arrive on once the accumulator stage is drained (may be null); remote_empty: the same
+// as a shared::cluster address when the MMA issuer lives in the other CTA of a pair (0 = use the local barrier).
 template <int BN, bool POOL = false>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* s_aux, uint32_t taddr, int nt, int n, int y,
-                                              int x, bool inside, uint64_t* acc_empty_bar, int lane) {
+                                              int x, bool inside, uint64_t* acc_empty_bar, int lane, uint32_t remote_empty = 0) {
   const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
   const bool head_on = BN == 64 && p.head_w != nullptr;
   float head[8];
@@ -145,10 +147,13 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     // What matters to the MMA warp is how long a stage is held, and the 64-wide tiles are short.
     tmem_ld_32x32(taddr + 32, r[1]);
     tmem_ld_wait();
-    if (acc_empty_bar != nullptr) {
+    if (acc_empty_bar != nullptr || remote_empty != 0) {
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(acc_empty_bar);
+      if (lane == 0) {
+        if (remote_empty) mbar_arrive_cluster(remote_empty);
+        else mbar_arrive(acc_empty_bar);
+      }
     }
   }
 #pragma unroll
@@ -224,10 +229,13 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     }
   }
   // accumulator stage drained: hand it back to the MMA warp
-  if (BN != 64 && acc_empty_bar != nullptr) {
+  if (BN != 64 && (acc_empty_bar != nullptr || remote_empty != 0)) {
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(acc_empty_bar);
+    if (lane == 0) {
+      if (remote_empty) mbar_arrive_cluster(remote_empty);
+      else mbar_arrive(acc_empty_bar);
+    }
   }
   if (BN == 64 && head_on && inside) {
     const size_t hw_px = (size_t)p.H * p.W, off = (size_t)y * p.W + x;
@@ -387,6 +395,12 @@ constexpr int HALO_BAR_BYTES = 512;  // barriers; the epilogue constants follow 
 // shift[cout], then (only for the head layer) OutConv weights and bias
 inline int aux_bytes(int cout, bool head) { return (cout + (head ? AUX_HEAD_FLOATS + 8 : 0)) * 4; }
 
+// Accumulator stages in tensor memory: the 64-wide layers finish a tile's MMAs in about a microsecond while their
+// epilogue stores a whole tile (and its pooled copy) to HBM, so four stages (256 of the 512 columns) let the MMA warp
+// run ahead of a slow store instead of waiting for it; the wider layers keep two.
+__host__ __device__ constexpr int acc_stages(int bn, int tiles) { return (bn == 64 && tiles == 1) ? 4 : 2; }
+constexpr int MAX_ACC_STAGES = 4;
+
 struct HaloCfg {
   int sa, sb;  // A (halo) stages, B (weight slice) stages
   int sl;      // source-patch stages of the fused upsample (1 or 2)
@@ -420,10 +434,11 @@ __device__ __forceinline__ void halo_mma_loop(const ConvParams& p, const HaloCfg
     mbar_wait(w_full, 0);
     tc_fence_after();
   }
+  constexpr int NACC = acc_stages(BN, TILES);
   int work = blockIdx.x;
   while (work < p.total_work) {
 #pragma unroll
-    for (int as = 0; as < 2; ++as) {
+    for (int as = 0; as < NACC; ++as) {
       if (work < p.total_work) {
         RDP_DEV(t0 = clock64();)
         mbar_wait(&acc_empty[as], aphase ^ 1);
@@ -541,7 +556,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint8_t* smem_a = smem;
   constexpr int HW = halo_w(TILES), HALO_BYTES = halo_bytes(TILES), HALO_STRIDE = halo_stride(TILES);
   constexpr int PATCH_W = patch_w(TILES), PATCH_BYTES = patch_bytes(TILES), PATCH_STRIDE = patch_stride(TILES);
-  static_assert(2 * TILES * BN <= 512, "accumulators exceed TMEM");
+  static_assert(acc_stages(BN, TILES) * TILES * BN <= 512, "accumulators exceed TMEM");
   uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
   const int b_bytes = RESIDENT ? 9 * ncb * B_BLOCK : cfg.sb * B_BLOCK;
   uint8_t* smem_l = smem_b + b_bytes;  // low-resolution source patches (INTERP only)
@@ -551,12 +566,13 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   uint64_t* full_b = bars + 2 * HALO_MAX_STAGES;    // [HALO_MAX_STAGES]
   uint64_t* empty_b = bars + 3 * HALO_MAX_STAGES;   // [HALO_MAX_STAGES]
   uint64_t* w_full = bars + 4 * HALO_MAX_STAGES;    // [1]
-  uint64_t* acc_full = w_full + 1;                  // [2]
-  uint64_t* acc_empty = w_full + 3;                 // [2]
-  uint64_t* full_l = w_full + 5;                    // [PATCH_STAGES]
-  uint64_t* empty_l = w_full + 5 + PATCH_STAGES;    // [PATCH_STAGES]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_full + 5 + 2 * PATCH_STAGES);
-  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 512);
+  uint64_t* acc_full = w_full + 1;                  // [MAX_ACC_STAGES]
+  uint64_t* acc_empty = acc_full + MAX_ACC_STAGES;  // [MAX_ACC_STAGES]
+  uint64_t* full_l = acc_empty + MAX_ACC_STAGES;    // [PATCH_STAGES]
+  uint64_t* empty_l = full_l + PATCH_STAGES;        // [PATCH_STAGES]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(empty_l + PATCH_STAGES);
+  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + HALO_BAR_BYTES);
+  constexpr int NACC = acc_stages(BN, TILES);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   stage_aux(p, s_aux);
@@ -572,7 +588,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       mbar_init(&empty_b[s], 1);
     }
     mbar_init(w_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < MAX_ACC_STAGES; ++s) {
       mbar_init(&acc_full[s], 1);
       mbar_init(&acc_empty[s], 4);
     }
@@ -582,7 +598,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 2 * TILES * BN);
+  if (warp == 1) tmem_alloc(tmem_slot, NACC * TILES * BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -694,7 +710,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     int it = 0;
     for (int work = blockIdx.x; work < p.total_work; work += gridDim.x, ++it) {
       if (EG > 1 && (it % EG) != group) continue;
-      const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+      const uint32_t as = it % NACC, aphase = (it / NACC) & 1;
       const int nt = work % p.n_tiles;
       int m = work / p.n_tiles;
       const int tx = m % p.tiles_x; m /= p.tiles_x;
@@ -721,7 +737,267 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 2 * TILES * BN);
+    tmem_dealloc(tmem_base, NACC * TILES * BN);
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// k_conv3x3_pair: the halo kernel on CTA pairs (tcgen05 cta_group::2) for the 64- and 128-wide layers
+// ---------------------------------------------------------------------------------------------------------
+// With both operands in shared memory a 128 x N x 16 MMA reads 4 KB of A and N*32 bytes of B: at 128 bytes per cycle
+// that is 48 cycles for 32 cycles of tensor work at N = 64 and 64 for 64 at N = 128 - the full-resolution layers are
+// bounded by operand reads, not by the tensor pipe.  A pair of CTAs on the two SMs of a TPC issues one M = 256 MMA:
+// each CTA keeps its own 128-pixel tile (its own halo blocks) and only HALF of the weight slice, so the reads per MMA
+// drop to 4 KB + N*16 bytes per SM (40 cycles at N = 64, 48 at N = 128), and the halved weights stay resident in shared
+// memory for every 64-wide layer and for down1.  Layout, halo addressing, epilogue and the fused up-sampling are those
+// of k_conv3x3_halo (TILES = 1); what changes is the synchronisation:
+//   * the leader (cluster rank 0) issues every MMA; the barriers it waits on (full_a, full_b, w_full, acc_empty) live
+//     in ITS shared memory and expect one arrival per CTA (acc_empty: four epilogue warps per CTA); the peer reaches them
+//     through their shared::cluster address, its TMA loads complete on them directly (cp.async.bulk.tensor .cta_group::2);
+//   * the barriers the producers and epilogues wait on (empty_a, empty_b, acc_full) are local to each CTA and are
+//     signalled in both CTAs at once by tcgen05.commit ... .multicast::cluster;
+//   * tensor memory is allocated and freed by one warp in each CTA with the cta_group::2 forms, with cluster-wide
+//     barriers after set-up and before tear-down (the peer's shared memory and barriers must outlive the leader's MMAs).
+// Work item = two spatial tiles with consecutive indices (the leader takes the even one); an odd tile count leaves the
+// last peer a tile beyond the batch: its loads are zero-filled by the TMA unit and its epilogue stores nothing.
+template <int BN, bool RESIDENT, bool INTERP>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(conv_threads(INTERP, BN, 1), 1)
+k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
+               const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
+  constexpr int B_HALF = (BN / 2) * BLOCK_K * 2;  // this CTA's half of one 64-wide weight slice
+  constexpr int HW = halo_w(1), HALO_BYTES = halo_bytes(1), HALO_STRIDE = halo_stride(1);
+  constexpr int PATCH_W = patch_w(1), PATCH_BYTES = patch_bytes(1), PATCH_STRIDE = patch_stride(1);
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int ncb = p.kb0 + p.kb1;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
+  const int b_bytes = RESIDENT ? 9 * ncb * B_HALF : cfg.sb * B_HALF;
+  uint8_t* smem_l = smem_b + b_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_l + (INTERP ? cfg.sl * PATCH_STRIDE : 0));
+  uint64_t* full_a = bars;                          // [HALO_MAX_STAGES]  leader's is used (2 arrivals)
+  uint64_t* empty_a = bars + HALO_MAX_STAGES;       // [HALO_MAX_STAGES]  local, multicast commit
+  uint64_t* full_b = bars + 2 * HALO_MAX_STAGES;    // [HALO_MAX_STAGES]  leader's
+  uint64_t* empty_b = bars + 3 * HALO_MAX_STAGES;   // [HALO_MAX_STAGES]  local
+  uint64_t* w_full = bars + 4 * HALO_MAX_STAGES;    // [1]                leader's
+  uint64_t* acc_full = w_full + 1;                  // [MAX_ACC_STAGES]   local
+  uint64_t* acc_empty = acc_full + MAX_ACC_STAGES;  // [MAX_ACC_STAGES]   leader's (8 arrivals)
+  uint64_t* full_l = acc_empty + MAX_ACC_STAGES;    // [PATCH_STAGES]     local
+  uint64_t* empty_l = full_l + PATCH_STAGES;        // [PATCH_STAGES]     local
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(empty_l + PATCH_STAGES);
+  float* s_aux = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + HALO_BAR_BYTES);
+  constexpr int NACC = acc_stages(BN, 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int m_total = p.B * p.tiles_y * p.tiles_x;       // spatial tiles (n_tiles == 1 for these layers)
+  const int pair_work = (m_total + 1) >> 1;
+  stage_aux(p, s_aux);
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_src0);
+    prefetch_tensormap(&map_src1);
+    prefetch_tensormap(&map_w);
+    for (int s = 0; s < HALO_MAX_STAGES; ++s) {
+      mbar_init(&full_a[s], 2);
+      mbar_init(&empty_a[s], 1);
+      mbar_init(&full_b[s], 2);
+      mbar_init(&empty_b[s], 1);
+    }
+    mbar_init(w_full, 2);
+    for (int s = 0; s < MAX_ACC_STAGES; ++s) {
+      mbar_init(&acc_full[s], 1);
+      mbar_init(&acc_empty[s], 8);
+    }
+    for (int s = 0; s < PATCH_STAGES; ++s) {
+      mbar_init(&full_l[s], 1);
+      mbar_init(&empty_l[s], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc_pair(tmem_slot, NACC * BN);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // both CTAs' barriers are initialised and both allocations done before anyone touches the peer
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // tile of this CTA for pair-level work item w
+  auto decode = [&](int w, int& tx, int& ty, int& n) {
+    int m = 2 * w + (int)rank;
+    tx = m % p.tiles_x; m /= p.tiles_x;
+    ty = m % p.tiles_y;
+    n = m / p.tiles_y;   // n >= B: the tile beyond the batch (loads zero-filled, nothing stored)
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ================= TMA producer (both CTAs; completion on the leader's barriers) =================
+      if (RESIDENT) {
+        const uint32_t wbar = mapa_u32(smem_u32(w_full), 0);
+        mbar_arrive_expect_tx_cluster(wbar, 9 * ncb * B_HALF);
+        for (int cb = 0; cb < ncb; ++cb)
+          for (int tap = 0; tap < 9; ++tap)
+            tma_load_2d_pair(smem_b + (cb * 9 + tap) * B_HALF, &map_w, tap * p.cin_pad + cb * BLOCK_K, (int)rank * (BN / 2), wbar);
+      }
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, sl = 0, pl = 0;
+      for (int work = pair; work < pair_work; work += n_pairs) {
+        int tx, ty, n;
+        decode(work, tx, ty, n);
+        const int x0 = tx * 8, y0 = ty * 16;
+        const int sy0 = INTERP ? patch_origin(p.ry, y0 - 1, p.pad_y) : 0, sx0 = INTERP ? patch_origin(p.rx, x0 - 1, p.pad_x) : 0;
+        int next_patch = p.kb0;
+        auto issue_patch = [&]() {
+          mbar_wait(&empty_l[sl], pl ^ 1);
+          mbar_arrive_expect_tx(&full_l[sl], PATCH_BYTES);
+          tma_load_4d(smem_l + sl * PATCH_STRIDE, &map_src1, (next_patch - p.kb0) * BLOCK_K, sx0, sy0, n, &full_l[sl]);
+          if (++sl == (uint32_t)cfg.sl) { sl = 0; pl ^= 1; }
+          ++next_patch;
+        };
+        if (INTERP) {
+          for (int i = 0; i < cfg.sl && next_patch < ncb; ++i) issue_patch();
+        }
+        for (int cb = 0; cb < ncb; ++cb) {
+          const CUtensorMap* src = cb < p.kb0 ? &map_src0 : &map_src1;
+          const int c0 = (cb < p.kb0 ? cb : cb - p.kb0) * BLOCK_K;
+          mbar_wait(&empty_a[sa], pa ^ 1);
+          if (!INTERP || cb < p.kb0) {
+            const uint32_t abar = mapa_u32(smem_u32(&full_a[sa]), 0);
+            mbar_arrive_expect_tx_cluster(abar, HALO_BYTES);
+            tma_load_4d_pair(smem_a + sa * HALO_STRIDE, src, c0, x0 - 1, y0 - 1, n, abar);
+          }
+          if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+          if (!RESIDENT) {
+#pragma unroll 1
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(&empty_b[sb], pb ^ 1);
+              const uint32_t bbar = mapa_u32(smem_u32(&full_b[sb]), 0);
+              mbar_arrive_expect_tx_cluster(bbar, B_HALF);
+              tma_load_2d_pair(smem_b + sb * B_HALF, &map_w, tap * p.cin_pad + cb * BLOCK_K, (int)rank * (BN / 2), bbar);
+              if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
+            }
+          }
+          if (INTERP && cb >= p.kb0 && next_patch < ncb) issue_patch();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer: the leader's warp walks the loop converged, one elected lane issues =================
+    if (rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * TILE_M, BN);
+      constexpr uint32_t hi_a = desc_hi(HW * 128), hi_b = desc_hi(1024);
+      uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
+      const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
+      if (RESIDENT) {
+        mbar_wait_cluster(w_full, 0);
+        tc_fence_after();
+      }
+      int work = pair;
+      while (work < pair_work) {
+#pragma unroll
+        for (int as = 0; as < NACC; ++as) {
+          if (work < pair_work) {
+            mbar_wait_cluster(&acc_empty[as], aphase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_acc = tmem_base + as * BN;
+            for (int cb = 0; cb < ncb; ++cb) {
+              mbar_wait_cluster(&full_a[sa], pa);
+              tc_fence_after();
+              const uint32_t a_lo = a_lo0 + sa * (HALO_STRIDE >> 4);
+              const uint32_t bres_lo = b_lo0 + cb * (9 * B_HALF >> 4);
+#pragma unroll
+              for (int tap = 0; tap < 9; ++tap) {
+                uint32_t b_lo;
+                if (RESIDENT) {
+                  b_lo = bres_lo + tap * (B_HALF >> 4);
+                } else {
+                  mbar_wait_cluster(&full_b[sb], pb);
+                  tc_fence_after();
+                  b_lo = b_lo0 + sb * (B_HALF >> 4);
+                }
+                const uint32_t at_lo = a_lo + ((tap / 3) * HW + tap % 3) * 8;  // 128 bytes per halo row
+#pragma unroll
+                for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+                  mma_bf16_ss_pair_elect(tmem_acc, desc_pack(at_lo + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc, (cb | tap | k) != 0);
+                if (!RESIDENT) {
+                  tc_commit_pair_elect(&empty_b[sb]);
+                  if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
+                }
+              }
+              tc_commit_pair_elect(&empty_a[sa]);
+              if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+            }
+            tc_commit_pair_elect(&acc_full[as]);
+            work += n_pairs;
+          }
+        }
+        aphase ^= 1;
+      }
+    }
+  } else if (INTERP && warp >= 2 + 4 * epi_groups(BN, INTERP)) {
+    // ================= interpolation producers: halo blocks of the up-sampled branch, each CTA its own tile =================
+    constexpr int IT = interp_warps(BN, 1) * 32;
+    const int t = threadIdx.x - (2 + 4 * epi_groups(BN, INTERP)) * 32;
+    const int j = t & 7;
+    uint32_t sa = 0, pa = 0, sl = 0, pl = 0;
+    for (int work = pair; work < pair_work; work += n_pairs) {
+      int tx, ty, n;
+      decode(work, tx, ty, n);
+      const int x0 = tx * 8 - 1, y0 = ty * 16 - 1;
+      const int sy0 = patch_origin(p.ry, y0, p.pad_y), sx0 = patch_origin(p.rx, x0, p.pad_x);
+      for (int cb = 0; cb < ncb; ++cb) {
+        mbar_wait(&empty_a[sa], pa ^ 1);
+        if (cb >= p.kb0) {
+          mbar_wait(&full_l[sl], pl);
+          uint8_t* stage = smem_a + sa * HALO_STRIDE;
+          const uint8_t* patch = smem_l + sl * PATCH_STRIDE;
+#pragma unroll 4
+          for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
+            const int hy = px / HW, hx = px - hy * HW;
+            const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
+            *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;
+          }
+          fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (the leader's MMA reads both CTAs)
+          asm volatile("bar.sync 1, %0;" ::"n"(IT) : "memory");
+          if (t == 0) {
+            mbar_arrive_cluster(mapa_u32(smem_u32(&full_a[sa]), 0));
+            mbar_arrive(&empty_l[sl]);
+          }
+          if (++sl == (uint32_t)cfg.sl) { sl = 0; pl ^= 1; }
+        }
+        if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue: each CTA drains its own 128 rows =================
+    constexpr int EG = epi_groups(BN, INTERP);
+    const int group = (warp - 2) >> 2;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    int it = 0;
+    for (int work = pair; work < pair_work; work += n_pairs, ++it) {
+      if (EG > 1 && (it % EG) != group) continue;
+      const uint32_t as = it % NACC, aphase = (it / NACC) & 1;
+      int tx, ty, n;
+      decode(work, tx, ty, n);
+      const bool real = n < p.B;
+      const int y = real ? ty * 16 + (row >> 3) : p.H + 16, x = tx * 8 + (row & 7);
+      const bool inside = y < p.H && x < p.W;
+      mbar_wait(&acc_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
+      epilogue_tile<BN, true>(p, s_aux, taddr, 0, real ? n : 0, y, x, inside, nullptr, lane, mapa_u32(smem_u32(&acc_empty[as]), 0));
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();  // the peer's shared memory, barriers and tensor memory stay alive until the leader is done with them
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, NACC * BN);
   }
 }
 
@@ -1199,6 +1475,7 @@ constexpr int MAP_CACHE_ENTRIES = 8;
 struct RdpUnet {
   RdpUnetWeights w;
   CUtensorMap wmap[18];
+  CUtensorMap wmap_half[18];  // box of bn/2 rows: each CTA of a pair loads its half of a weight slice (bn <= 128 only)
   int bn[18];
   int cin_pad[18];
   int num_sms;
@@ -1339,6 +1616,50 @@ int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUten
   return RDP_OK;
 }
 
+template <int BN, bool RESIDENT, bool INTERP>
+int launch_conv_pair_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm_half, const ConvParams& p,
+                       const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3_pair<BN, RESIDENT, INTERP>), HALO_SMEM_TOTAL));
+  const int pair_work = (p.B * p.tiles_y * p.tiles_x + 1) / 2;
+  const int pairs = std::min(pair_work, num_sms / 2);
+  k_conv3x3_pair<BN, RESIDENT, INTERP><<<2 * pairs, conv_threads(INTERP, BN, 1), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm_half, p, cfg);
+  return RDP_OK;
+}
+
+// Pairs pay where the halved weight slices stay resident in shared memory; with streamed slices every tap is a
+// two-CTA hand-shake and the pair runs several times slower than two independent CTAs (measured on up3.0, up2.3).
+inline bool pair_weights_resident(int bn, int ncb, int cout, bool head, bool low) {
+  const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(cout, head) + (low ? patch_stride(1) : 0);
+  return 9 * ncb * (bn / 2) * BLOCK_K * 2 + 3 * halo_stride(1) <= HALO_SMEM_TOTAL - fixed;
+}
+
+// CTA pairs (k_conv3x3_pair): 8x16 tiles, each CTA holds half of every weight slice.
+template <int BN>
+int launch_conv_pair(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm_half, const ConvParams& p, int num_sms,
+                     cudaStream_t stream) {
+  const int ncb = p.kb0 + p.kb1, b_half = (BN / 2) * BLOCK_K * 2;
+  const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(p.cout, p.head_w != nullptr) + (p.low ? patch_stride(1) : 0);
+  int budget = HALO_SMEM_TOTAL - fixed;
+  HaloCfg cfg{};
+  cfg.sl = 1;
+  const int w_bytes = 9 * ncb * b_half;
+  if (w_bytes + 3 * halo_stride(1) <= budget) {  // half slices resident: every 64-wide layer, down1.0 and down1.3
+    cfg.sb = 0;
+    cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / halo_stride(1));
+    if (p.low && budget - w_bytes - cfg.sa * halo_stride(1) >= patch_stride(1)) cfg.sl = 2;
+    return p.low ? launch_conv_pair_t<BN, true, true>(s0, s1, wm_half, p, cfg, num_sms, stream)
+                 : launch_conv_pair_t<BN, true, false>(s0, s1, wm_half, p, cfg, num_sms, stream);
+  }
+  cfg.sa = 3;
+  if (p.low) {
+    cfg.sl = 2;
+    budget -= patch_stride(1);
+  }
+  cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * halo_stride(1)) / b_half);
+  return p.low ? launch_conv_pair_t<BN, false, true>(s0, s1, wm_half, p, cfg, num_sms, stream)
+               : launch_conv_pair_t<BN, false, false>(s0, s1, wm_half, p, cfg, num_sms, stream);
+}
+
 // Super-tiles (two 8x16 tiles per work item) pay off where weights stream from L2 and two accumulator pairs fit TMEM.
 inline int halo_tiles_for(int bn, int n_tiles, int ncb, bool interp) {
   static const int env = dev_env("RDP_HALO_TILES") ? atoi(dev_env("RDP_HALO_TILES")) : 0;
@@ -1420,7 +1741,8 @@ extern "C" int rdp_unet_create(const RdpUnetWeights* w, RdpUnet** out) {
     net->cin_pad[i] = i == 0 ? 64 : cin[i];
     net->bn[i] = cout[i] >= 256 ? 256 : cout[i];
     const int K = i == 0 ? 64 : 9 * cin[i];
-    const int rc = make_weight_map(&net->wmap[i], L.weight, K, cout[i], net->bn[i]);
+    int rc = make_weight_map(&net->wmap[i], L.weight, K, cout[i], net->bn[i]);
+    if (rc == RDP_OK && i > 0 && net->bn[i] <= 128) rc = make_weight_map(&net->wmap_half[i], L.weight, K, cout[i], net->bn[i] / 2);
     if (rc != RDP_OK) {
       delete net;
       return rc;
@@ -1493,7 +1815,10 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   static const bool force_v1 = dev_env("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
   static const char* sel_env = dev_env("RDP_CONV_SEL");
-  const char* sel = (sel_env && strlen(sel_env) == 18) ? sel_env : "1hhhhhhhhhhhhhhhhh";
+  // 'p' = halo reuse on CTA pairs (cta_group::2): the 64- and 128-wide layers, whose MMAs are bounded by operand reads
+  // (measured, batch 64 at 640x480, pair vs two independent CTAs: down1.3 0.94 vs 1.19 ms, up3.3 0.59 vs 0.69, up4.0 2.34
+  // vs 2.80, up4.3 1.40 vs 1.49; inc.3 and down1.0, one 64-channel block per tile, lose to the per-tile hand-shake)
+  const char* sel = (sel_env && strlen(sel_env) == 18) ? sel_env : "1hhphhhhhhhhhhhppp";
   auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
   int n_marks = 0;
   auto mark = [&]() {
@@ -1541,9 +1866,11 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const Level L = buf.lv[kConvLevel[i]];
     ConvParams p{};
     p.B = B; p.H = L.H; p.W = L.W;
-    const bool halo = taps == 9 && !force_v1 && sel[i] == 'h';
     const int cout_i = net->w.conv[i].cout;
-    const int tiles = halo ? halo_tiles_for(net->bn[i], cout_i / net->bn[i], (c0 + c1) / 64, low != nullptr) : 1;
+    const bool pair = taps == 9 && !force_v1 && sel[i] == 'p' && net->bn[i] <= 128 && cout_i == net->bn[i] && net->num_sms >= 2 &&
+                      pair_weights_resident(net->bn[i], (c0 + c1) / 64, cout_i, i == 17 && !debug_nohead, low != nullptr);
+    const bool halo = taps == 9 && !force_v1 && (sel[i] == 'h' || sel[i] == 'p');
+    const int tiles = (halo && !pair) ? halo_tiles_for(net->bn[i], cout_i / net->bn[i], (c0 + c1) / 64, low != nullptr) : 1;
     if (halo) { p.tile_w = 8 * tiles; p.tile_h = 16; }
     else pick_tile(L.H, L.W, p.tile_w, p.tile_h);
     p.tiles_x = (L.W + p.tile_w - 1) / p.tile_w;
@@ -1584,6 +1911,12 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     });
     if (rc != RDP_OK) return rc;
     const CUtensorMap &m0 = *pm0, &m1 = *pm1;
+    if (pair) {
+      rc = net->bn[i] == 64 ? launch_conv_pair<64>(m0, m1, net->wmap_half[i], p, net->num_sms, stream)
+                            : launch_conv_pair<128>(m0, m1, net->wmap_half[i], p, net->num_sms, stream);
+      mark();
+      return rc;
+    }
     if (halo) {
       switch (net->bn[i]) {
         case 64: rc = launch_conv_halo<64>(m0, m1, net->wmap[i], p, tiles, net->num_sms, stream); break;
@@ -1611,7 +1944,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   if (!first_fused) RDP_TRY(conv(0, buf.col, 64, nullptr, 0, 1));
   // MaxPool2d(2) of x1..x4 is a second output of the producing conv's epilogue (halo kernels); the stand-alone
   // pooling kernel remains for the per-tap fallback
-  auto fused_pool = [&](int i) { return !force_v1 && !no_fuse_pool && sel[i] == 'h'; };
+  auto fused_pool = [&](int i) { return !force_v1 && !no_fuse_pool && (sel[i] == 'h' || sel[i] == 'p'); };
   RDP_TRY(conv(1, buf.act[0], 64, nullptr, 0, 9, nullptr, fused_pool(1) ? buf.pool[0] : nullptr));
   for (int d = 0; d < 4; ++d) {
     const Level L = buf.lv[d];
@@ -1634,7 +1967,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const int C8 = Cl / 8;
     // up4.0 (64 output channels): interpolation warps slow the MMA issue warp down as much as the copy costs - measured
     // equal, so it keeps the simpler stand-alone upsample unless asked
-    const bool fuse_up = !force_v1 && !no_fuse_up && sel[10 + 2 * j] == 'h' && (net->bn[10 + 2 * j] >= 128 || fuse_up4);
+    const bool fuse_up = !force_v1 && !no_fuse_up && (sel[10 + 2 * j] == 'h' || sel[10 + 2 * j] == 'p') && (net->bn[10 + 2 * j] >= 128 || fuse_up4);
     if (fuse_up) {
       // the convolution's interpolation warps read the low-resolution tensor directly: no upsampled copy in HBM
       mark();

@@ -23,6 +23,7 @@ EXPORTS = [
     "rdp_geom_workspace_bytes", "rdp_geom_curvature", "rdp_geom_launch_count", "rdp_geom_curvature_profiled",
     "rdp_geom_deproject_static",
     "rdp_pre_resize", "rdp_post_mask_nearest", "rdp_post_mask_png_sizes", "rdp_post_mask_png",
+    "rdp_pre_decode_sizes", "rdp_pre_decode_jpeg", "rdp_pre_decode_png16",
 ]
 
 
@@ -96,6 +97,12 @@ def load() -> C.CDLL:
         lib.rdp_post_mask_png.argtypes = [C.c_void_p] + [C.c_int] * 3 + [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p,
                                                                         C.c_size_t, C.c_void_p]
         lib.rdp_post_mask_png.restype = C.c_int
+        lib.rdp_pre_decode_sizes.argtypes = [C.c_int] * 3 + [C.POINTER(C.c_size_t)] * 2
+        lib.rdp_pre_decode_sizes.restype = C.c_int
+        for name in ("rdp_pre_decode_jpeg", "rdp_pre_decode_png16"):
+            getattr(lib, name).argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_size_t, C.c_void_p]
+            getattr(lib, name).restype = C.c_int
         lib.rdp_unet_forward_profiled.argtypes = lib.rdp_unet_forward.argtypes + [C.POINTER(C.c_float)]
         lib.rdp_geom_curvature_profiled.argtypes = lib.rdp_geom_curvature.argtypes + [C.POINTER(C.c_float)]
         for name in ("rdp_unet_create", "rdp_unet_workspace_bytes", "rdp_unet_forward", "rdp_unet_launch_count",

@@ -15,7 +15,7 @@ from . import _lib
 
 NUM_SAMPLES = 100
 NUM_BINS = 50
-LAUNCH_NAMES = ["memset", "deproject", "xrange", "bin_hist", "bin_offsets", "scatter", "select_sort", "fit", "fit_knots"]
+LAUNCH_NAMES = ["memset", "deproject", "bin_hist", "scatter", "select_sort", "fit", "fit_knots"]
 
 
 @dataclass

@@ -3,8 +3,9 @@
     color (B,H,W,3) uint8 --rdp_pre_resize--> (B,3,S,S) f32 --UNet (mask rule fused)--> (B,S,S) u8
           --rdp_post_mask_nearest--> (B,H,W) u8 + non-zero counts --rdp_geom_curvature(depth)--> curvature, coverage
 
-Decoding the PNG/JPEG payloads and the gRPC plumbing stay with the caller (out of scope); every
-array between them and the response fields stays in HBM.  No CPU fallback.
+`decode_color_jpeg` / `decode_depth_png` take the encoded payloads of the requests themselves (`server.py:117-118`); the
+gRPC plumbing stays with the caller.  Every array between the payload bytes and the response fields stays in HBM.
+No CPU fallback.
 """
 from __future__ import annotations
 
@@ -78,6 +79,100 @@ def encode_mask_png(final_mask: torch.Tensor, *, to_host: bool = True):
     n = nbytes.cpu().numpy()
     host = png[:, :int(n.max())].cpu().numpy()
     return [host[i, :n[i]].tobytes() for i in range(B)]
+
+
+DECODE_STATUS = {1: "not an image", 2: "truncated", 3: "unsupported format", 4: "wrong size", 5: "corrupt stream",
+                 6: "length mismatch", 7: "bad filter type"}
+
+
+def jpeg_size(data) -> tuple:
+    """(H, W) from a JPEG's first SOFn segment (host side, a few hundred bytes are looked at)."""
+    d = memoryview(data)
+    i = 2
+    while i + 9 < len(d):
+        if d[i] != 0xFF:
+            break
+        m = d[i + 1]
+        if m == 0xFF:
+            i += 1
+            continue
+        if 0xC0 <= m <= 0xCF and m not in (0xC4, 0xC8, 0xCC):
+            return (d[i + 5] << 8) | d[i + 6], (d[i + 7] << 8) | d[i + 8]
+        i += 2 + ((d[i + 2] << 8) | d[i + 3])
+    raise _lib.RdpError("no frame header found in the JPEG payload")
+
+
+def png_size(data) -> tuple:
+    d = memoryview(data)
+    if len(d) < 24 or bytes(d[:8]) != b"\x89PNG\r\n\x1a\n":
+        raise _lib.RdpError("payload is not a PNG")
+    return int.from_bytes(d[20:24], "big"), int.from_bytes(d[16:20], "big")
+
+
+def _upload_payloads(payloads, device):
+    """Encoded images of a batch -> (concatenated bytes, int64 offsets) on the device, through one pinned staging copy."""
+    import numpy as np
+    sizes = [len(x) for x in payloads]
+    offs = np.zeros(len(sizes) + 1, dtype=np.int64)
+    np.cumsum(sizes, out=offs[1:])
+    host = torch.empty(int(offs[-1]) + 8, dtype=torch.uint8).pin_memory()
+    hv = host.numpy()
+    for x, o in zip(payloads, offs[:-1]):
+        hv[o:o + len(x)] = np.frombuffer(x, dtype=np.uint8)
+    return host.to(device, non_blocking=True), torch.from_numpy(offs).to(device, non_blocking=True)
+
+
+def _decode(payloads, fn_name: str, shape_of, out_shape, out_dtype, which: int, device, check: bool):
+    import ctypes as C
+    if len(payloads) == 0:
+        raise _lib.RdpError("no payloads")
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    H, W = shape_of(payloads[0])
+    B = len(payloads)
+    lib = _lib.load()
+    sizes = [C.c_size_t(), C.c_size_t()]
+    _lib.check(lib.rdp_pre_decode_sizes(B, H, W, C.byref(sizes[0]), C.byref(sizes[1])), "rdp_pre_decode_sizes")
+    with torch.cuda.device(device):
+        data, offs = _upload_payloads(payloads, device)
+        out = torch.empty((B, H, W) + out_shape, dtype=out_dtype, device=device)
+        status = torch.empty(B, dtype=torch.int32, device=device)
+        ws = torch.empty(sizes[which].value, dtype=torch.uint8, device=device)
+        _lib.check(getattr(lib, fn_name)(data.data_ptr(), offs.data_ptr(), B, H, W, out.data_ptr(), status.data_ptr(),
+                                         ws.data_ptr(), ws.numel(), torch.cuda.current_stream(device).cuda_stream), fn_name)
+        for t in (data, offs, ws):
+            t.record_stream(torch.cuda.current_stream(device))
+    if check:
+        st = status.cpu().numpy()
+        bad = [(i, DECODE_STATUS.get(int(v), str(int(v)))) for i, v in enumerate(st) if v]
+        if bad:
+            raise _lib.RdpError(f"{fn_name}: {len(bad)} of {B} payloads could not be decoded: {bad[:8]}")
+    return out, status
+
+
+def decode_color_jpeg(payloads, *, device=None, check: bool = True):
+    """JPEG payloads of a batch of requests -> ((B,H,W,3) uint8 BGR on the GPU, status (B,) int32): what
+    `cv2.imdecode(np.frombuffer(request.color_image.data, np.uint8), cv2.IMREAD_COLOR)` (`server.py:117`) returns,
+    bit for bit, for the baseline JPEGs `cv2.imencode('.jpg', ...)` writes.  All images of a batch have one size.
+    `check=True` reads the status back (one small synchronising copy) and raises on a failed image."""
+    return _decode(payloads, "rdp_pre_decode_jpeg", jpeg_size, (3,), torch.uint8, 0, device, check)
+
+
+def decode_depth_png(payloads, *, device=None, check: bool = True):
+    """16-bit greyscale PNG payloads -> ((B,H,W) uint16 on the GPU, status): `cv2.imdecode(..., cv2.IMREAD_UNCHANGED)`
+    of `server.py:118`, bit for bit."""
+    return _decode(payloads, "rdp_pre_decode_png16", png_size, (), torch.uint16, 1, device, check)
+
+
+@torch.no_grad()
+def analyze_encoded(model, color_payloads, depth_payloads, intrinsics, depth_scale, *, size: int = MODEL_IMG_SIZE):
+    """The whole loop body of the server from the request's bytes (`server.py:117-141`): both decodes, BGR->RGB, resize,
+    U-Net, mask up-size, curvature - nothing decoded ever visits the host."""
+    color, cs = decode_color_jpeg(color_payloads, check=False)
+    depth, ds = decode_depth_png(depth_payloads, device=color.device, check=False)
+    bad = torch.nonzero((cs != 0) | (ds != 0)).flatten().cpu().tolist()
+    if bad:
+        raise _lib.RdpError(f"payloads {bad[:8]} could not be decoded (JPEG status {cs.cpu().tolist()}, PNG status {ds.cpu().tolist()})")
+    return analyze_frames(model, color, depth, intrinsics, depth_scale, size=size, bgr=True)
 
 
 @dataclass

@@ -136,3 +136,33 @@ def test_two_lanes_serve_everything_and_overlap_batches():
     assert sum(log) == 46 and max(log) <= 4 and peak[0] == 2                                  # two batches in flight
     with pytest.raises(ValueError):
         MicroBatcher(run_batch=run, lanes=0)
+
+
+def test_encoded_requests_form_their_own_batches_and_keep_their_payloads():
+    """`submit_encoded` takes the request's JPEG / PNG bytes: batches are keyed by image size, never mixed with decoded
+    frames, and every caller gets the result of its own payload."""
+    cv2 = pytest.importorskip("cv2")
+    seen = []
+
+    def run(colors, depths):
+        kinds = {isinstance(c, bytes) for c in colors}
+        assert len(kinds) == 1
+        seen.append((kinds.pop(), len(colors)))
+        if isinstance(colors[0], bytes):
+            return [FrameResult(None, None, float(len(c)), len(colors)) for c in colors]
+        return [FrameResult(None, None, -1.0, len(colors)) for _ in colors]
+
+    def enc(H, W, v):
+        return (cv2.imencode(".jpg", np.full((H, W, 3), v, np.uint8))[1].tobytes(),
+                cv2.imencode(".png", np.full((H, W), v, np.uint16))[1].tobytes())
+
+    with MicroBatcher(run_batch=run, max_batch=8, max_wait_ms=30) as mb:
+        small, big = [enc(8, 8, v) for v in range(3)], [enc(16, 24, v) for v in range(2)]
+        futs = [mb.submit_encoded(*p) for p in small] + [mb.submit(*_frame(5))] + [mb.submit_encoded(*p) for p in big]
+        res = [f.result(5) for f in futs]
+        assert [r.mask_coverage for r in res[:3]] == [float(len(p[0])) for p in small]
+        assert res[3].mask_coverage == -1.0
+        assert [r.mask_coverage for r in res[4:]] == [float(len(p[0])) for p in big]
+        assert sorted(seen) == sorted([(True, 3), (False, 1), (True, 2)])
+        with pytest.raises(ValueError):
+            mb.submit_encoded(small[0][0], big[0][1])            # colour and depth of different sizes
