@@ -512,8 +512,9 @@ def run_b200(args):
     # FramePipeline = the per-GPU stream pipeline a user runs: H2D of micro-batch i+1 and D2H of i-1 overlap compute of i
     from rdp_b200.pipeline import FramePipeline
     pipe = FramePipeline(model, K, scale, B, H, W, depth_dtype=dev_depth[0].dtype, slots=args.slots, device=dev)
-    pipe.submit(host_rgb[0], host_depth[0])
-    pipe.collect()
+    for i in range(max(args.warmup, args.slots + 1)):       # every slot once: allocator blocks, tensor maps, pinned buffers
+        pipe.submit(host_rgb[i % RING], host_depth[i % RING])
+        pipe.collect()
     barrier()
     s_in, _, s_out = pipe.events()
     e0.record(s_in)

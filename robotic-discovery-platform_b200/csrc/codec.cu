@@ -71,23 +71,32 @@ struct JpegBits {
   const uint8_t* end;
   uint64_t acc;
   int n;
+  int fake;  // zero bits fed behind a marker or the end of the file; the reader looks ahead, so only CONSUMING them is an error
   __device__ __forceinline__ void fill() {
     while (n <= 56) {
       uint32_t b = 0;
+      bool real = false;
       if (p < end) {
         b = *p;
         if (b == 0xFF) {
           const uint32_t nx = (p + 1 < end) ? p[1] : 0xD9u;
-          if (nx == 0) p += 2;
-          else b = 0;  // a marker: stay on it
+          if (nx == 0) {
+            p += 2;
+            real = true;
+          } else {
+            b = 0;  // a marker: stay on it
+          }
         } else {
           ++p;
+          real = true;
         }
       }
+      if (!real) fake += 8;
       acc = (acc << 8) | b;
       n += 8;
     }
   }
+  __device__ __forceinline__ bool overrun() const { return n < fake; }
   __device__ __forceinline__ uint32_t peek(int k) { return (uint32_t)(acc >> (n - k)) & ((1u << k) - 1u); }
   __device__ __forceinline__ void skip(int k) { n -= k; }
   __device__ __forceinline__ int receive_extend(int s) {  // F.2.2.1 RECEIVE + EXTEND
@@ -99,6 +108,7 @@ struct JpegBits {
   __device__ void restart() {  // drop buffered bits, continue behind the next RSTn
     acc = 0;
     n = 0;
+    fake = 0;
     while (p + 1 < end && !(p[0] == 0xFF && p[1] >= 0xD0 && p[1] <= 0xD7)) ++p;
     p += 2;
   }
@@ -302,6 +312,7 @@ __global__ void __launch_bounds__(32) k_jpeg_blocks(const JpegParams p) {
   bits.end = d + len;
   bits.acc = 0;
   bits.n = 0;
+  bits.fake = 0;
   int pred[3] = {0, 0, 0};
   int count = 0;
   for (int my = 0; my < f.mcuy; ++my) {
@@ -344,10 +355,11 @@ __global__ void __launch_bounds__(32) k_jpeg_blocks(const JpegParams p) {
             }
           }
         }
+        if (!err && bits.overrun()) err = 2;  // the scan ended (marker or end of file) before this MCU did
         s_more = err;
       }
       __syncwarp();
-      if (s_more) JPEG_FAIL(5);
+      if (s_more) JPEG_FAIL(s_more);
       // ---- dequantisation + inverse DCT of the MCU's blocks, whole warp ----
       for (int t = lane; t < blocks_per_mcu * 8; t += 32) {  // pass 1: columns
         const int blk = t >> 3, col = t & 7;
@@ -499,19 +511,20 @@ struct InflateBits {
   PngBytes in;
   uint64_t acc;
   int n;
-  bool eof;
+  int fake;  // zero bits appended behind the end of the data (the reader looks up to 8 bytes ahead of what is consumed)
   __device__ __forceinline__ void fill() {
     while (n <= 56) {
       const int b = in.get();
       if (b < 0) {
-        eof = true;
-        n += 8;  // zeros
+        fake += 8;
+        n += 8;
       } else {
         acc |= (uint64_t)b << n;
         n += 8;
       }
     }
   }
+  __device__ __forceinline__ bool overrun() const { return n < fake; }  // bits that were never in the file were consumed
   __device__ __forceinline__ uint32_t peek(int k) { return (uint32_t)acc & ((1u << k) - 1u); }
   __device__ __forceinline__ void skip(int k) {
     acc >>= k;
@@ -605,7 +618,7 @@ __global__ void __launch_bounds__(32) k_png_inflate(const PngParams p) {
   bits.in.seg_end = 8;
   bits.acc = 0;
   bits.n = 0;
-  bits.eof = false;
+  bits.fake = 0;
   if (!bits.in.next_chunk()) return fail(2);
   {
     const uint32_t cmf = bits.get(8), flg = bits.get(8);  // RFC 1950
@@ -684,11 +697,12 @@ __global__ void __launch_bounds__(32) k_png_inflate(const PngParams p) {
           if (dist > op || op + length > want) return fail(6);
           for (int i = 0; i < length; ++i, ++op) out[op] = out[op - dist];
         }
-        if (bits.eof) return fail(5);
+        if (bits.overrun()) return fail(2);
       }
     } else {
       return fail(5);
     }
+    if (bits.overrun()) return fail(2);
     if (final) break;
   }
   if (op != want) return fail(6);
