@@ -261,6 +261,55 @@ int rdp_pre_decode_jpeg(const uint8_t* data, const int64_t* offsets, int B, int 
 int rdp_pre_decode_png16(const uint8_t* data, const int64_t* offsets, int B, int H, int W, uint16_t* depth, int32_t* status,
                          void* workspace, size_t workspace_bytes, void* stream);
 
+/* ------------------------------------------------------------------------------------------------------ */
+/* Training step: what `model(images)` in train mode and `loss.backward()` compute in the  */
+/* reference's loop (scripts/train_segmenter.py:151-165).  The loss and the optimiser stay the caller's        */
+/* (torch's BCEWithLogitsLoss and Adam there); BatchNorm running statistics are updated by the caller from the */
+/* batch statistics returned here (momentum 0.1, unbiased variance, pkg/segmentation_model.py:32,35).          */
+/* ------------------------------------------------------------------------------------------------------ */
+
+typedef struct {
+  const void* w;      /* bf16 [cout][9][cin_pad], tap = 3*ky+kx, NOT folded with BatchNorm (first layer: [cout][64], k = tap*cin + c) */
+  const void* w_t;    /* bf16 [cin_pad][9][cout]: w_t[ci][3*ky+kx][co] = W[co][ci][2-ky][2-kx], for the input gradient (NULL for layer 0) */
+  const float* gamma; /* fp32 [cout]  BatchNorm2d.weight */
+  const float* beta;  /* fp32 [cout]  BatchNorm2d.bias   */
+  int32_t cin, cout;
+} RdpTrainLayer;
+
+typedef struct {
+  int32_t n_channels, n_classes;
+  RdpTrainLayer conv[18];
+  const float* outc_weight; /* fp32 [n_classes][64] */
+  const float* outc_bias;   /* fp32 [n_classes] */
+  float bn_eps;             /* 1e-5 when 0 */
+} RdpTrainWeights;
+
+typedef struct {  /* batch statistics of every BatchNorm layer (device, fp32 [cout]; entries may be NULL) */
+  float* mean[18];
+  float* var_biased[18];
+} RdpTrainBatchStats;
+
+typedef struct {  /* parameter gradients (device, fp32), each overwritten by the call */
+  float* dw[18];      /* [cout][cin][3][3], the layout of Conv2d.weight */
+  float* dgamma[18];  /* [cout] */
+  float* dbeta[18];   /* [cout] */
+  float* d_outc_weight; /* [n_classes][64] */
+  float* d_outc_bias;   /* [n_classes] */
+} RdpTrainGrads;
+
+/* H and W must be divisible by 16 (the reference trains at 256 x 256, train_segmenter.py:49). */
+int rdp_unet_train_workspace_bytes(const RdpTrainWeights* w, int B, int H, int W, size_t* bytes);
+
+/* x_nchw: fp32 (B, n_channels, H, W) as the DataLoader yields it; logits: fp32 (B, n_classes, H, W).  Keeps every
+ * activation the backward pass needs in `workspace`. */
+int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_nchw, int B, int H, int W, float* logits,
+                           const RdpTrainBatchStats* stats, void* workspace, size_t workspace_bytes, void* stream);
+
+/* dlogits: fp32 (B, n_classes, H, W), the gradient of the loss with respect to the logits.  Must follow an
+ * rdp_unet_train_forward with the same weights, shape and workspace. */
+int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dlogits, int B, int H, int W, const RdpTrainGrads* grads,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

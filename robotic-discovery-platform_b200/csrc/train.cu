@@ -1,0 +1,810 @@
+// One training step of the U-Net on sm_100a: the forward pass in training mode and the backward pass
+// that `loss.backward()` runs in the reference's loop (scripts/train_segmenter.py:151-165; `model.train()`, so every
+// BatchNorm2d normalises with the statistics of the batch, pkg/segmentation_model.py:31-36).  The loss
+// (BCEWithLogitsLoss) and the optimiser (Adam) stay torch's, exactly as in that loop: this file provides what sits
+// between `model(images)` and the parameters' `.grad`.
+//
+// Data: activations NHWC bf16 as in the inference path, gradients of activations bf16, parameter gradients fp32,
+// batch statistics accumulated in fp64.  Per 3x3 conv + BatchNorm + ReLU stage i, forward
+//     Z_i = conv(X_i, W_i)            k_conv3x3<BN, RAW> (tcgen05 implicit GEMM, csrc/unet.cu)
+//     mu, var = stats(Z_i)            k_bn_stats      per-channel sum and sum of squares over B*H*W
+//     Y_i = relu(g (Z_i - mu)/sqrt(var + eps) + b)     k_bn_relu
+// and backward, given dY_i,
+//     dbeta, dgamma                   k_bn_bwd_reduce (dY masked by Y > 0)
+//     dZ_i = g/sigma (dY~ - dbeta/n - xhat dgamma/n)   k_bn_bwd_apply
+//     dW_i = sum_p dZ_i[p] (x) X_i[p + tap]            k_wgrad: tcgen05 GEMM with K = the pixels (both operands transposed to
+//                                                      pixel-major by k_transpose so that K is contiguous for TMA / UMMA)
+//     dX_i = conv(dZ_i, W_i flipped and transposed)    k_conv3x3<BN, RAW> again
+// plus the adjoints of MaxPool2d(2) (first maximum wins, like ATen), of the bilinear x2 up-sampling with its pad, of the
+// channel concatenation, and the 1x1 OutConv in both directions.
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdarg.h>
+
+#include <algorithm>
+
+#include "rdp_common.cuh"
+#include "sm100_ptx.cuh"
+#include "unet_internal.cuh"
+
+namespace rdp {
+namespace train {
+
+using namespace ptx;
+
+// ---------------------------------------------------------------------------------------------------------
+// small helpers on 8 bf16 (16 bytes)
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 v;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// BatchNorm (training mode) forward
+// ---------------------------------------------------------------------------------------------------------
+// sums[c] += sum_p z[p][c], sums[C + c] += sum_p z[p][c]^2 (fp64 atomics; z is bf16 [P][C], C a multiple of 8 and
+// a divisor of 2048).  A thread owns 8 channels and walks rows; partial sums go through shared memory once per block.
+constexpr int ST_THREADS = 256;
+__global__ void __launch_bounds__(ST_THREADS) k_bn_stats(const __nv_bfloat16* __restrict__ z, size_t P, int C, double* sums) {
+  extern __shared__ double s_acc[];  // [2][C]
+  const int c8 = C / 8, tid = threadIdx.x;
+  const int lanes = ST_THREADS / c8 > 0 ? ST_THREADS / c8 : 1;  // rows handled side by side
+  for (int i = tid; i < 2 * C; i += ST_THREADS) s_acc[i] = 0.0;
+  __syncthreads();
+  if (tid < lanes * c8) {
+    const int cg = tid % c8, rl = tid / c8;
+    double a[8], q[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = q[k] = 0.0;
+    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += (size_t)gridDim.x * lanes) {
+      float f[8];
+      unpack8(*reinterpret_cast<const uint4*>(z + r * C + cg * 8), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        a[k] += (double)f[k];
+        q[k] += (double)f[k] * (double)f[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      atomicAdd(&s_acc[cg * 8 + k], a[k]);
+      atomicAdd(&s_acc[C + cg * 8 + k], q[k]);
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < 2 * C; i += ST_THREADS) atomicAdd(&sums[i], s_acc[i]);
+}
+
+// mean, biased variance, and the affine form of the normalisation: y = z * scale + shift
+__global__ void k_bn_finalize(const double* sums, int C, double n, const float* gamma, const float* beta, float eps, float* mean,
+                              float* var, float* invstd, float* scale, float* shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const double m = sums[c] / n;
+  double v = sums[C + c] / n - m * m;
+  v = v > 0.0 ? v : 0.0;
+  const double is = 1.0 / sqrt(v + (double)eps);
+  mean[c] = (float)m;
+  var[c] = (float)v;
+  invstd[c] = (float)is;
+  scale[c] = (float)((double)gamma[c] * is);
+  shift[c] = (float)((double)beta[c] - m * (double)gamma[c] * is);
+}
+
+__global__ void __launch_bounds__(256) k_bn_relu(const __nv_bfloat16* __restrict__ z, size_t n8, int c8, const float* __restrict__ scale,
+                                                 const float* __restrict__ shift, __nv_bfloat16* __restrict__ y) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    float f[8];
+    unpack8(reinterpret_cast<const uint4*>(z)[i], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = fmaxf(fmaf(f[k], scale[cg * 8 + k], shift[cg * 8 + k]), 0.f);
+    reinterpret_cast<uint4*>(y)[i] = pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// OutConv (1x1, 64 -> n_classes, bias), both directions
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_outconv_fwd(const __nv_bfloat16* __restrict__ y, size_t P, size_t HW, int ncls,
+                                                     const float* __restrict__ w, const float* __restrict__ bias, float* __restrict__ logits) {
+  const size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  float x[64];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float f[8];
+    unpack8(reinterpret_cast<const uint4*>(y + p * 64)[j], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x[8 * j + k] = f[k];
+  }
+  const size_t n = p / HW, off = p % HW;
+  for (int cls = 0; cls < ncls; ++cls) {
+    float a = 0.f;
+#pragma unroll
+    for (int c = 0; c < 64; ++c) a = fmaf(x[c], w[cls * 64 + c], a);
+    logits[(n * ncls + cls) * HW + off] = a + bias[cls];
+  }
+}
+
+// dY[p][c] = sum_cls dlogit[cls][p] w[cls][c];  dW[cls][c] += sum_p dlogit y;  db[cls] += sum_p dlogit
+__global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ dlogits, const __nv_bfloat16* __restrict__ y, size_t P,
+                                                     size_t HW, int ncls, const float* __restrict__ w, __nv_bfloat16* __restrict__ dy,
+                                                     float* dw, float* db) {
+  __shared__ float s_dw[8 * 64 + 8];
+  for (int i = threadIdx.x; i < 8 * 64 + 8; i += blockDim.x) s_dw[i] = 0.f;
+  __syncthreads();
+  const size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (p < P) {
+    const size_t n = p / HW, off = p % HW;
+    float g[8];
+    for (int cls = 0; cls < ncls; ++cls) g[cls] = dlogits[(n * ncls + cls) * HW + off];
+#pragma unroll 1
+    for (int j = 0; j < 8; ++j) {
+      float f[8], o[8];
+      unpack8(reinterpret_cast<const uint4*>(y + p * 64)[j], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+      for (int cls = 0; cls < ncls; ++cls) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          o[k] = fmaf(g[cls], w[cls * 64 + 8 * j + k], o[k]);
+          atomicAdd(&s_dw[cls * 64 + 8 * j + k], g[cls] * f[k]);
+        }
+      }
+      reinterpret_cast<uint4*>(dy + p * 64)[j] = pack8(o);
+    }
+    for (int cls = 0; cls < ncls; ++cls) atomicAdd(&s_dw[8 * 64 + cls], g[cls]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < ncls * 64; i += blockDim.x) atomicAdd(&dw[i], s_dw[i]);
+  if (threadIdx.x < ncls) atomicAdd(&db[threadIdx.x], s_dw[8 * 64 + threadIdx.x]);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// BatchNorm + ReLU backward
+// ---------------------------------------------------------------------------------------------------------
+// sums[c] += sum_p dY~, sums[C + c] += sum_p dY~ xhat,  dY~ = dY [Y > 0],  xhat = (Z - mean) invstd
+__global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                                                              const __nv_bfloat16* __restrict__ z, size_t P, int C,
+                                                              const float* __restrict__ mean, const float* __restrict__ invstd, double* sums) {
+  extern __shared__ double s_acc[];
+  const int c8 = C / 8, tid = threadIdx.x;
+  const int lanes = ST_THREADS / c8 > 0 ? ST_THREADS / c8 : 1;
+  for (int i = tid; i < 2 * C; i += ST_THREADS) s_acc[i] = 0.0;
+  __syncthreads();
+  if (tid < lanes * c8) {
+    const int cg = tid % c8, rl = tid / c8;
+    double a[8], q[8];
+    float mu[8], is[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      a[k] = q[k] = 0.0;
+      mu[k] = mean[cg * 8 + k];
+      is[k] = invstd[cg * 8 + k];
+    }
+    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += (size_t)gridDim.x * lanes) {
+      float g[8], yy[8], zz[8];
+      unpack8(*reinterpret_cast<const uint4*>(dy + r * C + cg * 8), g);
+      unpack8(*reinterpret_cast<const uint4*>(y + r * C + cg * 8), yy);
+      unpack8(*reinterpret_cast<const uint4*>(z + r * C + cg * 8), zz);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gm = yy[k] > 0.f ? g[k] : 0.f;
+        a[k] += (double)gm;
+        q[k] += (double)gm * (double)((zz[k] - mu[k]) * is[k]);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      atomicAdd(&s_acc[cg * 8 + k], a[k]);
+      atomicAdd(&s_acc[C + cg * 8 + k], q[k]);
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < 2 * C; i += ST_THREADS) atomicAdd(&sums[i], s_acc[i]);
+}
+
+// dbeta, dgamma out (fp32) and the two per-channel terms of dZ
+__global__ void k_bn_bwd_finalize(const double* sums, int C, double n, const float* gamma, const float* invstd, float* dgamma,
+                                  float* dbeta, float* k_scale, float* k_mean_db, float* k_mean_dg) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  dbeta[c] = (float)sums[c];
+  dgamma[c] = (float)sums[C + c];
+  k_scale[c] = gamma[c] * invstd[c];
+  k_mean_db[c] = (float)(sums[c] / n);
+  k_mean_dg[c] = (float)(sums[C + c] / n);
+}
+
+__global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                                                      const __nv_bfloat16* __restrict__ z, size_t n8, int c8, const float* __restrict__ mean,
+                                                      const float* __restrict__ invstd, const float* __restrict__ k_scale,
+                                                      const float* __restrict__ k_mean_db, const float* __restrict__ k_mean_dg,
+                                                      __nv_bfloat16* __restrict__ dz) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % c8);
+    float g[8], yy[8], zz[8], o[8];
+    unpack8(reinterpret_cast<const uint4*>(dy)[i], g);
+    unpack8(reinterpret_cast<const uint4*>(y)[i], yy);
+    unpack8(reinterpret_cast<const uint4*>(z)[i], zz);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = cg * 8 + k;
+      const float gm = yy[k] > 0.f ? g[k] : 0.f;
+      const float xh = (zz[k] - mean[c]) * invstd[c];
+      o[k] = k_scale[c] * (gm - k_mean_db[c] - xh * k_mean_dg[c]);
+    }
+    reinterpret_cast<uint4*>(dz)[i] = pack8(o);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// adjoints of the shape-changing ops
+// ---------------------------------------------------------------------------------------------------------
+// MaxPool2d(2) backward: the gradient of a pooled pixel goes to the first maximum of its window in row-major order
+// (ATen's max_pool2d keeps the first index where `val > max`); rows / columns beyond the last full window get none.
+// `accumulate`: add to what dst already holds (the skip connection's other consumer wrote it before).
+__global__ void __launch_bounds__(256) k_maxpool_bwd(const __nv_bfloat16* __restrict__ src_y, const __nv_bfloat16* __restrict__ dpool, int B,
+                                                     int H, int W, int C8, int accumulate, __nv_bfloat16* __restrict__ dst) {
+  const size_t total = (size_t)B * H * W * C8;
+  const int Ho = H / 2, Wo = W / 2;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % C8);
+    size_t r = i / C8;
+    const int x = (int)(r % W);
+    r /= W;
+    const int y = (int)(r % H), n = (int)(r / H);
+    float o[8];
+    if (accumulate) unpack8(reinterpret_cast<const uint4*>(dst)[i], o);
+    else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+    }
+    const int yo = y >> 1, xo = x >> 1;
+    if (yo < Ho && xo < Wo) {
+      float w4[4][8], g[8];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        unpack8(reinterpret_cast<const uint4*>(src_y)[(((size_t)n * H + 2 * yo + (q >> 1)) * W + 2 * xo + (q & 1)) * C8 + cg], w4[q]);
+      unpack8(reinterpret_cast<const uint4*>(dpool)[(((size_t)n * Ho + yo) * Wo + xo) * C8 + cg], g);
+      const int me = ((y & 1) << 1) | (x & 1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        int best = 0;
+        float m = w4[0][k];
+#pragma unroll
+        for (int q = 1; q < 4; ++q)
+          if (w4[q][k] > m) {
+            m = w4[q][k];
+            best = q;
+          }
+        if (best == me) o[k] += g[k];
+      }
+    }
+    reinterpret_cast<uint4*>(dst)[i] = pack8(o);
+  }
+}
+
+// Adjoint of `Upsample(x2, bilinear, align_corners=True)` + the zero pad of Up.forward, as a gather: a low-resolution
+// pixel collects, with the forward pass's own weights (same fp32 expressions as k_upsample2x), every output pixel that
+// read it.  src = gradient of the padded, up-sampled tensor: channels [c_off, c_off + 8*C8) of rows of `src_c` channels.
+__global__ void __launch_bounds__(256) k_upsample_bwd(const __nv_bfloat16* __restrict__ src, int src_c, int c_off, int B, int h, int w,
+                                                      int C8, int Hs, int Ws, int py, int px, __nv_bfloat16* __restrict__ dst) {
+  const size_t total = (size_t)B * h * w * C8;
+  const int Ho = 2 * h, Wo = 2 * w;
+  const float ry = Ho > 1 ? (float)(h - 1) / (float)(Ho - 1) : 0.f, rx = Wo > 1 ? (float)(w - 1) / (float)(Wo - 1) : 0.f;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % C8);
+    size_t r = i / C8;
+    const int xl = (int)(r % w);
+    r /= w;
+    const int yl = (int)(r % h), n = (int)(r / h);
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    // output rows whose source interval touches yl: fy = ry * yo in (yl - 1, yl + 1); scan a safe window and test exactly
+    const int y_lo = max(0, 2 * yl - 3), y_hi = min(Ho - 1, 2 * yl + 4);
+    const int x_lo = max(0, 2 * xl - 3), x_hi = min(Wo - 1, 2 * xl + 4);
+    for (int yo = y_lo; yo <= y_hi; ++yo) {
+      const float fy = ry * (float)yo;
+      const int y0 = (int)fy, y1 = y0 + (y0 < h - 1 ? 1 : 0);
+      const float ly1 = fy - (float)y0, ly0 = 1.f - ly1;
+      const float wy = (y0 == yl ? ly0 : 0.f) + (y1 == yl ? ly1 : 0.f);
+      if (wy == 0.f) continue;
+      const int ys = yo + py;
+      if (ys < 0 || ys >= Hs) continue;
+      for (int xo = x_lo; xo <= x_hi; ++xo) {
+        const float fx = rx * (float)xo;
+        const int x0 = (int)fx, x1 = x0 + (x0 < w - 1 ? 1 : 0);
+        const float lx1 = fx - (float)x0, lx0 = 1.f - lx1;
+        const float wx = (x0 == xl ? lx0 : 0.f) + (x1 == xl ? lx1 : 0.f);
+        if (wx == 0.f) continue;
+        const int xs = xo + px;
+        if (xs < 0 || xs >= Ws) continue;
+        float g[8];
+        unpack8(*reinterpret_cast<const uint4*>(src + (((size_t)n * Hs + ys) * Ws + xs) * src_c + c_off + cg * 8), g);
+        const float wgt = wy * wx;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, g[k], acc[k]);
+      }
+    }
+    reinterpret_cast<uint4*>(dst)[i] = pack8(acc);
+  }
+}
+
+// dst[p][0..C) (+)= src[p][c_off .. c_off + C): the skip half of a concatenated gradient
+__global__ void __launch_bounds__(256) k_slice_channels(const __nv_bfloat16* __restrict__ src, int src_c8, int off8, size_t P, int C8,
+                                                        __nv_bfloat16* __restrict__ dst) {
+  const size_t total = P * C8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t p = i / C8;
+    const int cg = (int)(i % C8);
+    reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[p * src_c8 + off8 + cg];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// weight gradient: tcgen05 GEMM with K = pixels
+// ---------------------------------------------------------------------------------------------------------
+// [B][H][W][C] (NHWC) -> [C][B][H][Wp] (channel-major, a row of pixels contiguous, rows padded to Wp = W rounded up to 8 so
+// that every TMA stride is a multiple of 16 bytes) at channel offset c_off: both wgrad operands need the contraction
+// index (the pixel) as the contiguous one.  Pad columns are never read: the tensor map's width is W, so x >= W is
+// out of bounds and zero-filled, exactly like the convolution's own padding.
+__global__ void __launch_bounds__(256) k_transpose(const __nv_bfloat16* __restrict__ src, int rows /*B*H*/, int W, int Wp, int C,
+                                                   __nv_bfloat16* __restrict__ dst, int c_off) {
+  __shared__ __nv_bfloat16 tile[64][64 + 2];
+  const int row = blockIdx.x, x0 = blockIdx.z * 64, c0 = blockIdx.y * 64;
+  for (int i = threadIdx.x; i < 64 * 64; i += 256) {
+    const int r = i >> 6, c = i & 63;
+    tile[r][c] = (x0 + r < W) ? src[((size_t)row * W + x0 + r) * C + c0 + c] : __float2bfloat16(0.f);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 64 * 64; i += 256) {
+    const int c = i >> 6, r = i & 63;
+    if (x0 + r < W) dst[((size_t)(c_off + c0 + c) * rows + row) * Wp + x0 + r] = tile[r][c];
+  }
+}
+
+constexpr int WG_STAGES = 4;
+constexpr int WG_THREADS = 192;  // warp 0: TMA, warp 1: MMA, warps 2-5: epilogue
+struct WgradParams {
+  int B, H, W;
+  int cout, cin_real, cin_pad;  // cin_pad: channels of the transposed input (multiple of 64)
+  int n_tile;                   // columns (input channels) per work item: 64, 128 or 256
+  int m_tiles, n_tiles, taps, ksplit, wsteps;
+  int first_layer;              // the input is the im2col'ed image: column k = tap * cin_real + c  ->  dW[co][c][tap]
+  float* dw;                    // fp32 [cout][cin_real][3][3]
+};
+
+// D[128 output channels x n_tile input channels] += dZ^T[128 x 64 pixels] * X^T(shifted by the tap)[n_tile x 64 pixels]^T over
+// this CTA's share of the pixels; the partial result is added to dW with fp32 atomics (split-K).
+template <int NT>
+__global__ void __launch_bounds__(WG_THREADS, 1)
+k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUtensorMap map_x, const WgradParams p) {
+  constexpr int A_BYTES = 128 * 128, B_BYTES = NT * 128, STAGE = A_BYTES + B_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_STAGES * STAGE);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + WG_STAGES;
+  uint64_t* done = bars + 2 * WG_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  int item = blockIdx.x;
+  const int ks = item % p.ksplit; item /= p.ksplit;
+  const int tap = item % p.taps; item /= p.taps;
+  const int nt = item % p.n_tiles;
+  const int mt = item / p.n_tiles;
+  const int dy = p.taps == 9 ? tap / 3 - 1 : 0, dx = p.taps == 9 ? tap % 3 - 1 : 0;
+  const long long total_steps = (long long)p.B * p.H * p.wsteps;
+  const long long s0 = total_steps * ks / p.ksplit, s1 = total_steps * (ks + 1) / p.ksplit;
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_dz);
+    prefetch_tensormap(&map_x);
+    for (int s = 0; s < WG_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, NT < 32 ? 32 : NT);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (long long s = s0; s < s1; ++s) {
+        const int xs = (int)(s % p.wsteps) * 64;
+        long long r = s / p.wsteps;
+        const int y = (int)(r % p.H), n = (int)(r / p.H);
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full[stage], STAGE);
+        tma_load_4d(smem + stage * STAGE, &map_dz, xs, y, n, mt * 128, &full[stage]);
+        tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs + dx, y + dy, n, nt * NT, &full[stage]);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, NT);
+      uint32_t stage = 0, phase = 0;
+      for (long long s = s0; s < s1; ++s) {
+        mbar_wait(&full[stage], phase);
+        tc_fence_after();
+        const uint64_t da = make_sw128_desc(smem_u32(smem + stage * STAGE));
+        const uint64_t db = make_sw128_desc(smem_u32(smem + stage * STAGE + A_BYTES));
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc, (s != s0) || k != 0);
+        tc_commit(&empty[stage]);
+        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+      }
+      tc_commit(done);
+    }
+  } else if (s1 > s0) {
+    const int quarter = warp & 3;
+    const int co = mt * 128 + quarter * 32 + lane;
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+    for (int c = 0; c < NT / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(taddr + c * 32, r);
+      tmem_ld_wait();
+      if (co < p.cout) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int ci = nt * NT + c * 32 + j;
+          const float v = __uint_as_float(r[j]);
+          if (p.first_layer) {
+            if (ci < 9 * p.cin_real) atomicAdd(&p.dw[((size_t)co * p.cin_real + ci % p.cin_real) * 9 + ci / p.cin_real], v);
+          } else if (ci < p.cin_real) {
+            atomicAdd(&p.dw[((size_t)co * p.cin_real + ci) * 9 + tap], v);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, NT < 32 ? 32 : NT);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+// map over a channel-major tensor [C][B][H][Wp]: dims (W, H, B, C), box (64 pixels of a row, 1, 1, rows channels)
+static int make_cm_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int Wp, int C, int rows) {
+  EncodeTiledFn fn = encode_fn();
+  RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  cuuint64_t dims[4] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B, (cuuint64_t)C};
+  cuuint64_t strides[3] = {(cuuint64_t)Wp * 2, (cuuint64_t)H * Wp * 2, (cuuint64_t)B * H * Wp * 2};
+  cuuint32_t box[4] = {64, 1, 1, (cuuint32_t)rows};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(channel-major %dx%dx%dx%d) failed: %d", C, B, H, W, (int)r);
+  return RDP_OK;
+}
+
+template <int NT>
+static int launch_wgrad_t(const CUtensorMap& mz, const CUtensorMap& mx, const WgradParams& p, cudaStream_t stream) {
+  constexpr int SMEM = WG_STAGES * (128 * 128 + NT * 128) + 1024 + 256;
+  static bool set[64] = {};
+  int dev = 0;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 64 && !set[dev]) {
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_wgrad<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    set[dev] = true;
+  }
+  k_wgrad<NT><<<p.m_tiles * p.n_tiles * p.taps * p.ksplit, WG_THREADS, SMEM, stream>>>(mz, mx, p);
+  return RDP_OK;
+}
+
+}  // namespace train
+}  // namespace rdp
+
+using namespace rdp;
+using namespace rdp::train;
+
+namespace {
+
+const int kLevel[18] = {0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
+
+struct Shape { int H, W; };
+
+// Everything one forward/backward pair keeps in the workspace.
+struct TrainBuffers {
+  Shape lv[5];
+  __nv_bfloat16* col;        // im2col of the input (64 channels)
+  __nv_bfloat16* z[18];      // conv outputs before BatchNorm
+  __nv_bfloat16* y[18];      // after BatchNorm + ReLU
+  __nv_bfloat16* pool[4];    // pooled x1..x4
+  __nv_bfloat16* up[4];      // up-sampled + padded low branch of up1..up4
+  float* zero_shift;         // 1024 zeros
+  float *mean[18], *var[18], *invstd[18], *scale[18], *shift[18];
+  double* sums;              // [2 * 1024]
+  // backward scratch
+  __nv_bfloat16* dy[18];     // gradient wrt y[i]
+  __nv_bfloat16* dz;         // gradient wrt the current layer's z (largest layer)
+  __nv_bfloat16* dx;         // gradient wrt the current layer's (concatenated) input
+  __nv_bfloat16* dpool;      // gradient wrt a pooled tensor (alias of dx is not possible: both live)
+  __nv_bfloat16* xt;         // transposed input of the current layer
+  __nv_bfloat16* dzt;        // transposed dz
+  float *kscale, *kdb, *kdg;  // [1024] each
+  size_t bytes;
+};
+
+TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W) {
+  TrainBuffers b{};
+  b.lv[0] = {H, W};
+  for (int i = 1; i < 5; ++i) b.lv[i] = {b.lv[i - 1].H / 2, b.lv[i - 1].W / 2};
+  Carver c(ws);
+  auto px = [&](int l) { return (size_t)B * b.lv[l].H * b.lv[l].W; };
+  auto px_padded = [&](int l) { return (size_t)B * b.lv[l].H * ((b.lv[l].W + 7) / 8 * 8); };
+  b.col = c.take<__nv_bfloat16>(px(0) * 64);
+  size_t max_act = 0, max_in = 0, max_act_t = 0, max_in_t = 0;
+  for (int i = 0; i < 18; ++i) {
+    const size_t n = px(kLevel[i]) * w->conv[i].cout;
+    b.z[i] = c.take<__nv_bfloat16>(n);
+    b.y[i] = c.take<__nv_bfloat16>(n);
+    b.dy[i] = c.take<__nv_bfloat16>(n);
+    max_act = std::max(max_act, n);
+    const int cin_pad = i == 0 ? 64 : (w->conv[i].cin + 63) / 64 * 64;
+    max_in = std::max(max_in, px(kLevel[i]) * cin_pad);
+    max_act_t = std::max(max_act_t, px_padded(kLevel[i]) * w->conv[i].cout);
+    max_in_t = std::max(max_in_t, px_padded(kLevel[i]) * cin_pad);
+    b.mean[i] = c.take<float>(w->conv[i].cout);
+    b.var[i] = c.take<float>(w->conv[i].cout);
+    b.invstd[i] = c.take<float>(w->conv[i].cout);
+    b.scale[i] = c.take<float>(w->conv[i].cout);
+    b.shift[i] = c.take<float>(w->conv[i].cout);
+  }
+  for (int i = 0; i < 4; ++i) b.pool[i] = c.take<__nv_bfloat16>(px(i + 1) * w->conv[2 * i + 1].cout);
+  for (int j = 0; j < 4; ++j) b.up[j] = c.take<__nv_bfloat16>(px(3 - j) * w->conv[9 + 2 * j].cout);
+  b.zero_shift = c.take<float>(1024);
+  b.sums = c.take<double>(2048);
+  b.dz = c.take<__nv_bfloat16>(max_act);
+  b.dx = c.take<__nv_bfloat16>(max_in);
+  b.dpool = c.take<__nv_bfloat16>(max_act);
+  b.xt = c.take<__nv_bfloat16>(max_in_t);
+  b.dzt = c.take<__nv_bfloat16>(max_act_t);
+  b.kscale = c.take<float>(1024);
+  b.kdb = c.take<float>(1024);
+  b.kdg = c.take<float>(1024);
+  b.bytes = c.total();
+  return b;
+}
+
+int ew_grid(size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)148 * 16); }
+
+int check_train_args(const RdpTrainWeights* w, int B, int H, int W, const char* who) {
+  RDP_REQUIRE(w, RDP_ERR_BAD_ARGUMENT, "%s: null weights", who);
+  RDP_REQUIRE(B > 0 && H >= 16 && W >= 16 && H % 16 == 0 && W % 16 == 0, RDP_ERR_UNSUPPORTED,
+              "%s: training needs H and W divisible by 16 (got %dx%dx%d; the reference trains at 256x256)", who, B, H, W);
+  RDP_REQUIRE(w->n_channels >= 1 && 9 * w->n_channels <= 64 && w->n_classes >= 1 && w->n_classes <= 8, RDP_ERR_UNSUPPORTED,
+              "%s: n_channels %d / n_classes %d unsupported", who, w->n_channels, w->n_classes);
+  static const int cin[18] = {0, 64, 64, 128, 128, 256, 256, 512, 512, 512, 1024, 512, 512, 256, 256, 128, 128, 64};
+  static const int cout[18] = {64, 64, 128, 128, 256, 256, 512, 512, 512, 512, 512, 256, 256, 128, 128, 64, 64, 64};
+  for (int i = 0; i < 18; ++i) {
+    const RdpTrainLayer& L = w->conv[i];
+    RDP_REQUIRE(L.w && L.gamma && L.beta && (i == 0 || L.w_t) && L.cout == cout[i] && L.cin == (i == 0 ? w->n_channels : cin[i]),
+                RDP_ERR_BAD_ARGUMENT, "%s: layer %d is incomplete or has the wrong shape", who, i);
+  }
+  RDP_REQUIRE(w->outc_weight && w->outc_bias, RDP_ERR_BAD_ARGUMENT, "%s: missing OutConv parameters", who);
+  return RDP_OK;
+}
+
+}  // namespace
+
+extern "C" int rdp_unet_train_workspace_bytes(const RdpTrainWeights* w, int B, int H, int W, size_t* bytes) {
+  RDP_REQUIRE(bytes, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_workspace_bytes: null argument");
+  const int rc = check_train_args(w, B, H, W, "rdp_unet_train_workspace_bytes");
+  if (rc != RDP_OK) return rc;
+  *bytes = carve_train(w, nullptr, B, H, W).bytes;
+  return RDP_OK;
+}
+
+extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_nchw, int B, int H, int W, float* logits,
+                                      const RdpTrainBatchStats* stats, void* workspace, size_t workspace_bytes, void* stream_) {
+  int rc = check_train_args(w, B, H, W, "rdp_unet_train_forward");
+  if (rc != RDP_OK) return rc;
+  RDP_REQUIRE(x_nchw && logits && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_forward: null pointer");
+  RDP_REQUIRE(((uintptr_t)workspace & 255) == 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_forward: workspace must be 256-byte aligned");
+  const TrainBuffers buf = carve_train(w, workspace, B, H, W);
+  RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_train_forward: workspace %zu < required %zu bytes",
+              workspace_bytes, buf.bytes);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int dev = 0, num_sms = 148;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  RDP_CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  RDP_CUDA_TRY(cudaMemsetAsync(buf.zero_shift, 0, 1024 * sizeof(float), stream));
+  const float eps = w->bn_eps > 0.f ? w->bn_eps : 1e-5f;
+
+  // conv -> batch statistics -> normalise + ReLU, for stage i with input (src0[c0] ++ src1[c1]) at level `lvl`
+  auto stage = [&](int i, const __nv_bfloat16* src0, int c0, const __nv_bfloat16* src1, int c1, int taps) -> int {
+    const Shape L = buf.lv[kLevel[i]];
+    const int C = w->conv[i].cout;
+    const size_t P = (size_t)B * L.H * L.W;
+    int r = unet::raw_conv(src0, c0, src1, c1, w->conv[i].w, C, taps, B, L.H, L.W, buf.zero_shift, buf.z[i], num_sms, stream);
+    if (r != RDP_OK) return r;
+    RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
+    const int lanes = std::max(1, ST_THREADS / (C / 8));
+    const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
+    k_bn_stats<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.z[i], P, C, buf.sums);
+    k_bn_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, w->conv[i].beta, eps, buf.mean[i], buf.var[i],
+                                                       buf.invstd[i], buf.scale[i], buf.shift[i]);
+    k_bn_relu<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.z[i], P * C / 8, C / 8, buf.scale[i], buf.shift[i], buf.y[i]);
+    if (stats && stats->mean[i]) RDP_CUDA_TRY(cudaMemcpyAsync(stats->mean[i], buf.mean[i], C * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    if (stats && stats->var_biased[i]) RDP_CUDA_TRY(cudaMemcpyAsync(stats->var_biased[i], buf.var[i], C * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+    return RDP_OK;
+  };
+#define RDP_TRY(expr)              \
+  do {                             \
+    const int _rc = (expr);        \
+    if (_rc != RDP_OK) return _rc; \
+  } while (0)
+  RDP_TRY(unet::im2col_first(x_nchw, RDP_IN_F32_NCHW, B, H, W, w->n_channels, buf.col, stream));
+  RDP_TRY(stage(0, buf.col, 64, nullptr, 0, 1));
+  RDP_TRY(stage(1, buf.y[0], 64, nullptr, 0, 9));
+  for (int d = 0; d < 4; ++d) {
+    const Shape L = buf.lv[d];
+    const int C = w->conv[2 * d + 1].cout;
+    RDP_TRY(unet::maxpool2(buf.y[2 * d + 1], B, L.H, L.W, C, buf.pool[d], stream));
+    RDP_TRY(stage(2 * d + 2, buf.pool[d], C, nullptr, 0, 9));
+    RDP_TRY(stage(2 * d + 3, buf.y[2 * d + 2], w->conv[2 * d + 2].cout, nullptr, 0, 9));
+  }
+  for (int j = 0; j < 4; ++j) {
+    const int low_i = 9 + 2 * j, skip_i = 7 - 2 * j;
+    const Shape Ls = buf.lv[3 - j], Ll = buf.lv[4 - j];
+    const int Cl = w->conv[low_i].cout, Cs = w->conv[skip_i].cout;
+    RDP_TRY(unet::upsample2x(buf.y[low_i], B, Ll.H, Ll.W, Cl, Ls.H, Ls.W, buf.up[j], stream));
+    RDP_TRY(stage(10 + 2 * j, buf.y[skip_i], Cs, buf.up[j], Cl, 9));
+    RDP_TRY(stage(11 + 2 * j, buf.y[10 + 2 * j], w->conv[10 + 2 * j].cout, nullptr, 0, 9));
+  }
+  const size_t P0 = (size_t)B * H * W;
+  k_outconv_fwd<<<(int)((P0 + 255) / 256), 256, 0, stream>>>(buf.y[17], P0, (size_t)H * W, w->n_classes, w->outc_weight, w->outc_bias, logits);
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
+
+extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dlogits, int B, int H, int W, const RdpTrainGrads* g,
+                                       void* workspace, size_t workspace_bytes, void* stream_) {
+  int rc = check_train_args(w, B, H, W, "rdp_unet_train_backward");
+  if (rc != RDP_OK) return rc;
+  RDP_REQUIRE(dlogits && g && workspace, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_backward: null pointer");
+  const TrainBuffers buf = carve_train(w, workspace, B, H, W);
+  RDP_REQUIRE(workspace_bytes >= buf.bytes, RDP_ERR_WORKSPACE_TOO_SMALL, "rdp_unet_train_backward: workspace %zu < required %zu bytes",
+              workspace_bytes, buf.bytes);
+  for (int i = 0; i < 18; ++i)
+    RDP_REQUIRE(g->dw[i] && g->dgamma[i] && g->dbeta[i], RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_backward: missing gradient buffer of layer %d", i);
+  RDP_REQUIRE(g->d_outc_weight && g->d_outc_bias, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_backward: missing OutConv gradient buffers");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int dev = 0, num_sms = 148;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  RDP_CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+
+  const size_t P0 = (size_t)B * H * W;
+  RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_weight, 0, (size_t)w->n_classes * 64 * sizeof(float), stream));
+  RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_bias, 0, (size_t)w->n_classes * sizeof(float), stream));
+  k_outconv_bwd<<<(int)((P0 + 255) / 256), 256, 0, stream>>>(dlogits, buf.y[17], P0, (size_t)H * W, w->n_classes, w->outc_weight, buf.dy[17],
+                                                             g->d_outc_weight, g->d_outc_bias);
+
+  // the input of stage i as (src0[c0] ++ src1[c1]); what the gradient of that input feeds
+  auto input_of = [&](int i, const __nv_bfloat16*& s0, int& c0, const __nv_bfloat16*& s1, int& c1) {
+    s1 = nullptr;
+    c1 = 0;
+    if (i == 0) { s0 = buf.col; c0 = 64; }
+    else if (i >= 10 && i % 2 == 0) {
+      const int j = (i - 10) / 2;
+      s0 = buf.y[7 - 2 * j]; c0 = w->conv[7 - 2 * j].cout;
+      s1 = buf.up[j]; c1 = w->conv[9 + 2 * j].cout;
+    } else if (i >= 2 && i <= 8 && i % 2 == 0) { s0 = buf.pool[i / 2 - 1]; c0 = w->conv[i - 1].cout; }
+    else { s0 = buf.y[i - 1]; c0 = w->conv[i - 1].cout; }
+  };
+
+  for (int i = 17; i >= 0; --i) {
+    const Shape L = buf.lv[kLevel[i]];
+    const int C = w->conv[i].cout;
+    const size_t P = (size_t)B * L.H * L.W;
+    // ---- BatchNorm + ReLU backward: dgamma, dbeta, dz ----
+    RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
+    const int lanes = std::max(1, ST_THREADS / (C / 8));
+    const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
+    k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.y[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.sums);
+    k_bn_bwd_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, buf.invstd[i], g->dgamma[i], g->dbeta[i],
+                                                           buf.kscale, buf.kdb, buf.kdg);
+    k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.y[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
+                                                           buf.kdb, buf.kdg, buf.dz);
+    // ---- weight gradient: transposed operands, tcgen05 GEMM over the pixels ----
+    const __nv_bfloat16 *s0, *s1;
+    int c0, c1;
+    input_of(i, s0, c0, s1, c1);
+    const int cin_pad = c0 + c1, cin_real = w->conv[i].cin;
+    const int Wp = (L.W + 7) / 8 * 8, trows = B * L.H, xchunks = (L.W + 63) / 64;
+    k_transpose<<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0);
+    k_transpose<<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, 0);
+    if (c1) k_transpose<<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, c0);
+    RDP_CUDA_TRY(cudaMemsetAsync(g->dw[i], 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
+    {
+      WgradParams wp{};
+      wp.B = B; wp.H = L.H; wp.W = L.W;
+      wp.cout = C; wp.cin_real = cin_real; wp.cin_pad = cin_pad;
+      wp.n_tile = cin_pad >= 256 ? 256 : cin_pad;
+      wp.m_tiles = (C + 127) / 128;
+      wp.n_tiles = cin_pad / wp.n_tile;
+      wp.taps = i == 0 ? 1 : 9;
+      wp.wsteps = (L.W + 63) / 64;
+      const long long steps = (long long)B * L.H * wp.wsteps;
+      const int items = wp.m_tiles * wp.n_tiles * wp.taps;
+      int ks = (2 * num_sms + items - 1) / items;
+      ks = (int)std::max<long long>(1, std::min<long long>(ks, steps / 4 > 0 ? steps / 4 : 1));
+      wp.ksplit = ks;
+      wp.first_layer = i == 0;
+      wp.dw = g->dw[i];
+      CUtensorMap mz, mx;
+      RDP_TRY(make_cm_map(&mz, buf.dzt, B, L.H, L.W, Wp, C, 128));
+      RDP_TRY(make_cm_map(&mx, buf.xt, B, L.H, L.W, Wp, cin_pad, wp.n_tile));
+      switch (wp.n_tile) {
+        case 64: RDP_TRY(launch_wgrad_t<64>(mz, mx, wp, stream)); break;
+        case 128: RDP_TRY(launch_wgrad_t<128>(mz, mx, wp, stream)); break;
+        default: RDP_TRY(launch_wgrad_t<256>(mz, mx, wp, stream)); break;
+      }
+    }
+    if (i == 0) break;  // the image needs no gradient
+    // ---- input gradient: the same convolution kernel with the flipped, transposed weights ----
+    RDP_TRY(unet::raw_conv(buf.dz, C, nullptr, 0, w->conv[i].w_t, cin_pad, 9, B, L.H, L.W, buf.zero_shift, buf.dx, num_sms, stream));
+    // ---- route it to the producers of the input ----
+    if (i >= 10 && i % 2 == 0) {                       // Up block: [skip | up-sampled low branch]
+      const int j = (i - 10) / 2, skip_i = 7 - 2 * j, low_i = 9 + 2 * j;
+      const Shape Ll = buf.lv[4 - j];
+      k_slice_channels<<<ew_grid(P * c0 / 8), 256, 0, stream>>>(buf.dx, cin_pad / 8, 0, P, c0 / 8, buf.dy[skip_i]);
+      const int dyp = L.H - 2 * Ll.H, dxp = L.W - 2 * Ll.W;
+      const size_t Pl = (size_t)B * Ll.H * Ll.W;
+      k_upsample_bwd<<<ew_grid(Pl * c1 / 8), 256, 0, stream>>>(buf.dx, cin_pad, c0, B, Ll.H, Ll.W, c1 / 8, L.H, L.W, dyp / 2, dxp / 2, buf.dy[low_i]);
+    } else if (i >= 2 && i <= 8 && i % 2 == 0) {       // Down block: the input was pooled from y[i-1], which also feeds a skip
+      const Shape Lp = buf.lv[kLevel[i] - 1];
+      const size_t Pp = (size_t)B * Lp.H * Lp.W;
+      // the skip consumer (an Up block) ran earlier in this loop and wrote dy[i-1]: accumulate
+      k_maxpool_bwd<<<ew_grid(Pp * c0 / 8), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1, buf.dy[i - 1]);
+    } else {
+      RDP_CUDA_TRY(cudaMemcpyAsync(buf.dy[i - 1], buf.dx, P * c0 * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, stream));
+    }
+  }
+#undef RDP_TRY
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}

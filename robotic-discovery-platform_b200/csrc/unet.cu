@@ -34,6 +34,7 @@
 
 #include "rdp_common.cuh"
 #include "sm100_ptx.cuh"
+#include "unet_internal.cuh"
 
 // Development switches are compiled out of the shipped library: an environment variable must never change what a
 // server computes.  Build with -DRDP_DEVELOPMENT (RDP_DEVELOPMENT=1 python rdp_b200/build.py --force) to get them.
@@ -132,7 +133,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // flight while the current one is processed.
 // acc_empty_bar: local barrier to arrive on once the accumulator stage is drained (may be null); remote_empty: the same
 // as a shared::cluster address when the MMA issuer lives in the other CTA of a pair (0 = use the local barrier).
-template <int BN, bool POOL = false>
+template <int BN, bool POOL = false, bool RAW = false>
 __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* s_aux, uint32_t taddr, int nt, int n, int y,
                                               int x, bool inside, uint64_t* acc_empty_bar, int lane, uint32_t remote_empty = 0) {
   const size_t pixel = ((size_t)n * p.H + y) * p.W + x;
@@ -199,7 +200,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
       for (int q = 0; q < 2; ++q) {
         uint32_t o[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = pack_bf16x2<true>(v[16 * q + 2 * e], v[16 * q + 2 * e + 1]);
+        for (int e = 0; e < 8; ++e) o[e] = pack_bf16x2<!RAW>(v[16 * q + 2 * e], v[16 * q + 2 * e + 1]);
         if (inside)
           asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst + 16 * q), "r"(o[0]), "r"(o[1]),
                        "r"(o[2]), "r"(o[3]), "r"(o[4]), "r"(o[5]), "r"(o[6]), "r"(o[7])
@@ -249,7 +250,9 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
   }
 }
 
-template <int BN>
+// RAW: the plain convolution (no ReLU; the caller passes a zero shift) for the training step, where BatchNorm needs the
+// pre-normalisation values and the gradient convolutions have no activation at all.
+template <int BN, bool RAW = false>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
 k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
           const __grid_constant__ CUtensorMap map_w, const ConvParams p) {
@@ -357,7 +360,7 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
       mbar_wait(&acc_full[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
-      epilogue_tile<BN>(p, s_aux, taddr, nt, n, y, x, inside, &acc_empty[as], lane);
+      epilogue_tile<BN, false, RAW>(p, s_aux, taddr, nt, n, y, x, inside, &acc_empty[as], lane);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
   }
@@ -1706,6 +1709,76 @@ int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtenso
 }
 
 }  // namespace
+
+namespace {
+template <int BN>
+int launch_raw_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms, cudaStream_t stream) {
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3<BN, true>), (int)ConvCfg<BN>::SMEM_BYTES));
+  const int grid = p.total_work < num_sms ? p.total_work : num_sms;
+  k_conv3x3<BN, true><<<grid, CONV_THREADS, ConvCfg<BN>::SMEM_BYTES, stream>>>(s0, s1, wm, p);
+  return RDP_OK;
+}
+}  // namespace
+
+// Used by the training step (csrc/train.cu): out[B,H,W,cout] = conv(cat(src0[c0], src1[c1]), w) with `taps` = 9 (3x3, pad 1)
+// or 1 (1x1 over an im2col'ed input), bf16 in and out, no BatchNorm, no ReLU.  `w` = bf16 [cout][taps][c0+c1];
+// `zero_shift` = cout zeros (fp32).  Channel counts are multiples of 64.
+int rdp::unet::raw_conv(const void* src0, int c0, const void* src1, int c1, const void* w, int cout, int taps, int B, int H, int W,
+                        const float* zero_shift, void* out, int num_sms, void* stream_) {
+  RDP_REQUIRE(c0 % 64 == 0 && c1 % 64 == 0 && cout % 64 == 0 && (cout <= 256 || cout % 256 == 0), RDP_ERR_UNSUPPORTED,
+              "raw_conv: channel counts %d+%d -> %d unsupported", c0, c1, cout);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  ConvParams p{};
+  p.B = B; p.H = H; p.W = W;
+  pick_tile(H, W, p.tile_w, p.tile_h);
+  p.tiles_x = (W + p.tile_w - 1) / p.tile_w;
+  p.tiles_y = (H + p.tile_h - 1) / p.tile_h;
+  const int bn = cout >= 256 ? 256 : cout;
+  p.cout = cout;
+  p.n_tiles = cout / bn;
+  p.kb0 = c0 / 64; p.kb1 = c1 / 64;
+  p.taps = taps;
+  p.cin_pad = c0 + c1;
+  p.total_work = B * p.tiles_y * p.tiles_x * p.n_tiles;
+  p.shift = zero_shift;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  CUtensorMap m0, m1, wm;
+  RDP_TRY_RC(make_act_map(&m0, src0, B, H, W, c0, p.tile_w, p.tile_h));
+  RDP_TRY_RC(make_act_map(&m1, c1 ? src1 : src0, B, H, W, c1 ? c1 : c0, p.tile_w, p.tile_h));
+  RDP_TRY_RC(make_weight_map(&wm, w, taps * (c0 + c1), cout, bn));
+  int rc;
+  switch (bn) {
+    case 64: rc = launch_raw_bn<64>(m0, m1, wm, p, num_sms, stream); break;
+    case 128: rc = launch_raw_bn<128>(m0, m1, wm, p, num_sms, stream); break;
+    default: rc = launch_raw_bn<256>(m0, m1, wm, p, num_sms, stream); break;
+  }
+  RDP_CUDA_TRY(cudaGetLastError());
+  return rc;
+}
+
+int rdp::unet::im2col_first(const void* in, int in_fmt, int B, int H, int W, int C, void* out, void* stream_) {
+  const size_t items = (size_t)B * H * W * 8;
+  k_im2col_first<<<(int)std::min<size_t>((items + 255) / 256, 148 * 16), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      in, in_fmt, B, H, W, C, static_cast<__nv_bfloat16*>(out));
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
+
+int rdp::unet::maxpool2(const void* in, int B, int H, int W, int C, void* out, void* stream_) {
+  const int C8 = C / 8;
+  k_maxpool2<<<dim3(((W / 2) * C8 + 255) / 256, H / 2, B), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(in), H, W, C8, log2_exact(C8), static_cast<__nv_bfloat16*>(out));
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
+
+int rdp::unet::upsample2x(const void* in, int B, int h, int w, int C, int Hs, int Ws, void* out, void* stream_) {
+  const int C8 = C / 8, dy = Hs - 2 * h, dx = Ws - 2 * w;
+  k_upsample2x<<<dim3((Ws * C8 + 255) / 256, Hs, B), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(in), h, w, C8, log2_exact(C8), Hs, Ws, dy / 2, dx / 2, static_cast<__nv_bfloat16*>(out));
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
 
 extern "C" int rdp_unet_create(const RdpUnetWeights* w, RdpUnet** out) {
   RDP_REQUIRE(w && out, RDP_ERR_BAD_ARGUMENT, "rdp_unet_create: null argument");

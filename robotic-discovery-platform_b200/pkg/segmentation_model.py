@@ -7,9 +7,9 @@ Same class tree and parameter names as the reference (`pkg/segmentation_model.py
   `pkg.segmentation_model.{UNet, DoubleConv, Down, Up, OutConv}`.
 
 The modules only *hold* parameters.  `UNet.forward` folds BatchNorm into bf16 weights (lazily, and again whenever a
-parameter changes) and runs the hand-written CUDA path; it needs `model.eval()` and a CUDA input, like the server
-provides (`server.py:83,121-123`).  Training-mode forward and CPU tensors raise instead of silently running
-something else; `bilinear=False` constructs like the reference and raises in `forward` as it does there.
+parameter changes) and runs the hand-written CUDA path on a CUDA input, like the server provides
+(`server.py:83,121-123`); in `train()` mode it runs the training step's forward and backward kernels
+(`rdp_b200.train`, `scripts/train_segmenter.py:151-165`).  CPU tensors raise instead of silently running something else; `bilinear=False` constructs like the reference and raises in `forward` as it does there.
 """
 from __future__ import annotations
 
@@ -110,9 +110,9 @@ class UNet(nn.Module):
             state.pop(k, None)
         return state
 
-    def _check(self, x):
-        if self.training:
-            raise RuntimeError("UNet (rdp_b200) runs inference only: call model.eval() first (server.py:83)")
+    def _check(self, x, inference_only=False):
+        if self.training and inference_only:
+            raise RuntimeError("this entry point is the inference fast path: call model.eval() first (server.py:83)")
         if not getattr(self, "bilinear", True):
             # the reference raises here too, from up1's first convolution (`segmentation_model.py:65,75`)
             raise RuntimeError("UNet(bilinear=False): Up.forward concatenates 1024 channels into a DoubleConv built for 512 "
@@ -121,11 +121,22 @@ class UNet(nn.Module):
             raise RuntimeError("UNet (rdp_b200) has no CPU path: move the model and the input to a CUDA device")
 
     # ---- reference interface -----------------------------------------------------------------------------
-    @torch.no_grad()
     def forward(self, x):
-        """(B, n_channels, H, W) float32 on CUDA -> logits (B, n_classes, H, W) float32 (`segmentation_model.py:109`)."""
+        """(B, n_channels, H, W) float32 on CUDA -> logits (B, n_classes, H, W) float32 (`segmentation_model.py:109`).
+
+        In `eval()` mode this is the inference engine (BatchNorm folded into bf16 weights).  In `train()` mode - the
+        reference's training loop, `scripts/train_segmenter.py:151-165` - BatchNorm uses the statistics of the batch and
+        updates its running statistics, and the returned logits carry an autograd graph to every parameter
+        (`rdp_b200.train`), so `criterion(outputs, masks).backward()` and `optimizer.step()` work unchanged."""
         self._check(x)
-        logits, _, _ = self._engine_for(x.device).forward(x.float(), want_logits=True, want_mask=False)
+        if self.training and torch.is_grad_enabled():
+            from rdp_b200.train import train_forward
+            return train_forward(self, x)
+        if self.training:
+            raise RuntimeError("UNet (rdp_b200): train() mode without autograd is not a path the reference uses; "
+                               "call model.eval() for inference (server.py:83)")
+        with torch.no_grad():
+            logits, _, _ = self._engine_for(x.device).forward(x.float(), want_logits=True, want_mask=False)
         return logits
 
     # ---- additive fast path ------------------------------------------------------------------------------
@@ -135,7 +146,7 @@ class UNet(nn.Module):
 
         The mask is `sigmoid(logit) > 0.5` (`server.py:124`) written straight from the last convolution's epilogue.
         """
-        self._check(rgb_u8)
+        self._check(rgb_u8, inference_only=True)
         logits, mask, ws = self._engine_for(rgb_u8.device).forward(rgb_u8, want_logits=want_logits, want_mask=True,
                                                                    workspace=workspace)
         return mask, logits, ws

@@ -13,7 +13,7 @@ CSRC = os.path.join(PKG_ROOT, "csrc")
 LIB_DIR = os.path.join(PKG_ROOT, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "librdp_b200.so")
 BUILD_DIR = os.path.join(PKG_ROOT, "build")
-SOURCES = ["capi.cu", "geometry.cu", "unet.cu", "service.cu", "codec.cu"]
+SOURCES = ["capi.cu", "geometry.cu", "unet.cu", "service.cu", "codec.cu", "train.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

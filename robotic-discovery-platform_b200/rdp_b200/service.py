@@ -193,7 +193,7 @@ def analyze_frames(model, color_u8: torch.Tensor, depth: torch.Tensor, intrinsic
     depth image batch (B,H,W) uint16 | float32 at camera resolution."""
     B, H, W, _ = color_u8.shape
     x = preprocess(color_u8, size, bgr=bgr)
-    model._check(x)
+    model._check(x, inference_only=True)
     _, mask, _ = model._engine_for(x.device).forward(x, want_logits=False, want_mask=True)   # sigmoid(logit) > 0.5
     if mask.shape[1] != 1:
         raise _lib.RdpError("the server's mask path is defined for n_classes == 1 (server.py:124-125)")

@@ -171,8 +171,10 @@ def test_module_interface_matches_fast_path():
     mask, logits, _ = model.forward_mask(torch.from_numpy(batch["rgb"]).cuda(), want_logits=True)
     assert torch.equal(out, logits)
     assert torch.equal((torch.sigmoid(out) > 0.5).to(torch.uint8), mask)          # server.py:124 on our logits
+    with pytest.raises(RuntimeError), torch.no_grad():
+        model.train()(x)                    # train mode is the training step (tests/test_train_gpu.py); it needs autograd
     with pytest.raises(RuntimeError):
-        model.train()(x)
+        model.train().forward_mask(torch.from_numpy(batch["rgb"]).cuda())
     with pytest.raises(RuntimeError):
         model.eval()(x.cpu())
 
