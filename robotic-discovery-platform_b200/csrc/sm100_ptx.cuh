@@ -35,8 +35,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a pipeline bug becomes a trap (launch error) instead of a hung GPU.
+#ifdef RDP_DEVELOPMENT
+// development builds record who timed out (block, thread, barrier address, parity) and carry on, so that the host can
+// read it back (rdp_debug_timeouts) - after a trap the device printf buffer is lost with the context
+__device__ int g_rdp_timeout[8];
+#endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin) {
+#ifdef RDP_DEVELOPMENT
+    if (spin > (1u << 20)) {
+      if (atomicAdd(&g_rdp_timeout[0], 1) == 0) {
+        g_rdp_timeout[1] = (int)blockIdx.x;
+        g_rdp_timeout[2] = (int)threadIdx.x;
+        g_rdp_timeout[3] = (int)smem_u32(bar);
+        g_rdp_timeout[4] = (int)parity;
+      }
+      return;
+    }
+#endif
     if (spin > (1u << 26)) {
       printf("rdp_b200: mbarrier wait timed out (block %d thread %d parity %u)\n", (int)blockIdx.x, (int)threadIdx.x, parity);
       __trap();

@@ -20,12 +20,32 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
 #include "rdp_common.cuh"
 #include "sm100_ptx.cuh"
 #include "unet_internal.cuh"
+
+// Development builds (-DRDP_DEVELOPMENT) with RDP_TRAIN_SYNC set wait after every launch group and name the one that failed.
+#ifdef RDP_DEVELOPMENT
+#define TRAIN_CHECKPOINT(stream, ...)                                                     \
+  do {                                                                                    \
+    if (getenv("RDP_TRAIN_SYNC")) {                                                       \
+      const cudaError_t _e = cudaStreamSynchronize(stream);                               \
+      fprintf(stderr, "train checkpoint: ");                                              \
+      fprintf(stderr, __VA_ARGS__);                                                       \
+      fprintf(stderr, " -> %s\n", cudaGetErrorString(_e));                                \
+      if (_e != cudaSuccess) {                                                            \
+        ::rdp::set_error("training step failed at a checkpoint: %s", cudaGetErrorString(_e)); \
+        return RDP_ERR_CUDA;                                                              \
+      }                                                                                   \
+    }                                                                                     \
+  } while (0)
+#else
+#define TRAIN_CHECKPOINT(stream, ...) do { } while (0)
+#endif
 
 namespace rdp {
 namespace train {
@@ -364,13 +384,17 @@ __global__ void __launch_bounds__(256) k_slice_channels(const __nv_bfloat16* __r
 // that every TMA stride is a multiple of 16 bytes) at channel offset c_off: both wgrad operands need the contraction
 // index (the pixel) as the contiguous one.  Pad columns are never read: the tensor map's width is W, so x >= W is
 // out of bounds and zero-filled, exactly like the convolution's own padding.
+// `dx`: the copy is shifted, dst[.., x] = src[.., x + dx] (zero outside the row).  TMA can shift a box by whole rows
+// (the tap's dy) but not by one pixel along the contiguous dimension - box starts must be 16-byte aligned - so the
+// input is transposed three times, once per horizontal tap offset.
 __global__ void __launch_bounds__(256) k_transpose(const __nv_bfloat16* __restrict__ src, int rows /*B*H*/, int W, int Wp, int C,
-                                                   __nv_bfloat16* __restrict__ dst, int c_off) {
+                                                   __nv_bfloat16* __restrict__ dst, int c_off, int dx) {
   __shared__ __nv_bfloat16 tile[64][64 + 2];
   const int row = blockIdx.x, x0 = blockIdx.z * 64, c0 = blockIdx.y * 64;
   for (int i = threadIdx.x; i < 64 * 64; i += 256) {
     const int r = i >> 6, c = i & 63;
-    tile[r][c] = (x0 + r < W) ? src[((size_t)row * W + x0 + r) * C + c0 + c] : __float2bfloat16(0.f);
+    const int xs = x0 + r + dx;
+    tile[r][c] = (xs >= 0 && xs < W) ? src[((size_t)row * W + xs) * C + c0 + c] : __float2bfloat16(0.f);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < 64 * 64; i += 256) {
@@ -388,6 +412,7 @@ struct WgradParams {
   int m_tiles, n_tiles, taps, ksplit, wsteps;
   int first_layer;              // the input is the im2col'ed image: column k = tap * cin_real + c  ->  dW[co][c][tap]
   float* dw;                    // fp32 [cout][cin_real][3][3]
+  int debug;                    // development builds: 1 = no TMA loads, 2 = no MMAs, 4 = no TMEM reads, 8 = load A only, 16 = load B only
 };
 
 // D[128 output channels x n_tile input channels] += dZ^T[128 x 64 pixels] * X^T(shifted by the tap)[n_tile x 64 pixels]^T over
@@ -438,9 +463,14 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
         long long r = s / p.wsteps;
         const int y = (int)(r % p.H), n = (int)(r / p.H);
         mbar_wait(&empty[stage], phase ^ 1);
+        if (p.debug & 1) { mbar_arrive(&full[stage]); }
+        else if (p.debug & 8) { mbar_arrive_expect_tx(&full[stage], A_BYTES); tma_load_4d(smem + stage * STAGE, &map_dz, xs, y, n, mt * 128, &full[stage]); }
+        else if (p.debug & 16) { mbar_arrive_expect_tx(&full[stage], B_BYTES); tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs, y + dy, n, (dx + 1) * p.cin_pad + nt * NT, &full[stage]); }
+        else {
         mbar_arrive_expect_tx(&full[stage], STAGE);
         tma_load_4d(smem + stage * STAGE, &map_dz, xs, y, n, mt * 128, &full[stage]);
-        tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs + dx, y + dy, n, nt * NT, &full[stage]);
+        tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs, y + dy, n, (dx + 1) * p.cin_pad + nt * NT, &full[stage]);
+        }
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
     }
@@ -454,7 +484,8 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
         const uint64_t da = make_sw128_desc(smem_u32(smem + stage * STAGE));
         const uint64_t db = make_sw128_desc(smem_u32(smem + stage * STAGE + A_BYTES));
 #pragma unroll
-        for (int k = 0; k < 4; ++k) mma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc, (s != s0) || k != 0);
+        for (int k = 0; k < 4; ++k)
+          if (!(p.debug & 2)) mma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc, (s != s0) || k != 0);
         tc_commit(&empty[stage]);
         if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
       }
@@ -469,8 +500,12 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
 #pragma unroll 1
     for (int c = 0; c < NT / 32; ++c) {
       uint32_t r[32];
-      tmem_ld_32x32(taddr + c * 32, r);
-      tmem_ld_wait();
+      if (p.debug & 4) {
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      } else {
+        tmem_ld_32x32(taddr + c * 32, r);
+        tmem_ld_wait();
+      }
       if (co < p.cout) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
@@ -586,7 +621,7 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
     const int cin_pad = i == 0 ? 64 : (w->conv[i].cin + 63) / 64 * 64;
     max_in = std::max(max_in, px(kLevel[i]) * cin_pad);
     max_act_t = std::max(max_act_t, px_padded(kLevel[i]) * w->conv[i].cout);
-    max_in_t = std::max(max_in_t, px_padded(kLevel[i]) * cin_pad);
+    max_in_t = std::max(max_in_t, 3 * px_padded(kLevel[i]) * cin_pad);   // three horizontally shifted copies
     b.mean[i] = c.take<float>(w->conv[i].cout);
     b.var[i] = c.take<float>(w->conv[i].cout);
     b.invstd[i] = c.take<float>(w->conv[i].cout);
@@ -630,6 +665,12 @@ int check_train_args(const RdpTrainWeights* w, int B, int H, int W, const char* 
 
 }  // namespace
 
+#ifdef RDP_DEVELOPMENT
+extern "C" int rdp_debug_timeouts(int* out8) {  // development builds only: first mbarrier wait of this module that timed out
+  return cudaMemcpyFromSymbol(out8, rdp::ptx::g_rdp_timeout, 8 * sizeof(int)) == cudaSuccess ? 0 : -3;
+}
+#endif
+
 extern "C" int rdp_unet_train_workspace_bytes(const RdpTrainWeights* w, int B, int H, int W, size_t* bytes) {
   RDP_REQUIRE(bytes, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_workspace_bytes: null argument");
   const int rc = check_train_args(w, B, H, W, "rdp_unet_train_workspace_bytes");
@@ -661,6 +702,7 @@ extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_n
     const size_t P = (size_t)B * L.H * L.W;
     int r = unet::raw_conv(src0, c0, src1, c1, w->conv[i].w, C, taps, B, L.H, L.W, buf.zero_shift, buf.z[i], num_sms, stream);
     if (r != RDP_OK) return r;
+    TRAIN_CHECKPOINT(stream, "forward conv %d (%dx%d, %d+%d -> %d channels)", i, L.H, L.W, c0, c1, C);
     RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
     const int lanes = std::max(1, ST_THREADS / (C / 8));
     const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
@@ -668,6 +710,7 @@ extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_n
     k_bn_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, w->conv[i].beta, eps, buf.mean[i], buf.var[i],
                                                        buf.invstd[i], buf.scale[i], buf.shift[i]);
     k_bn_relu<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.z[i], P * C / 8, C / 8, buf.scale[i], buf.shift[i], buf.y[i]);
+    TRAIN_CHECKPOINT(stream, "forward batch norm %d", i);
     if (stats && stats->mean[i]) RDP_CUDA_TRY(cudaMemcpyAsync(stats->mean[i], buf.mean[i], C * sizeof(float), cudaMemcpyDeviceToDevice, stream));
     if (stats && stats->var_biased[i]) RDP_CUDA_TRY(cudaMemcpyAsync(stats->var_biased[i], buf.var[i], C * sizeof(float), cudaMemcpyDeviceToDevice, stream));
     return RDP_OK;
@@ -749,16 +792,21 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
                                                            buf.kscale, buf.kdb, buf.kdg);
     k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.y[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
                                                            buf.kdb, buf.kdg, buf.dz);
+    TRAIN_CHECKPOINT(stream, "backward batch norm %d", i);
     // ---- weight gradient: transposed operands, tcgen05 GEMM over the pixels ----
     const __nv_bfloat16 *s0, *s1;
     int c0, c1;
     input_of(i, s0, c0, s1, c1);
     const int cin_pad = c0 + c1, cin_real = w->conv[i].cin;
     const int Wp = (L.W + 7) / 8 * 8, trows = B * L.H, xchunks = (L.W + 63) / 64;
-    k_transpose<<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0);
-    k_transpose<<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, 0);
-    if (c1) k_transpose<<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, c0);
+    k_transpose<<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0, 0);
+    for (int sdx = (i == 0 ? 0 : -1); sdx <= (i == 0 ? 0 : 1); ++sdx) {   // the first layer's input is already im2col'ed
+      const int base = (sdx + 1) * cin_pad;
+      k_transpose<<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, base, sdx);
+      if (c1) k_transpose<<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, base + c0, sdx);
+    }
     RDP_CUDA_TRY(cudaMemsetAsync(g->dw[i], 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
+    TRAIN_CHECKPOINT(stream, "transposes %d", i);
     {
       WgradParams wp{};
       wp.B = B; wp.H = L.H; wp.W = L.W;
@@ -775,18 +823,23 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       wp.ksplit = ks;
       wp.first_layer = i == 0;
       wp.dw = g->dw[i];
+#ifdef RDP_DEVELOPMENT
+      wp.debug = getenv("RDP_WGRAD_DEBUG") ? atoi(getenv("RDP_WGRAD_DEBUG")) : 0;
+#endif
       CUtensorMap mz, mx;
       RDP_TRY(make_cm_map(&mz, buf.dzt, B, L.H, L.W, Wp, C, 128));
-      RDP_TRY(make_cm_map(&mx, buf.xt, B, L.H, L.W, Wp, cin_pad, wp.n_tile));
+      RDP_TRY(make_cm_map(&mx, buf.xt, B, L.H, L.W, Wp, 3 * cin_pad, wp.n_tile));
       switch (wp.n_tile) {
         case 64: RDP_TRY(launch_wgrad_t<64>(mz, mx, wp, stream)); break;
         case 128: RDP_TRY(launch_wgrad_t<128>(mz, mx, wp, stream)); break;
         default: RDP_TRY(launch_wgrad_t<256>(mz, mx, wp, stream)); break;
       }
     }
+    TRAIN_CHECKPOINT(stream, "weight gradient %d (%dx%d, %d x %d)", i, L.H, L.W, C, cin_pad);
     if (i == 0) break;  // the image needs no gradient
     // ---- input gradient: the same convolution kernel with the flipped, transposed weights ----
     RDP_TRY(unet::raw_conv(buf.dz, C, nullptr, 0, w->conv[i].w_t, cin_pad, 9, B, L.H, L.W, buf.zero_shift, buf.dx, num_sms, stream));
+    TRAIN_CHECKPOINT(stream, "input gradient %d", i);
     // ---- route it to the producers of the input ----
     if (i >= 10 && i % 2 == 0) {                       // Up block: [skip | up-sampled low branch]
       const int j = (i - 10) / 2, skip_i = 7 - 2 * j, low_i = 9 + 2 * j;
@@ -803,6 +856,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     } else {
       RDP_CUDA_TRY(cudaMemcpyAsync(buf.dy[i - 1], buf.dx, P * c0 * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, stream));
     }
+    TRAIN_CHECKPOINT(stream, "routing %d", i);
   }
 #undef RDP_TRY
   RDP_CUDA_TRY(cudaGetLastError());
