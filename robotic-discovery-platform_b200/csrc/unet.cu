@@ -776,7 +776,7 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
   const int ncb = p.kb0 + p.kb1;
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + cfg.sa * HALO_STRIDE;
-  const int b_bytes = RESIDENT ? 9 * ncb * B_HALF : cfg.sb * B_HALF;
+  const int b_bytes = RESIDENT ? 9 * ncb * B_HALF : cfg.sb * 9 * B_HALF;  // streamed: a stage = the nine taps of one channel block
   uint8_t* smem_l = smem_b + b_bytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_l + (INTERP ? cfg.sl * PATCH_STRIDE : 0));
   uint64_t* full_a = bars;                          // [HALO_MAX_STAGES]  leader's is used (2 arrivals)
@@ -872,15 +872,14 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
             tma_load_4d_pair(smem_a + sa * HALO_STRIDE, src, c0, x0 - 1, y0 - 1, n, abar);
           }
           if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
-          if (!RESIDENT) {
+          if (!RESIDENT) {  // one hand-shake per channel block, not per tap: nine half slices land on one barrier
+            mbar_wait(&empty_b[sb], pb ^ 1);
+            const uint32_t bbar = mapa_u32(smem_u32(&full_b[sb]), 0);
+            mbar_arrive_expect_tx_cluster(bbar, 9 * B_HALF);
 #pragma unroll 1
-            for (int tap = 0; tap < 9; ++tap) {
-              mbar_wait(&empty_b[sb], pb ^ 1);
-              const uint32_t bbar = mapa_u32(smem_u32(&full_b[sb]), 0);
-              mbar_arrive_expect_tx_cluster(bbar, B_HALF);
-              tma_load_2d_pair(smem_b + sb * B_HALF, &map_w, tap * p.cin_pad + cb * BLOCK_K, (int)rank * (BN / 2), bbar);
-              if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
-            }
+            for (int tap = 0; tap < 9; ++tap)
+              tma_load_2d_pair(smem_b + (sb * 9 + tap) * B_HALF, &map_w, tap * p.cin_pad + cb * BLOCK_K, (int)rank * (BN / 2), bbar);
+            if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
           }
           if (INTERP && cb >= p.kb0 && next_patch < ncb) issue_patch();
         }
@@ -909,25 +908,23 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
               mbar_wait_cluster(&full_a[sa], pa);
               tc_fence_after();
               const uint32_t a_lo = a_lo0 + sa * (HALO_STRIDE >> 4);
-              const uint32_t bres_lo = b_lo0 + cb * (9 * B_HALF >> 4);
+              uint32_t bres_lo = b_lo0 + cb * (9 * B_HALF >> 4);
+              if (!RESIDENT) {
+                mbar_wait_cluster(&full_b[sb], pb);
+                tc_fence_after();
+                bres_lo = b_lo0 + sb * (9 * B_HALF >> 4);
+              }
 #pragma unroll
               for (int tap = 0; tap < 9; ++tap) {
-                uint32_t b_lo;
-                if (RESIDENT) {
-                  b_lo = bres_lo + tap * (B_HALF >> 4);
-                } else {
-                  mbar_wait_cluster(&full_b[sb], pb);
-                  tc_fence_after();
-                  b_lo = b_lo0 + sb * (B_HALF >> 4);
-                }
+                const uint32_t b_lo = bres_lo + tap * (B_HALF >> 4);
                 const uint32_t at_lo = a_lo + ((tap / 3) * HW + tap % 3) * 8;  // 128 bytes per halo row
 #pragma unroll
                 for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
                   mma_bf16_ss_pair_elect(tmem_acc, desc_pack(at_lo + 2 * k, hi_a), desc_pack(b_lo + 2 * k, hi_b), idesc, (cb | tap | k) != 0);
-                if (!RESIDENT) {
-                  tc_commit_pair_elect(&empty_b[sb]);
-                  if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
-                }
+              }
+              if (!RESIDENT) {
+                tc_commit_pair_elect(&empty_b[sb]);
+                if (++sb == (uint32_t)cfg.sb) { sb = 0; pb ^= 1; }
               }
               tc_commit_pair_elect(&empty_a[sa]);
               if (++sa == (uint32_t)cfg.sa) { sa = 0; pa ^= 1; }
@@ -1635,6 +1632,11 @@ inline bool pair_weights_resident(int bn, int ncb, int cout, bool head, bool low
   const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(cout, head) + (low ? patch_stride(1) : 0);
   return 9 * ncb * (bn / 2) * BLOCK_K * 2 + 3 * halo_stride(1) <= HALO_SMEM_TOTAL - fixed;
 }
+// streamed pair: two stages of nine half slices plus at least two halo stages must fit
+inline bool pair_weights_streamable(int bn, int cout, bool head, bool low) {
+  const int fixed = 1024 + HALO_BAR_BYTES + aux_bytes(cout, head) + (low ? patch_stride(1) : 0);
+  return 2 * 9 * (bn / 2) * BLOCK_K * 2 + 2 * halo_stride(1) <= HALO_SMEM_TOTAL - fixed;
+}
 
 // CTA pairs (k_conv3x3_pair): 8x16 tiles, each CTA holds half of every weight slice.
 template <int BN>
@@ -1653,12 +1655,15 @@ int launch_conv_pair(const CUtensorMap& s0, const CUtensorMap& s1, const CUtenso
     return p.low ? launch_conv_pair_t<BN, true, true>(s0, s1, wm_half, p, cfg, num_sms, stream)
                  : launch_conv_pair_t<BN, true, false>(s0, s1, wm_half, p, cfg, num_sms, stream);
   }
-  cfg.sa = 3;
-  if (p.low) {
+  // streamed: two stages of nine half slices each (a whole channel block per hand-shake), the rest goes to halo stages
+  cfg.sb = 2;
+  budget -= cfg.sb * 9 * b_half;
+  if (p.low && budget - 2 * halo_stride(1) >= patch_stride(1)) {
     cfg.sl = 2;
     budget -= patch_stride(1);
   }
-  cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * halo_stride(1)) / b_half);
+  cfg.sa = std::min(HALO_MAX_STAGES, budget / halo_stride(1));
+  RDP_REQUIRE(cfg.sa >= 2, RDP_ERR_UNSUPPORTED, "launch_conv_pair: no room for two halo stages (bn %d, %d channel blocks)", BN, ncb);
   return p.low ? launch_conv_pair_t<BN, false, true>(s0, s1, wm_half, p, cfg, num_sms, stream)
                : launch_conv_pair_t<BN, false, false>(s0, s1, wm_half, p, cfg, num_sms, stream);
 }
@@ -1941,7 +1946,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     p.B = B; p.H = L.H; p.W = L.W;
     const int cout_i = net->w.conv[i].cout;
     const bool pair = taps == 9 && !force_v1 && sel[i] == 'p' && net->bn[i] <= 128 && cout_i == net->bn[i] && net->num_sms >= 2 &&
-                      pair_weights_resident(net->bn[i], (c0 + c1) / 64, cout_i, i == 17 && !debug_nohead, low != nullptr);
+                      (pair_weights_resident(net->bn[i], (c0 + c1) / 64, cout_i, i == 17 && !debug_nohead, low != nullptr) ||
+                       pair_weights_streamable(net->bn[i], cout_i, false, low != nullptr));
     const bool halo = taps == 9 && !force_v1 && (sel[i] == 'h' || sel[i] == 'p');
     const int tiles = (halo && !pair) ? halo_tiles_for(net->bn[i], cout_i / net->bn[i], (c0 + c1) / 64, low != nullptr) : 1;
     if (halo) { p.tile_w = 8 * tiles; p.tile_h = 16; }
