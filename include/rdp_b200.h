@@ -247,8 +247,7 @@ int rdp_pre_decode_sizes(int B, int H, int W, size_t* jpeg_workspace_bytes, size
  * JPEGs `cv2.imencode('.jpg', ...)` writes (client.py:65): baseline sequential Huffman JPEG, decoded with libjpeg's
  * accurate integer inverse DCT, "fancy" chroma up-sampling and fixed-point colour conversion, so the BGR bytes equal
  * OpenCV's (libjpeg-turbo) bit for bit.
- *   data     concatenated JPEG files (device, 16-byte aligned, readable for 64 bytes beyond offsets[B]: the bit readers
- *            fetch aligned 16-byte windows ahead of the byte they need)     offsets  [B+1] int64 byte offsets into data (device)
+ *   data     concatenated JPEG files (device)            offsets  [B+1] int64 byte offsets into data (device)
  *   bgr      [B][H][W][3] uint8 (device)                 status   [B] int32 RDP_DECODE_* (device); a failed image is all zero
  * Two launches.  A Huffman-coded scan is one serial bit stream: one warp per image, so throughput comes from the batch. */
 int rdp_pre_decode_jpeg(const uint8_t* data, const int64_t* offsets, int B, int H, int W, uint8_t* bgr, int32_t* status,

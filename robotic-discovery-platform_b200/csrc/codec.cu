@@ -27,43 +27,6 @@
 namespace rdp {
 namespace codec {
 
-// Sequential byte reader over global memory for the one lane that walks a bit stream: 16-byte aligned loads, the next
-// 16 bytes always already in flight, so the serial decoder never waits for a byte it is about to need (a plain `d[pos]`
-// per byte put an L1 round trip on the critical path of every symbol).  The payload buffer is padded by 64 bytes.
-struct ByteWindow {
-  const uint8_t* d;
-  int wbase;  // offset (relative to d, may be slightly negative) of the 16 bytes held in lo/hi
-  uint64_t lo, hi, nlo, nhi;
-  __device__ __forceinline__ void load(int base, uint64_t& a, uint64_t& b) const {
-    const uint4 v = __ldg(reinterpret_cast<const uint4*>(d + base));
-    a = (uint64_t)v.x | ((uint64_t)v.y << 32);
-    b = (uint64_t)v.z | ((uint64_t)v.w << 32);
-  }
-  __device__ __forceinline__ void init(const uint8_t* data, int pos) {
-    d = data;
-    wbase = pos - (int)(((uintptr_t)data + pos) & 15);
-    load(wbase, lo, hi);
-    load(wbase + 16, nlo, nhi);
-  }
-  __device__ __forceinline__ uint32_t at(int pos) {
-    int off = pos - wbase;
-    if ((unsigned)off >= 16u) {
-      if ((unsigned)off < 32u) {
-        lo = nlo;
-        hi = nhi;
-        wbase += 16;
-      } else {
-        wbase = pos - (int)(((uintptr_t)d + pos) & 15);
-        load(wbase, lo, hi);
-      }
-      load(wbase + 16, nlo, nhi);
-      off = pos - wbase;
-    }
-    const uint64_t h = (off & 8) ? hi : lo;
-    return (uint32_t)(h >> ((off & 7) * 8)) & 0xffu;
-  }
-};
-
 // ---------------------------------------------------------------------------------------------------------
 // JPEG
 // ---------------------------------------------------------------------------------------------------------
@@ -104,8 +67,8 @@ __device__ __forceinline__ int zigzag_at(int k) {
 
 // Entropy-coded segment reader (T.81 F.2.2.5): FF00 is a stuffed FF, any other marker ends the data and feeds zeros.
 struct JpegBits {
-  ByteWindow w;
-  int p, end;  // byte positions inside the file
+  const uint8_t* p;
+  const uint8_t* end;
   uint64_t acc;
   int n;
   int fake;  // zero bits fed behind a marker or the end of the file; the reader looks ahead, so only CONSUMING them is an error
@@ -114,9 +77,9 @@ struct JpegBits {
       uint32_t b = 0;
       bool real = false;
       if (p < end) {
-        b = w.at(p);
+        b = *p;
         if (b == 0xFF) {
-          const uint32_t nx = (p + 1 < end) ? w.at(p + 1) : 0xD9u;
+          const uint32_t nx = (p + 1 < end) ? p[1] : 0xD9u;
           if (nx == 0) {
             p += 2;
             real = true;
@@ -146,7 +109,7 @@ struct JpegBits {
     acc = 0;
     n = 0;
     fake = 0;
-    while (p + 1 < end && !(w.at(p) == 0xFF && w.at(p + 1) >= 0xD0 && w.at(p + 1) <= 0xD7)) ++p;
+    while (p + 1 < end && !(p[0] == 0xFF && p[1] >= 0xD0 && p[1] <= 0xD7)) ++p;
     p += 2;
   }
 };
@@ -345,9 +308,8 @@ __global__ void __launch_bounds__(32) k_jpeg_blocks(const JpegParams p) {
   const int blocks_per_mcu = f.hmax * f.vmax + (f.ncomp == 3 ? 2 : 0);
 
   JpegBits bits;
-  bits.w.init(d, s_scan);
-  bits.p = s_scan;
-  bits.end = len;
+  bits.p = d + s_scan;
+  bits.end = d + len;
   bits.acc = 0;
   bits.n = 0;
   bits.fake = 0;
@@ -520,7 +482,6 @@ struct InflateTable {
 // Byte reader over the IDAT chunks of one PNG: chunk framing (length, type, CRC) is skipped on the fly.
 struct PngBytes {
   const uint8_t* d;
-  ByteWindow w;
   int len, pos, seg_end;
   __device__ bool next_chunk() {  // positions `pos` at the start of the next IDAT payload
     while (pos + 12 <= len) {
@@ -542,7 +503,7 @@ struct PngBytes {
       pos = seg_end + 4;  // CRC of the finished chunk
       if (!next_chunk()) return -1;
     }
-    return (int)w.at(pos++);
+    return d[pos++];
   }
 };
 
@@ -652,7 +613,6 @@ __global__ void __launch_bounds__(32) k_png_inflate(const PngParams p) {
 
   InflateBits bits;
   bits.in.d = d;
-  bits.in.w.init(d, 8);
   bits.in.len = len;
   bits.in.pos = 8;
   bits.in.seg_end = 8;

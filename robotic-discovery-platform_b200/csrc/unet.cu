@@ -1893,6 +1893,10 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   static const bool force_v1 = dev_env("RDP_CONV_V1") != nullptr;  // development switch: per-tap loads everywhere
   // per-layer kernel choice, 'h' = halo reuse, '1' = per-tap loads (RDP_CONV_SEL overrides, 18 characters)
   static const char* sel_env = dev_env("RDP_CONV_SEL");
+  // Streamed weights on a pair (two stages of nine half slices, one hand-shake per channel block) still lose to two
+  // independent CTAs with super-tiles: up3.0 3.14 vs 2.67 ms, up2.3 0.69 vs 0.63 (profiles/r02_pair_streamed_layer_times.txt);
+  // the path stays behind a development switch.
+  static const bool pair_streamed_ok = dev_env("RDP_PAIR_STREAMED") != nullptr;
   // 'p' = halo reuse on CTA pairs (cta_group::2): the 64- and 128-wide layers, whose MMAs are bounded by operand reads
   // (measured, batch 64 at 640x480, pair vs two independent CTAs: down1.3 0.94 vs 1.19 ms, up3.3 0.59 vs 0.69, up4.0 2.34
   // vs 2.80, up4.3 1.40 vs 1.49; inc.3 and down1.0, one 64-channel block per tile, lose to the per-tile hand-shake)
@@ -1947,7 +1951,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     const int cout_i = net->w.conv[i].cout;
     const bool pair = taps == 9 && !force_v1 && sel[i] == 'p' && net->bn[i] <= 128 && cout_i == net->bn[i] && net->num_sms >= 2 &&
                       (pair_weights_resident(net->bn[i], (c0 + c1) / 64, cout_i, i == 17 && !debug_nohead, low != nullptr) ||
-                       pair_weights_streamable(net->bn[i], cout_i, false, low != nullptr));
+                       (pair_streamed_ok && pair_weights_streamable(net->bn[i], cout_i, false, low != nullptr)));
     const bool halo = taps == 9 && !force_v1 && (sel[i] == 'h' || sel[i] == 'p');
     const int tiles = (halo && !pair) ? halo_tiles_for(net->bn[i], cout_i / net->bn[i], (c0 + c1) / 64, low != nullptr) : 1;
     if (halo) { p.tile_w = 8 * tiles; p.tile_h = 16; }

@@ -115,7 +115,7 @@ def _upload_payloads(payloads, device):
     sizes = [len(x) for x in payloads]
     offs = np.zeros(len(sizes) + 1, dtype=np.int64)
     np.cumsum(sizes, out=offs[1:])
-    host = torch.empty(int(offs[-1]) + 64, dtype=torch.uint8).pin_memory()     # the kernels read 16-byte windows ahead
+    host = torch.empty(int(offs[-1]) + 8, dtype=torch.uint8).pin_memory()
     hv = host.numpy()
     for x, o in zip(payloads, offs[:-1]):
         hv[o:o + len(x)] = np.frombuffer(x, dtype=np.uint8)

@@ -22,7 +22,6 @@ PRE = r'''
 #include <string.h>
 #include <vector>
 static inline unsigned __brev(unsigned v) { unsigned r = 0; for (int i = 0; i < 32; i++) { r = (r << 1) | (v & 1); v >>= 1; } return r; }
-struct ByteWindow { const uint8_t* d; void init(const uint8_t* data, int) { d = data; } uint32_t at(int pos) { return d[pos]; } };   // host stand-in
 struct PngParams { const uint8_t* data; const int64_t* offsets; int B, H, W; uint8_t* raw; size_t raw_stride; int* geom; uint16_t* out; int32_t* status; };
 '''
 POST = r'''

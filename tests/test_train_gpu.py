@@ -11,7 +11,8 @@ What is asserted:
   * loss within 1e-3 relative of the fp32 reference;
   * BatchNorm running statistics within 2e-4 + 1e-3 relative of the bf16-rounded reference (the forward pass reproduces
     it to 1e-5 typically) and within 1e-2 of fp32;
-  * every parameter gradient: norm within 3 % of fp32 plus 1.5 x the bf16-rounded reference's own norm shift; relative L2 error against fp32 no worse than 1.25 x that of the
+  * every parameter gradient: norm within 3 % of fp32 plus the larger of 1.5 x the bf16-rounded reference's own norm
+    shift and half its relative L2 error (an error vector of that size moves the norm that much); relative L2 error against fp32 no worse than 1.25 x that of the
     bf16-rounded reference itself + 0.01; closer to the bf16-rounded reference than that reference is to fp32 (+ 0.01);
   * the decoder's last two blocks and the head (up3, up4, outc), which sit before the amplification: within 2 % of the
     tensor's largest entry against fp32 at 4 x 256 x 256."""
@@ -71,7 +72,7 @@ def test_training_step_matches_reference_autograd(name):
         norm_rel = abs(float(p.grad.double().norm()) - n_ref) / n_ref
         if e_gpu > worst[1]:
             worst = (pname, e_gpu)
-        assert norm_rel <= 1.5 * abs(n_emu - n_ref) / n_ref + 0.03, (pname, norm_rel, abs(n_emu - n_ref) / n_ref)
+        assert norm_rel <= max(1.5 * abs(n_emu - n_ref) / n_ref, 0.5 * e_emu) + 0.03, (pname, norm_rel, abs(n_emu - n_ref) / n_ref, e_emu)
         assert e_gpu <= 1.25 * e_emu + 0.01, (pname, e_gpu, e_emu)
         assert e_between <= e_emu + 0.01, (pname, e_between, e_emu)
         if name == "train_step_4x256x256" and pname.split(".")[0] in ("up3", "up4", "outc"):

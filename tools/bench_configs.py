@@ -175,6 +175,36 @@ def server_shaped():
                         "mean_batch": mb.frames_run / max(1, mb.batches_run),
                         "dispatcher_seconds": {k: round(v, 4) for k, v in mb._run.seconds.items()}, "wall_seconds_last_pass": dt})
             print(json.dumps(out[-1]), file=sys.stderr)
+        # N3: the same closed loop from the request's own payloads (JPEG colour + 16-bit PNG depth, client.py:65-67):
+        # (a) host decode in the request thread (cv2.imdecode, server.py:117-118) then analyze(); (b) analyze_encoded(): decoded on the GPU
+        import cv2
+        enc = [(cv2.imencode(".jpg", np.ascontiguousarray(f["rgb"][:, :, ::-1]))[1].tobytes(), cv2.imencode(".png", f["depth"])[1].tobytes())
+               for f in frames]
+        for mode in ("host_decode", "gpu_decode"):
+            for n_thr in (10, 64):
+                with MicroBatcher(model, K, scale, max_batch=n_thr, max_wait_ms=2.0, bgr=True, want_mask=False, want_png=True,
+                                  lanes=2 if n_thr > 10 else 1) as mb:
+                    def worker(t):
+                        for j in range(32):
+                            jb, pb = enc[(t + j) % 8]
+                            if mode == "host_decode":
+                                color = cv2.imdecode(np.frombuffer(jb, np.uint8), cv2.IMREAD_COLOR)
+                                depth = cv2.imdecode(np.frombuffer(pb, np.uint8), cv2.IMREAD_UNCHANGED)
+                                mb.analyze(color, depth)
+                            else:
+                                mb.analyze_encoded(jb, pb)
+                    for rep in range(2):
+                        threads = [threading.Thread(target=worker, args=(t,)) for t in range(n_thr)]
+                        t0 = time.perf_counter()
+                        for t in threads:
+                            t.start()
+                        for t in threads:
+                            t.join()
+                        dt = time.perf_counter() - t0
+                    out.append({"config": f"S3: MicroBatcher from encoded payloads ({mode}), {n_thr} request threads x 32 frames {W}x{H}, wall clock",
+                                "frames_per_s": n_thr * 32 / dt, "mean_batch": mb.frames_run / max(1, mb.batches_run),
+                                "jpeg_kb": len(enc[0][0]) / 1e3, "png_kb": len(enc[0][1]) / 1e3})
+                    print(json.dumps(out[-1]), file=sys.stderr)
     return out
 
 
