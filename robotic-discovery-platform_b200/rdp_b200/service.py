@@ -163,12 +163,31 @@ def decode_depth_png(payloads, *, device=None, check: bool = True):
     return _decode(payloads, "rdp_pre_decode_png16", png_size, (), torch.uint16, 1, device, check)
 
 
+_SIDE_STREAMS: dict = {}
+
+
+def _side_stream(dev):
+    s = _SIDE_STREAMS.get(dev)
+    if s is None:
+        s = _SIDE_STREAMS[dev] = torch.cuda.Stream(dev)
+    return s
+
+
 @torch.no_grad()
 def analyze_encoded(model, color_payloads, depth_payloads, intrinsics, depth_scale, *, size: int = MODEL_IMG_SIZE):
     """The whole loop body of the server from the request's bytes (`server.py:117-141`): both decodes, BGR->RGB, resize,
     U-Net, mask up-size, curvature - nothing decoded ever visits the host."""
-    color, cs = decode_color_jpeg(color_payloads, check=False)
-    depth, ds = decode_depth_png(depth_payloads, device=color.device, check=False)
+    # the two decoders are one serial bit stream per image each: run them side by side on two streams
+    dev = torch.device("cuda", torch.cuda.current_device())
+    main = torch.cuda.current_stream(dev)
+    side = _side_stream(dev)
+    side.wait_stream(main)
+    with torch.cuda.stream(side):
+        depth, ds = decode_depth_png(depth_payloads, device=dev, check=False)
+    color, cs = decode_color_jpeg(color_payloads, device=dev, check=False)
+    main.wait_stream(side)
+    depth.record_stream(main)
+    ds.record_stream(main)
     bad = torch.nonzero((cs != 0) | (ds != 0)).flatten().cpu().tolist()
     if bad:
         raise _lib.RdpError(f"payloads {bad[:8]} could not be decoded (JPEG status {cs.cpu().tolist()}, PNG status {ds.cpu().tolist()})")
