@@ -63,6 +63,7 @@ struct FrameState {
   int bin_off[NUM_BINS + 1];
   int edge_off[NUM_BINS + 1];
   int bin_cursor[NUM_BINS];
+  unsigned char bin_done[NUM_BINS + 2];  // set by k_select_sort_warp for the bins it finished (the CTA kernel takes the others)
 };
 
 struct Params {
@@ -466,7 +467,7 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
   const FrameState& f = p.fs[b];
   if (f.status != RDP_FRAME_OK) return;
   const int cnt = f.bin_count[bin], k = f.bin_k[bin];
-  if (cnt == 0) return;
+  if (cnt == 0 || f.bin_done[bin]) return;  // done: k_select_sort_warp had it
   const size_t fbase = (size_t)b * p.P;
   const bool staged = cnt <= SEL_STAGE_CAP;
   const uint32_t* seg = p.binned + fbase + f.bin_off[bin];              // pixel ids of the bin
@@ -612,6 +613,169 @@ __global__ void __launch_bounds__(SEL_THREADS) k_select_sort(const Params p) {
     p.edge_pix[ebase + i] = px;
     if (p.out.edge_pixels) p.out.edge_pixels[ebase + i] = px;
   }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// k_select_sort_warp: the same selection and ordering, one WARP per (frame, bin), no block barriers
+// ---------------------------------------------------------------------------------------------------------
+// k_select_sort is a chain of ~40 short phases separated by block barriers; with 50 bins per frame of ~1000 points each
+// the launch is bound by that latency chain, not by memory.  Here a warp owns a bin and needs three passes over its keys:
+//   1. min / max of the y keys;
+//   2. a 1024-bucket histogram of the keys, bucket = floor((y - ymin) * 1023 / (ymax - ymin)) - monotone in y, so the
+//      k largest keys are every key in the buckets above a boundary bucket plus the best `need` keys of the boundary
+//      bucket, which are ranked exactly on the composite key (y, then smaller pixel id);
+//   3. gather of the selected points (with their fp64 x) into a per-warp list, ordered by (x, pixel id) by counting ranks.
+// Bins with more than WS_MAX_CNT points, more than WS_LIST selected points or more than WS_LIST tied candidates in the
+// boundary bucket are left to k_select_sort (bin_done stays 0).  Same total order, same result, bit for bit.
+constexpr int WS_WARPS = 4;         // warps (bins) per CTA (8 KB of shared memory each)
+constexpr int WS_BUCKETS = 1024;
+constexpr int WS_LIST = 256;        // selected points / boundary candidates a warp can hold
+constexpr int WS_MAX_CNT = 5000;    // k = int(cnt * 0.05) <= 250
+
+__global__ void __launch_bounds__(WS_WARPS * 32) k_select_sort_warp(const Params p) {
+  __shared__ int s_hist[WS_WARPS][WS_BUCKETS];
+  __shared__ unsigned long long s_key[WS_WARPS][WS_LIST];   // boundary candidates' y keys, then the selected points' x keys
+  __shared__ uint32_t s_px[WS_WARPS][WS_LIST];
+  __shared__ uint32_t s_cand_px[WS_WARPS][WS_LIST];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int item = blockIdx.x * WS_WARPS + warp;
+  if (item >= p.B * NUM_BINS) return;
+  const int b = item / NUM_BINS, bin = item - b * NUM_BINS;
+  FrameState& f = p.fs[b];
+  if (f.status != RDP_FRAME_OK) return;
+  const int cnt = f.bin_count[bin], k = f.bin_k[bin];
+  if (cnt == 0) {
+    if (lane == 0) f.bin_done[bin] = 1;
+    return;
+  }
+  if (cnt > WS_MAX_CNT || k > WS_LIST) return;
+  const size_t fbase = (size_t)b * p.P;
+  const uint32_t* seg = p.binned + fbase + f.bin_off[bin];
+  const unsigned long long* ykeys = p.ykey_b + fbase + f.bin_off[bin];
+  int* hist = s_hist[warp];
+  unsigned long long* lkey = s_key[warp];
+  uint32_t* lpx = s_px[warp];
+  uint32_t* cpx = s_cand_px[warp];
+
+  // pass 1: range of the y keys.  (The passes are latency-bound - one warp, L2 round trips - so every loop keeps
+  // several independent loads in flight.)
+  unsigned long long kmax = 0, kmin_inv = 0;
+#pragma unroll 8
+  for (int i = lane; i < cnt; i += 32) {
+    const unsigned long long yk = ykeys[i];
+    kmax = yk > kmax ? yk : kmax;
+    kmin_inv = ~yk > kmin_inv ? ~yk : kmin_inv;
+  }
+  kmax = warp_max(kmax);
+  const unsigned long long kmin = ~warp_max(kmin_inv);
+  const double ymin = key_to_double(kmin), ymax = key_to_double(kmax);
+  // bucket of a key: monotone non-decreasing in y (a product of non-negative doubles, then truncation)
+  const double scale = ymax > ymin ? (double)(WS_BUCKETS - 1) / (ymax - ymin) : 0.0;
+  auto bucket_of = [&](unsigned long long yk) {
+    const int q = (int)((key_to_double(yk) - ymin) * scale);
+    return q < 0 ? 0 : (q > WS_BUCKETS - 1 ? WS_BUCKETS - 1 : q);
+  };
+  // bucket q lives at hist[(q & 31) * 32 + (q >> 5)]: lane l then reads its 32 consecutive buckets from 32 different banks
+  auto slot = [](int q) { return ((q & 31) << 5) | (q >> 5); };
+  for (int i = lane; i < WS_BUCKETS; i += 32) hist[i] = 0;
+  __syncwarp();
+  // pass 2: histogram
+#pragma unroll 8
+  for (int i = lane; i < cnt; i += 32) atomicAdd(&hist[slot(bucket_of(ykeys[i]))], 1);
+  __syncwarp();
+  // boundary bucket: the highest bucket t with (number of keys in buckets >= t) >= k.  Lane l owns buckets 32l..32l+31.
+  int own = 0;
+  for (int e = 0; e < 32; ++e) own += hist[slot(32 * lane + e)];
+  int above = 0;  // keys in the buckets of higher lanes
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_down_sync(0xffffffffu, own + above, o);
+    if (lane + o < 32) above += v;
+  }
+  const bool mine = above < k && k <= above + own;
+  int tb = 0, need = 0;  // boundary bucket, how many of its keys are selected
+  if (mine) {
+    int cum = above, e = 31;
+    for (; e > 0; --e) {
+      if (cum + hist[slot(32 * lane + e)] >= k) break;
+      cum += hist[slot(32 * lane + e)];
+    }
+    tb = 32 * lane + e;
+    need = k - cum;
+  }
+  const unsigned who = __ballot_sync(0xffffffffu, mine);
+  const int src = __ffs(who) - 1;  // exactly one lane (k >= 1 and k <= cnt)
+  tb = __shfl_sync(0xffffffffu, tb, src);
+  need = __shfl_sync(0xffffffffu, need, src);
+  const int n_tb = hist[slot(tb)];
+  if (n_tb > WS_LIST) return;  // heavy ties at the boundary: the CTA kernel resolves them
+
+  // pass 3: everything above the boundary bucket is selected; the boundary bucket's keys become candidates
+  int n_sel = 0, n_cand = 0;  // warp-uniform running counts
+  for (int i0 = 0; i0 < cnt; i0 += 128) {
+    unsigned long long yk4[4];
+    uint32_t px4[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {  // all eight loads of the iteration are issued before the first use
+      const int i = i0 + 32 * q + lane;
+      yk4[q] = i < cnt ? ykeys[i] : 0ull;
+      px4[q] = i < cnt ? seg[i] : 0u;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i = i0 + 32 * q + lane;
+      const int bk = i < cnt ? bucket_of(yk4[q]) : -1;
+      const bool sel = bk > tb, cand = bk == tb;
+      const unsigned ms = __ballot_sync(0xffffffffu, sel), mc = __ballot_sync(0xffffffffu, cand);
+      const unsigned lt = (1u << lane) - 1u;
+      if (sel) lpx[n_sel + __popc(ms & lt)] = px4[q];
+      if (cand) {
+        const int pos = n_cand + __popc(mc & lt);
+        lkey[WS_LIST - 1 - pos] = yk4[q];  // candidates are parked at the top of the key list (the x keys fill it from the bottom)
+        cpx[pos] = px4[q];
+      }
+      n_sel += __popc(ms);
+      n_cand += __popc(mc);
+    }
+  }
+  __syncwarp();
+  // the `need` best candidates: rank on (y descending, pixel id ascending); ranks are distinct (pixel ids are)
+  for (int c = lane; c < n_cand; c += 32) {
+    const unsigned long long yk = lkey[WS_LIST - 1 - c];
+    const uint32_t px = cpx[c];
+    int rank = 0;
+    for (int j = 0; j < n_cand; ++j) {
+      const unsigned long long yj = lkey[WS_LIST - 1 - j];
+      const uint32_t pj = cpx[j];
+      rank += (yj > yk || (yj == yk && pj < px)) ? 1 : 0;
+    }
+    if (rank < need) lpx[n_sel + rank] = px;  // positions n_sel .. n_sel + need - 1, any order: the sort follows
+  }
+  __syncwarp();
+  // x keys of the k selected points
+  for (int i = lane; i < k; i += 32) {
+    const uint32_t px = lpx[i];
+    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
+    lkey[i] = ordered_key(deproject_axis((double)u, p.cx, depth_to_z(p, fbase + px), p.fx));
+  }
+  __syncwarp();
+  // order by (x, pixel id): rank by counting, then emit
+  const size_t ebase = (size_t)b * p.ecap + f.edge_off[bin];
+  for (int i = lane; i < k; i += 32) {
+    const unsigned long long xk = lkey[i];
+    const uint32_t px = lpx[i];
+    int rank = 0;
+    for (int j = 0; j < k; ++j) rank += (lkey[j] < xk || (lkey[j] == xk && lpx[j] < px)) ? 1 : 0;
+    const int v = (int)(px / (uint32_t)p.W), u = (int)(px - (uint32_t)v * (uint32_t)p.W);
+    const double z = depth_to_z(p, fbase + px);
+    double* dst = p.edge_xyz + 3 * (ebase + rank);
+    dst[0] = deproject_axis((double)u, p.cx, z, p.fx);
+    dst[1] = deproject_axis((double)v, p.cy, z, p.fy);
+    dst[2] = z;
+    p.edge_pix[ebase + rank] = px;
+    if (p.out.edge_pixels) p.out.edge_pixels[ebase + rank] = px;
+  }
+  if (lane == 0) f.bin_done[bin] = 1;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -2101,7 +2265,8 @@ static int curvature_impl(const uint8_t* mask, const void* depth, int depth_fmt,
   mark();
   k_scatter<<<pgrid, PT_THREADS, 0, stream>>>(p);
   mark();
-  k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, 0, stream>>>(p);
+  k_select_sort_warp<<<(B * NUM_BINS + WS_WARPS - 1) / WS_WARPS, WS_WARPS * 32, 0, stream>>>(p);
+  k_select_sort<<<dim3(NUM_BINS, B), SEL_THREADS, 0, stream>>>(p);  // the bins the warp kernel left (large, or heavily tied)
   mark();
   k_fit<<<B, FIT_THREADS, 0, stream>>>(p);
   mark();
