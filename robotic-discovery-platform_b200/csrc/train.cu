@@ -160,34 +160,49 @@ __global__ void __launch_bounds__(256) k_outconv_fwd(const __nv_bfloat16* __rest
   }
 }
 
-// dY[p][c] = sum_cls dlogit[cls][p] w[cls][c];  dW[cls][c] += sum_p dlogit y;  db[cls] += sum_p dlogit
+// dY[p][c] = sum_cls dlogit[cls][p] w[cls][c];  dW[cls][c] += sum_p dlogit y;  db[cls] += sum_p dlogit.
+// A thread owns one 8-channel group and walks pixels (32 side by side per block); its share of dW stays in registers
+// until the end, then one shared-memory and one global atomic per value.
 __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ dlogits, const __nv_bfloat16* __restrict__ y, size_t P,
                                                      size_t HW, int ncls, const float* __restrict__ w, __nv_bfloat16* __restrict__ dy,
                                                      float* dw, float* db) {
   __shared__ float s_dw[8 * 64 + 8];
   for (int i = threadIdx.x; i < 8 * 64 + 8; i += blockDim.x) s_dw[i] = 0.f;
   __syncthreads();
-  const size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (p < P) {
-    const size_t n = p / HW, off = p % HW;
-    float g[8];
-    for (int cls = 0; cls < ncls; ++cls) g[cls] = dlogits[(n * ncls + cls) * HW + off];
-#pragma unroll 1
-    for (int j = 0; j < 8; ++j) {
-      float f[8], o[8];
-      unpack8(reinterpret_cast<const uint4*>(y + p * 64)[j], f);
+  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  float acc[8][8], accb[8], wv[8][8];
+  for (int cls = 0; cls < 8; ++cls) {
+    accb[cls] = 0.f;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) o[k] = 0.f;
-      for (int cls = 0; cls < ncls; ++cls) {
+    for (int k = 0; k < 8; ++k) {
+      acc[cls][k] = 0.f;
+      wv[cls][k] = cls < ncls ? w[cls * 64 + cg * 8 + k] : 0.f;
+    }
+  }
+  for (size_t p = (size_t)blockIdx.x * 32 + rl; p < P; p += (size_t)gridDim.x * 32) {
+    const size_t n = p / HW, off = p % HW;
+    float f[8], o[8];
+    unpack8(reinterpret_cast<const uint4*>(y + p * 64)[cg], f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] = 0.f;
+#pragma unroll
+    for (int cls = 0; cls < 8; ++cls) {
+      if (cls < ncls) {
+        const float g = dlogits[(n * ncls + cls) * HW + off];
+        accb[cls] += g;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          o[k] = fmaf(g[cls], w[cls * 64 + 8 * j + k], o[k]);
-          atomicAdd(&s_dw[cls * 64 + 8 * j + k], g[cls] * f[k]);
+          o[k] = fmaf(g, wv[cls][k], o[k]);
+          acc[cls][k] = fmaf(g, f[k], acc[cls][k]);
         }
       }
-      reinterpret_cast<uint4*>(dy + p * 64)[j] = pack8(o);
     }
-    for (int cls = 0; cls < ncls; ++cls) atomicAdd(&s_dw[8 * 64 + cls], g[cls]);
+    reinterpret_cast<uint4*>(dy + p * 64)[cg] = pack8(o);
+  }
+  for (int cls = 0; cls < ncls; ++cls) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) atomicAdd(&s_dw[cls * 64 + cg * 8 + k], acc[cls][k]);
+    if (cg == 0) atomicAdd(&s_dw[8 * 64 + cls], accb[cls]);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < ncls * 64; i += blockDim.x) atomicAdd(&dw[i], s_dw[i]);
@@ -197,8 +212,11 @@ __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ d
 // ---------------------------------------------------------------------------------------------------------
 // BatchNorm + ReLU backward
 // ---------------------------------------------------------------------------------------------------------
-// sums[c] += sum_p dY~, sums[C + c] += sum_p dY~ xhat,  dY~ = dY [Y > 0],  xhat = (Z - mean) invstd
-__global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+// sums[c] += sum_p dY~, sums[C + c] += sum_p dY~ xhat,  dY~ = dY [Y > 0],  xhat = (Z - mean) invstd.
+// Y > 0 is re-derived from Z with the forward pass's own expression (fmaf(z, scale, shift) > 0: bf16 rounding keeps the
+// sign), which saves reading Y.
+__global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ scale,
+                                                              const float* __restrict__ shift,
                                                               const __nv_bfloat16* __restrict__ z, size_t P, int C,
                                                               const float* __restrict__ mean, const float* __restrict__ invstd, double* sums) {
   extern __shared__ double s_acc[];
@@ -209,21 +227,22 @@ __global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat1
   if (tid < lanes * c8) {
     const int cg = tid % c8, rl = tid / c8;
     double a[8], q[8];
-    float mu[8], is[8];
+    float mu[8], is[8], sc[8], sh[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       a[k] = q[k] = 0.0;
       mu[k] = mean[cg * 8 + k];
       is[k] = invstd[cg * 8 + k];
+      sc[k] = scale[cg * 8 + k];
+      sh[k] = shift[cg * 8 + k];
     }
     for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += (size_t)gridDim.x * lanes) {
-      float g[8], yy[8], zz[8];
+      float g[8], zz[8];
       unpack8(*reinterpret_cast<const uint4*>(dy + r * C + cg * 8), g);
-      unpack8(*reinterpret_cast<const uint4*>(y + r * C + cg * 8), yy);
       unpack8(*reinterpret_cast<const uint4*>(z + r * C + cg * 8), zz);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const float gm = yy[k] > 0.f ? g[k] : 0.f;
+        const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
         a[k] += (double)gm;
         q[k] += (double)gm * (double)((zz[k] - mu[k]) * is[k]);
       }
@@ -250,21 +269,21 @@ __global__ void k_bn_bwd_finalize(const double* sums, int C, double n, const flo
   k_mean_dg[c] = (float)(sums[C + c] / n);
 }
 
-__global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+__global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ scale,
+                                                      const float* __restrict__ shift,
                                                       const __nv_bfloat16* __restrict__ z, size_t n8, int c8, const float* __restrict__ mean,
                                                       const float* __restrict__ invstd, const float* __restrict__ k_scale,
                                                       const float* __restrict__ k_mean_db, const float* __restrict__ k_mean_dg,
                                                       __nv_bfloat16* __restrict__ dz) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     const int cg = (int)(i % c8);
-    float g[8], yy[8], zz[8], o[8];
+    float g[8], zz[8], o[8];
     unpack8(reinterpret_cast<const uint4*>(dy)[i], g);
-    unpack8(reinterpret_cast<const uint4*>(y)[i], yy);
     unpack8(reinterpret_cast<const uint4*>(z)[i], zz);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = cg * 8 + k;
-      const float gm = yy[k] > 0.f ? g[k] : 0.f;
+      const float gm = fmaf(zz[k], scale[c], shift[c]) > 0.f ? g[k] : 0.f;
       const float xh = (zz[k] - mean[c]) * invstd[c];
       o[k] = k_scale[c] * (gm - k_mean_db[c] - xh * k_mean_dg[c]);
     }
@@ -384,22 +403,37 @@ __global__ void __launch_bounds__(256) k_slice_channels(const __nv_bfloat16* __r
 // that every TMA stride is a multiple of 16 bytes) at channel offset c_off: both wgrad operands need the contraction
 // index (the pixel) as the contiguous one.  Pad columns are never read: the tensor map's width is W, so x >= W is
 // out of bounds and zero-filled, exactly like the convolution's own padding.
-// `dx`: the copy is shifted, dst[.., x] = src[.., x + dx] (zero outside the row).  TMA can shift a box by whole rows
-// (the tap's dy) but not by one pixel along the contiguous dimension - box starts must be 16-byte aligned - so the
-// input is transposed three times, once per horizontal tap offset.
+// NSHIFT = 3: three copies, dst_s[.., x] = src[.., x + s - 1] (zero outside the row), `copy_stride` elements apart.
+// TMA can shift a box by whole rows (the tap's dy) but not by one pixel along the contiguous dimension - box starts
+// must be 16-byte aligned - so the input exists once per horizontal tap offset; all three come from one tile read.
+// One CTA: 64 pixels of one image row x 64 channels; 16-byte loads along the channels, 16-byte stores along the pixels.
+template <int NSHIFT>
 __global__ void __launch_bounds__(256) k_transpose(const __nv_bfloat16* __restrict__ src, int rows /*B*H*/, int W, int Wp, int C,
-                                                   __nv_bfloat16* __restrict__ dst, int c_off, int dx) {
-  __shared__ __nv_bfloat16 tile[64][64 + 2];
+                                                   __nv_bfloat16* __restrict__ dst, int c_off, size_t copy_stride) {
+  __shared__ __nv_bfloat16 tile[64][66 + 6];  // [channel][pixel x0-1 .. x0+64], row pitch 72 elements = 144 bytes
   const int row = blockIdx.x, x0 = blockIdx.z * 64, c0 = blockIdx.y * 64;
-  for (int i = threadIdx.x; i < 64 * 64; i += 256) {
-    const int r = i >> 6, c = i & 63;
-    const int xs = x0 + r + dx;
-    tile[r][c] = (xs >= 0 && xs < W) ? src[((size_t)row * W + xs) * C + c0 + c] : __float2bfloat16(0.f);
+  const int first = NSHIFT == 3 ? -1 : 0, npx = NSHIFT == 3 ? 66 : 64;
+  for (int i = threadIdx.x; i < npx * 8; i += 256) {
+    const int r = i >> 3, cg = i & 7;  // pixel of the tile, 8-channel group
+    const int xs = x0 + first + r;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (xs >= 0 && xs < W) v = *reinterpret_cast<const uint4*>(src + ((size_t)row * W + xs) * C + c0 + cg * 8);
+    const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) tile[cg * 8 + k][r] = e[k];
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 64 * 64; i += 256) {
-    const int c = i >> 6, r = i & 63;
-    if (x0 + r < W) dst[((size_t)(c_off + c0 + c) * rows + row) * Wp + x0 + r] = tile[r][c];
+#pragma unroll
+  for (int sft = 0; sft < NSHIFT; ++sft) {
+    __nv_bfloat16* out = dst + (size_t)sft * copy_stride;
+    for (int i = threadIdx.x; i < 64 * 8; i += 256) {
+      const int c = i >> 3, pg = i & 7;  // channel, group of 8 pixels
+      if (x0 + pg * 8 >= W) continue;   // W is a multiple of 8 wherever this runs with a partial tile (Wp == W) or the row is padded
+      __align__(16) __nv_bfloat16 e[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) e[k] = tile[c][pg * 8 + k + sft];  // NSHIFT == 1: sft = 0 reads pixel x0 + ..; == 3: tile column 0 is x0 - 1
+      *reinterpret_cast<uint4*>(out + ((size_t)(c_off + c0 + c) * rows + row) * Wp + x0 + pg * 8) = *reinterpret_cast<const uint4*>(e);
+    }
   }
 }
 
@@ -763,8 +797,9 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
   const size_t P0 = (size_t)B * H * W;
   RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_weight, 0, (size_t)w->n_classes * 64 * sizeof(float), stream));
   RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_bias, 0, (size_t)w->n_classes * sizeof(float), stream));
-  k_outconv_bwd<<<(int)((P0 + 255) / 256), 256, 0, stream>>>(dlogits, buf.y[17], P0, (size_t)H * W, w->n_classes, w->outc_weight, buf.dy[17],
-                                                             g->d_outc_weight, g->d_outc_bias);
+  k_outconv_bwd<<<(int)std::min<size_t>((P0 + 31) / 32, (size_t)num_sms * 8), 256, 0, stream>>>(dlogits, buf.y[17], P0, (size_t)H * W, w->n_classes,
+                                                                                                  w->outc_weight, buf.dy[17], g->d_outc_weight,
+                                                                                                  g->d_outc_bias);
 
   // the input of stage i as (src0[c0] ++ src1[c1]); what the gradient of that input feeds
   auto input_of = [&](int i, const __nv_bfloat16*& s0, int& c0, const __nv_bfloat16*& s1, int& c1) {
@@ -787,10 +822,10 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
     const int lanes = std::max(1, ST_THREADS / (C / 8));
     const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
-    k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.y[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.sums);
+    k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.sums);
     k_bn_bwd_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, buf.invstd[i], g->dgamma[i], g->dbeta[i],
                                                            buf.kscale, buf.kdb, buf.kdg);
-    k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.y[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
+    k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
                                                            buf.kdb, buf.kdg, buf.dz);
     TRAIN_CHECKPOINT(stream, "backward batch norm %d", i);
     // ---- weight gradient: transposed operands, tcgen05 GEMM over the pixels ----
@@ -799,11 +834,13 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     input_of(i, s0, c0, s1, c1);
     const int cin_pad = c0 + c1, cin_real = w->conv[i].cin;
     const int Wp = (L.W + 7) / 8 * 8, trows = B * L.H, xchunks = (L.W + 63) / 64;
-    k_transpose<<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0, 0);
-    for (int sdx = (i == 0 ? 0 : -1); sdx <= (i == 0 ? 0 : 1); ++sdx) {   // the first layer's input is already im2col'ed
-      const int base = (sdx + 1) * cin_pad;
-      k_transpose<<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, base, sdx);
-      if (c1) k_transpose<<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, base + c0, sdx);
+    const size_t copy_stride = (size_t)cin_pad * trows * Wp;   // one horizontally shifted copy of the transposed input
+    k_transpose<1><<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0, 0);
+    if (i == 0) {   // the first layer's input is already im2col'ed: only the unshifted copy (channel block 1 of the map) is read
+      k_transpose<1><<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt + copy_stride, 0, 0);
+    } else {
+      k_transpose<3><<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, 0, copy_stride);
+      if (c1) k_transpose<3><<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, c0, copy_stride);
     }
     RDP_CUDA_TRY(cudaMemsetAsync(g->dw[i], 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
     TRAIN_CHECKPOINT(stream, "transposes %d", i);

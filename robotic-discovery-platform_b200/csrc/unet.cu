@@ -548,7 +548,7 @@ __device__ __forceinline__ int patch_origin(float r, int first_out, int pad) {
   return (int)(r * (float)(o > 0 ? o : 0));
 }
 
-template <int BN, bool RESIDENT, bool INTERP, int TILES>
+template <int BN, bool RESIDENT, bool INTERP, int TILES, bool RAW = false>
 __global__ void __launch_bounds__(conv_threads(INTERP, BN, TILES), 1)
 k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ CUtensorMap map_src1,
                const __grid_constant__ CUtensorMap map_w, const ConvParams p, const HaloCfg cfg) {
@@ -729,7 +729,7 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         const int x = tx * 8 * TILES + h * 8 + (row & 7);
         const bool inside = y < p.H && x < p.W;
         const uint32_t taddr = tmem_base + (as * TILES + h) * BN + ((uint32_t)(quarter * 32) << 16);
-        epilogue_tile<BN, true>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
+        epilogue_tile<BN, true, RAW>(p, s_aux, taddr, nt, n, y, x, inside, h == TILES - 1 ? &acc_empty[as] : nullptr, lane);
       }
     }
     RDP_DEV(if (p.debug_waits && blockIdx.x == 0 && threadIdx.x == 64)
@@ -1607,12 +1607,12 @@ int launch_conv_first(int C, bool u8, const CUtensorMap& wm, const CUtensorMap& 
   }
 }
 
-template <int BN, bool RESIDENT, bool INTERP, int TILES>
+template <int BN, bool RESIDENT, bool INTERP, int TILES, bool RAW = false>
 int launch_conv_halo_t(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p,
                        const HaloCfg& cfg, int num_sms, cudaStream_t stream) {
-  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3_halo<BN, RESIDENT, INTERP, TILES>), HALO_SMEM_TOTAL));
+  RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3_halo<BN, RESIDENT, INTERP, TILES, RAW>), HALO_SMEM_TOTAL));
   const int grid = p.total_work < num_sms ? p.total_work : num_sms;
-  k_conv3x3_halo<BN, RESIDENT, INTERP, TILES><<<grid, conv_threads(INTERP, BN, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
+  k_conv3x3_halo<BN, RESIDENT, INTERP, TILES, RAW><<<grid, conv_threads(INTERP, BN, TILES), HALO_SMEM_TOTAL, stream>>>(s0, s1, wm, p, cfg);
   return RDP_OK;
 }
 
@@ -1716,6 +1716,29 @@ int launch_conv_halo(const CUtensorMap& s0, const CUtensorMap& s1, const CUtenso
 }  // namespace
 
 namespace {
+// The halo kernel without ReLU (training step): same stage planning as launch_conv_halo, no fused up-sampling.
+template <int BN>
+int launch_conv_halo_raw(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int tiles,
+                         int num_sms, cudaStream_t stream) {
+  const int ncb = p.kb0 + p.kb1, b_block = BN * BLOCK_K * 2;
+  const int HALO_STRIDE = halo_stride(tiles);
+  const int budget = HALO_SMEM_TOTAL - (1024 + HALO_BAR_BYTES + aux_bytes(p.cout, false));
+  HaloCfg cfg{};
+  cfg.sl = 1;
+  const int w_bytes = 9 * ncb * b_block;
+  if (tiles == 1 && p.n_tiles == 1 && w_bytes + 3 * HALO_STRIDE <= budget) {
+    cfg.sb = 0;
+    cfg.sa = std::min(HALO_MAX_STAGES, (budget - w_bytes) / HALO_STRIDE);
+    return launch_conv_halo_t<BN, true, false, 1, true>(s0, s1, wm, p, cfg, num_sms, stream);
+  }
+  cfg.sa = (BN == 256 || tiles == 2) ? 2 : 3;
+  cfg.sb = std::min(HALO_MAX_STAGES, (budget - cfg.sa * HALO_STRIDE) / b_block);
+  if constexpr (BN == 128) {
+    if (tiles == 2) return launch_conv_halo_t<BN, false, false, 2, true>(s0, s1, wm, p, cfg, num_sms, stream);
+  }
+  return launch_conv_halo_t<BN, false, false, 1, true>(s0, s1, wm, p, cfg, num_sms, stream);
+}
+
 template <int BN>
 int launch_raw_bn(const CUtensorMap& s0, const CUtensorMap& s1, const CUtensorMap& wm, const ConvParams& p, int num_sms, cudaStream_t stream) {
   RDP_TRY_RC(ensure_dyn_smem(reinterpret_cast<const void*>(&k_conv3x3<BN, true>), (int)ConvCfg<BN>::SMEM_BYTES));
@@ -1735,10 +1758,13 @@ int rdp::unet::raw_conv(const void* src0, int c0, const void* src1, int c1, cons
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   ConvParams p{};
   p.B = B; p.H = H; p.W = W;
-  pick_tile(H, W, p.tile_w, p.tile_h);
+  const int bn = cout >= 256 ? 256 : cout;
+  const bool halo = taps == 9;   // 3x3: the halo-reuse kernel; the im2col'ed first layer (taps == 1) goes per tap
+  const int tiles = halo ? halo_tiles_for(bn, cout / bn, (c0 + c1) / 64, false) : 1;
+  if (halo) { p.tile_w = 8 * tiles; p.tile_h = 16; }
+  else pick_tile(H, W, p.tile_w, p.tile_h);
   p.tiles_x = (W + p.tile_w - 1) / p.tile_w;
   p.tiles_y = (H + p.tile_h - 1) / p.tile_h;
-  const int bn = cout >= 256 ? 256 : cout;
   p.cout = cout;
   p.n_tiles = cout / bn;
   p.kb0 = c0 / 64; p.kb1 = c1 / 64;
@@ -1748,10 +1774,20 @@ int rdp::unet::raw_conv(const void* src0, int c0, const void* src1, int c1, cons
   p.shift = zero_shift;
   p.out = static_cast<__nv_bfloat16*>(out);
   CUtensorMap m0, m1, wm;
-  RDP_TRY_RC(make_act_map(&m0, src0, B, H, W, c0, p.tile_w, p.tile_h));
-  RDP_TRY_RC(make_act_map(&m1, c1 ? src1 : src0, B, H, W, c1 ? c1 : c0, p.tile_w, p.tile_h));
+  const int box_w = halo ? halo_w(tiles) : p.tile_w, box_h = halo ? HALO_H : p.tile_h;
+  RDP_TRY_RC(make_act_map(&m0, src0, B, H, W, c0, box_w, box_h));
+  RDP_TRY_RC(make_act_map(&m1, c1 ? src1 : src0, B, H, W, c1 ? c1 : c0, box_w, box_h));
   RDP_TRY_RC(make_weight_map(&wm, w, taps * (c0 + c1), cout, bn));
   int rc;
+  if (halo) {
+    switch (bn) {
+      case 64: rc = launch_conv_halo_raw<64>(m0, m1, wm, p, tiles, num_sms, stream); break;
+      case 128: rc = launch_conv_halo_raw<128>(m0, m1, wm, p, tiles, num_sms, stream); break;
+      default: rc = launch_conv_halo_raw<256>(m0, m1, wm, p, tiles, num_sms, stream); break;
+    }
+    RDP_CUDA_TRY(cudaGetLastError());
+    return rc;
+  }
   switch (bn) {
     case 64: rc = launch_raw_bn<64>(m0, m1, wm, p, num_sms, stream); break;
     case 128: rc = launch_raw_bn<128>(m0, m1, wm, p, num_sms, stream); break;
