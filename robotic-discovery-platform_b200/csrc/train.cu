@@ -89,13 +89,32 @@ __global__ void __launch_bounds__(ST_THREADS) k_bn_stats(const __nv_bfloat16* __
     double a[8], q[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) a[k] = q[k] = 0.0;
-    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += (size_t)gridDim.x * lanes) {
-      float f[8];
-      unpack8(*reinterpret_cast<const uint4*>(z + r * C + cg * 8), f);
+    // four rows in flight; their sum and sum of squares in fp32 (exact to ~2^-22 relative for four bf16 values), then fp64
+    const size_t rstride = (size_t)gridDim.x * lanes;
+    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const size_t ru = r + u * rstride;
+        v[u] = ru < P ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
+      }
+      float sa[8], sq[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        unpack8(v[u], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          sa[k] += f[k];
+          sq[k] = fmaf(f[k], f[k], sq[k]);
+        }
+      }
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        a[k] += (double)f[k];
-        q[k] += (double)f[k] * (double)f[k];
+        a[k] += (double)sa[k];
+        q[k] += (double)sq[k];
       }
     }
 #pragma unroll
@@ -124,14 +143,37 @@ __global__ void k_bn_finalize(const double* sums, int C, double n, const float* 
   shift[c] = (float)((double)beta[c] - m * (double)gamma[c] * is);
 }
 
+// A thread keeps one 8-channel group for the whole walk (the grid stride is a multiple of c8: c8 divides 256), so the
+// affine coefficients sit in registers.
 __global__ void __launch_bounds__(256) k_bn_relu(const __nv_bfloat16* __restrict__ z, size_t n8, int c8, const float* __restrict__ scale,
                                                  const float* __restrict__ shift, __nv_bfloat16* __restrict__ y) {
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % c8);
+  const int cg = threadIdx.x % c8;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sc[k] = scale[cg * 8 + k];
+    sh[k] = shift[cg * 8 + k];
+  }
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (; i + stride < n8; i += 2 * stride) {
+    const uint4 v0 = reinterpret_cast<const uint4*>(z)[i], v1 = reinterpret_cast<const uint4*>(z)[i + stride];
+    float f0[8], f1[8];
+    unpack8(v0, f0);
+    unpack8(v1, f1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      f0[k] = fmaxf(fmaf(f0[k], sc[k], sh[k]), 0.f);
+      f1[k] = fmaxf(fmaf(f1[k], sc[k], sh[k]), 0.f);
+    }
+    reinterpret_cast<uint4*>(y)[i] = pack8(f0);
+    reinterpret_cast<uint4*>(y)[i + stride] = pack8(f1);
+  }
+  if (i < n8) {
     float f[8];
     unpack8(reinterpret_cast<const uint4*>(z)[i], f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] = fmaxf(fmaf(f[k], scale[cg * 8 + k], shift[cg * 8 + k]), 0.f);
+    for (int k = 0; k < 8; ++k) f[k] = fmaxf(fmaf(f[k], sc[k], sh[k]), 0.f);
     reinterpret_cast<uint4*>(y)[i] = pack8(f);
   }
 }
@@ -236,15 +278,35 @@ __global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat1
       sc[k] = scale[cg * 8 + k];
       sh[k] = shift[cg * 8 + k];
     }
-    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += (size_t)gridDim.x * lanes) {
-      float g[8], zz[8];
-      unpack8(*reinterpret_cast<const uint4*>(dy + r * C + cg * 8), g);
-      unpack8(*reinterpret_cast<const uint4*>(z + r * C + cg * 8), zz);
+    const size_t rstride = (size_t)gridDim.x * lanes;
+    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
+      uint4 vg[4], vz[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const size_t ru = r + u * rstride;
+        const bool in = ru < P;
+        vg[u] = in ? *reinterpret_cast<const uint4*>(dy + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
+        vz[u] = in ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
+      }
+      float sa[8], sq[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float g[8], zz[8];
+        unpack8(vg[u], g);   // rows beyond P carry dY = 0 and add nothing
+        unpack8(vz[u], zz);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
+          sa[k] += gm;
+          sq[k] = fmaf(gm, (zz[k] - mu[k]) * is[k], sq[k]);
+        }
+      }
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
-        a[k] += (double)gm;
-        q[k] += (double)gm * (double)((zz[k] - mu[k]) * is[k]);
+        a[k] += (double)sa[k];
+        q[k] += (double)sq[k];
       }
     }
 #pragma unroll
@@ -275,19 +337,47 @@ __global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __res
                                                       const float* __restrict__ invstd, const float* __restrict__ k_scale,
                                                       const float* __restrict__ k_mean_db, const float* __restrict__ k_mean_dg,
                                                       __nv_bfloat16* __restrict__ dz) {
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % c8);
+  // one 8-channel group per thread for the whole walk (c8 divides the grid stride): the seven per-channel terms in registers
+  const int cg = threadIdx.x % c8;
+  float sc[8], sh[8], mu[8], is[8], ks[8], mdb[8], mdg[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = cg * 8 + k;
+    sc[k] = scale[c];
+    sh[k] = shift[c];
+    mu[k] = mean[c];
+    is[k] = invstd[c];
+    ks[k] = k_scale[c];
+    mdb[k] = k_mean_db[c];
+    mdg[k] = k_mean_dg[c];
+  }
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
+    const bool two = i0 + stride < n8;
+    const size_t i1 = two ? i0 + stride : i0;
+    const uint4 g0 = reinterpret_cast<const uint4*>(dy)[i0], z0 = reinterpret_cast<const uint4*>(z)[i0];
+    const uint4 g1 = reinterpret_cast<const uint4*>(dy)[i1], z1 = reinterpret_cast<const uint4*>(z)[i1];
     float g[8], zz[8], o[8];
-    unpack8(reinterpret_cast<const uint4*>(dy)[i], g);
-    unpack8(reinterpret_cast<const uint4*>(z)[i], zz);
+    unpack8(g0, g);
+    unpack8(z0, zz);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const int c = cg * 8 + k;
-      const float gm = fmaf(zz[k], scale[c], shift[c]) > 0.f ? g[k] : 0.f;
-      const float xh = (zz[k] - mean[c]) * invstd[c];
-      o[k] = k_scale[c] * (gm - k_mean_db[c] - xh * k_mean_dg[c]);
+      const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
+      const float xh = (zz[k] - mu[k]) * is[k];
+      o[k] = ks[k] * (gm - mdb[k] - xh * mdg[k]);
     }
-    reinterpret_cast<uint4*>(dz)[i] = pack8(o);
+    reinterpret_cast<uint4*>(dz)[i0] = pack8(o);
+    if (two) {
+      unpack8(g1, g);
+      unpack8(z1, zz);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
+        const float xh = (zz[k] - mu[k]) * is[k];
+        o[k] = ks[k] * (gm - mdb[k] - xh * mdg[k]);
+      }
+      reinterpret_cast<uint4*>(dz)[i1] = pack8(o);
+    }
   }
 }
 
@@ -464,11 +554,13 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+  // taps vary fastest, the pixel range slowest: the CTAs that run side by side read the same pixels (dZ is the same for
+  // the nine taps, X differs by a row or by the shifted copy), so HBM sees every operand once and L2 serves the rest
   int item = blockIdx.x;
-  const int ks = item % p.ksplit; item /= p.ksplit;
   const int tap = item % p.taps; item /= p.taps;
-  const int nt = item % p.n_tiles;
-  const int mt = item / p.n_tiles;
+  const int nt = item % p.n_tiles; item /= p.n_tiles;
+  const int mt = item % p.m_tiles;
+  const int ks = item / p.m_tiles;
   const int dy = p.taps == 9 ? tap / 3 - 1 : 0, dx = p.taps == 9 ? tap % 3 - 1 : 0;
   const long long total_steps = (long long)p.B * p.H * p.wsteps;
   const long long s0 = total_steps * ks / p.ksplit, s1 = total_steps * (ks + 1) / p.ksplit;
@@ -875,23 +967,24 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     TRAIN_CHECKPOINT(stream, "weight gradient %d (%dx%d, %d x %d)", i, L.H, L.W, C, cin_pad);
     if (i == 0) break;  // the image needs no gradient
     // ---- input gradient: the same convolution kernel with the flipped, transposed weights ----
-    RDP_TRY(unet::raw_conv(buf.dz, C, nullptr, 0, w->conv[i].w_t, cin_pad, 9, B, L.H, L.W, buf.zero_shift, buf.dx, num_sms, stream));
+    const bool up_first = i >= 10 && i % 2 == 0, down_first = i >= 2 && i <= 8 && i % 2 == 0;
+    // second conv of a block: its input is y[i-1] and nothing else reads that, so dX is dY[i-1] itself
+    __nv_bfloat16* dx_out = (up_first || down_first) ? buf.dx : buf.dy[i - 1];
+    RDP_TRY(unet::raw_conv(buf.dz, C, nullptr, 0, w->conv[i].w_t, cin_pad, 9, B, L.H, L.W, buf.zero_shift, dx_out, num_sms, stream));
     TRAIN_CHECKPOINT(stream, "input gradient %d", i);
     // ---- route it to the producers of the input ----
-    if (i >= 10 && i % 2 == 0) {                       // Up block: [skip | up-sampled low branch]
+    if (up_first) {                                    // Up block: [skip | up-sampled low branch]
       const int j = (i - 10) / 2, skip_i = 7 - 2 * j, low_i = 9 + 2 * j;
       const Shape Ll = buf.lv[4 - j];
       k_slice_channels<<<ew_grid(P * c0 / 8), 256, 0, stream>>>(buf.dx, cin_pad / 8, 0, P, c0 / 8, buf.dy[skip_i]);
       const int dyp = L.H - 2 * Ll.H, dxp = L.W - 2 * Ll.W;
       const size_t Pl = (size_t)B * Ll.H * Ll.W;
       k_upsample_bwd<<<ew_grid(Pl * c1 / 8), 256, 0, stream>>>(buf.dx, cin_pad, c0, B, Ll.H, Ll.W, c1 / 8, L.H, L.W, dyp / 2, dxp / 2, buf.dy[low_i]);
-    } else if (i >= 2 && i <= 8 && i % 2 == 0) {       // Down block: the input was pooled from y[i-1], which also feeds a skip
+    } else if (down_first) {                           // Down block: the input was pooled from y[i-1], which also feeds a skip
       const Shape Lp = buf.lv[kLevel[i] - 1];
       const size_t Pp = (size_t)B * Lp.H * Lp.W;
       // the skip consumer (an Up block) ran earlier in this loop and wrote dy[i-1]: accumulate
       k_maxpool_bwd<<<ew_grid(Pp * c0 / 8), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1, buf.dy[i - 1]);
-    } else {
-      RDP_CUDA_TRY(cudaMemcpyAsync(buf.dy[i - 1], buf.dx, P * c0 * sizeof(__nv_bfloat16), cudaMemcpyDeviceToDevice, stream));
     }
     TRAIN_CHECKPOINT(stream, "routing %d", i);
   }
