@@ -487,95 +487,78 @@ __global__ void __launch_bounds__(256) k_slice_channels(const __nv_bfloat16* __r
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// weight gradient: tcgen05 GEMM with K = pixels
+// weight gradient: tcgen05 GEMM with K = pixels, both operands straight from the NHWC tensors
 // ---------------------------------------------------------------------------------------------------------
-// [B][H][W][C] (NHWC) -> [C][B][H][Wp] (channel-major, a row of pixels contiguous, rows padded to Wp = W rounded up to 8 so
-// that every TMA stride is a multiple of 16 bytes) at channel offset c_off: both wgrad operands need the contraction
-// index (the pixel) as the contiguous one.  Pad columns are never read: the tensor map's width is W, so x >= W is
-// out of bounds and zero-filled, exactly like the convolution's own padding.
-// NSHIFT = 3: three copies, dst_s[.., x] = src[.., x + s - 1] (zero outside the row), `copy_stride` elements apart.
-// TMA can shift a box by whole rows (the tap's dy) but not by one pixel along the contiguous dimension - box starts
-// must be 16-byte aligned - so the input exists once per horizontal tap offset; all three come from one tile read.
-// One CTA: 64 pixels of one image row x 64 channels; 16-byte loads along the channels, 16-byte stores along the pixels.
-template <int NSHIFT>
-__global__ void __launch_bounds__(256) k_transpose(const __nv_bfloat16* __restrict__ src, int rows /*B*H*/, int W, int Wp, int C,
-                                                   __nv_bfloat16* __restrict__ dst, int c_off, size_t copy_stride) {
-  __shared__ __nv_bfloat16 tile[64][66 + 6];  // [channel][pixel x0-1 .. x0+64], row pitch 72 elements = 144 bytes
-  const int row = blockIdx.x, x0 = blockIdx.z * 64, c0 = blockIdx.y * 64;
-  const int first = NSHIFT == 3 ? -1 : 0, npx = NSHIFT == 3 ? 66 : 64;
-  for (int i = threadIdx.x; i < npx * 8; i += 256) {
-    const int r = i >> 3, cg = i & 7;  // pixel of the tile, 8-channel group
-    const int xs = x0 + first + r;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (xs >= 0 && xs < W) v = *reinterpret_cast<const uint4*>(src + ((size_t)row * W + xs) * C + c0 + cg * 8);
-    const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&v);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) tile[cg * 8 + k][r] = e[k];
-  }
-  __syncthreads();
-#pragma unroll
-  for (int sft = 0; sft < NSHIFT; ++sft) {
-    __nv_bfloat16* out = dst + (size_t)sft * copy_stride;
-    for (int i = threadIdx.x; i < 64 * 8; i += 256) {
-      const int c = i >> 3, pg = i & 7;  // channel, group of 8 pixels
-      if (x0 + pg * 8 >= W) continue;   // W is a multiple of 8 wherever this runs with a partial tile (Wp == W) or the row is padded
-      __align__(16) __nv_bfloat16 e[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) e[k] = tile[c][pg * 8 + k + sft];  // NSHIFT == 1: sft = 0 reads pixel x0 + ..; == 3: tile column 0 is x0 - 1
-      *reinterpret_cast<uint4*>(out + ((size_t)(c_off + c0 + c) * rows + row) * Wp + x0 + pg * 8) = *reinterpret_cast<const uint4*>(e);
-    }
-  }
-}
-
-constexpr int WG_STAGES = 4;
+// dW[co][ci][tap] = sum over pixels p of dZ[p][co] * X[p + tap][ci].  The contraction index is the pixel, and in NHWC
+// the pixel is the STRIDED index of both operands: exactly the "MN-major" operand form of tcgen05.mma (instruction
+// descriptor bits 15/16; shared-memory descriptor: 64 channels = one 128-byte swizzled row per pixel, eight pixel rows
+// per group, SBO = distance between groups along K, LBO = distance between 64-channel blocks along M / N).  So the
+// tiles arrive by TMA exactly as the convolution loads them - no transposed copies - and a tap is a shifted view:
+//   * one pipeline stage = a patch of 16 x 8 pixels (K = 128): dZ as 64-channel blocks of 128 pixel rows (16 KB each),
+//     X as 64-channel blocks of an 18 x 8 halo (row y + dy of the tap row, columns x0 - 1 .. x0 + 16; TMA zero fill
+//     outside the image = the convolution's padding);
+//   * one MMA (K = 16) = one patch row; its B operand for the horizontal tap dx starts (dx + 1) pixels = 128 bytes
+//     further into the halo row;
+//   * a CTA owns one vertical tap dy and the three horizontal ones: three accumulators of 128 (co) x N (ci) in
+//     tensor memory (N = 128: 384 of the 512 columns), so dZ and the halo are loaded once for three taps;
+//   * split-K over the patches; partial sums go to dW with fp32 atomics.
+// Work items that share pixels (the three dy, the ci tiles, the co tiles) have neighbouring block indices and run
+// together, so HBM sees each tensor once and L2 serves the other readers.
+constexpr int WG_PW = 16, WG_PH = 8;                      // patch: 16 wide, 8 tall
+constexpr int WG_HALO_W = WG_PW + 2;
+constexpr int WG_DZ_BLOCK = WG_PW * WG_PH * 128;          // 16 KB: 128 pixels x 64 output channels
+constexpr int WG_X_BLOCK = WG_HALO_W * WG_PH * 128;       // 18 KB: 18 x 8 pixels x 64 input channels
+constexpr int WG_MAX_STAGES = 8;
 constexpr int WG_THREADS = 192;  // warp 0: TMA, warp 1: MMA, warps 2-5: epilogue
+constexpr int WG_SMEM_BUDGET = 225 * 1024;
 struct WgradParams {
   int B, H, W;
-  int cout, cin_real, cin_pad;  // cin_pad: channels of the transposed input (multiple of 64)
-  int n_tile;                   // columns (input channels) per work item: 64, 128 or 256
-  int m_tiles, n_tiles, taps, ksplit, wsteps;
-  int first_layer;              // the input is the im2col'ed image: column k = tap * cin_real + c  ->  dW[co][c][tap]
+  int cout, cin_real, c0;       // the input is src0[c0 channels] ++ src1[the rest]
+  int co_blocks;                // 64-channel blocks of dZ per M tile: 2, or 1 when cout = 64 (the upper 64 rows repeat the lower)
+  int m_tiles, n_tiles, dys, ksplit, stages;
+  int px_tiles, py_tiles;       // patches along x / y
+  int first_layer;              // the input is the im2col'ed image: column k = tap * cin_real + c  ->  dW[co][c][tap]; one "tap"
   float* dw;                    // fp32 [cout][cin_real][3][3]
-  int debug;                    // development builds: 1 = no TMA loads, 2 = no MMAs, 4 = no TMEM reads, 8 = load A only, 16 = load B only
 };
 
-// D[128 output channels x n_tile input channels] += dZ^T[128 x 64 pixels] * X^T(shifted by the tap)[n_tile x 64 pixels]^T over
-// this CTA's share of the pixels; the partial result is added to dW with fp32 atomics (split-K).
-template <int NT>
+template <int N>
 __global__ void __launch_bounds__(WG_THREADS, 1)
-k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUtensorMap map_x, const WgradParams p) {
-  constexpr int A_BYTES = 128 * 128, B_BYTES = NT * 128, STAGE = A_BYTES + B_BYTES;
+k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUtensorMap map_x0, const __grid_constant__ CUtensorMap map_x1,
+        const WgradParams p) {
+  constexpr int B_BYTES = (N / 64) * WG_X_BLOCK;
+  constexpr uint32_t TMEM_COLS = N == 64 ? 256 : 512;  // three accumulators of N columns
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_STAGES * STAGE);
+  const int a_bytes = p.co_blocks * WG_DZ_BLOCK, stage_bytes = a_bytes + B_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * stage_bytes);
   uint64_t* full = bars;
-  uint64_t* empty = bars + WG_STAGES;
-  uint64_t* done = bars + 2 * WG_STAGES;
+  uint64_t* empty = bars + WG_MAX_STAGES;
+  uint64_t* done = bars + 2 * WG_MAX_STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-  // taps vary fastest, the pixel range slowest: the CTAs that run side by side read the same pixels (dZ is the same for
-  // the nine taps, X differs by a row or by the shifted copy), so HBM sees every operand once and L2 serves the rest
   int item = blockIdx.x;
-  const int tap = item % p.taps; item /= p.taps;
+  const int dyi = item % p.dys; item /= p.dys;
   const int nt = item % p.n_tiles; item /= p.n_tiles;
   const int mt = item % p.m_tiles;
   const int ks = item / p.m_tiles;
-  const int dy = p.taps == 9 ? tap / 3 - 1 : 0, dx = p.taps == 9 ? tap % 3 - 1 : 0;
-  const long long total_steps = (long long)p.B * p.H * p.wsteps;
-  const long long s0 = total_steps * ks / p.ksplit, s1 = total_steps * (ks + 1) / p.ksplit;
+  const int dy = p.dys == 3 ? dyi - 1 : 0;
+  const int ntaps = p.dys == 3 ? 3 : 1;
+  const long long total = (long long)p.B * p.py_tiles * p.px_tiles;
+  const long long s0 = total * ks / p.ksplit, s1 = total * (ks + 1) / p.ksplit;
 
   if (threadIdx.x == 0) {
     prefetch_tensormap(&map_dz);
-    prefetch_tensormap(&map_x);
-    for (int s = 0; s < WG_STAGES; ++s) {
+    prefetch_tensormap(&map_x0);
+    prefetch_tensormap(&map_x1);
+    for (int s = 0; s < WG_MAX_STAGES; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
     mbar_init(done, 1);
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, NT < 32 ? 32 : NT);
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -585,62 +568,80 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
       for (long long s = s0; s < s1; ++s) {
-        const int xs = (int)(s % p.wsteps) * 64;
-        long long r = s / p.wsteps;
-        const int y = (int)(r % p.H), n = (int)(r / p.H);
+        const int px = (int)(s % p.px_tiles);
+        long long r = s / p.px_tiles;
+        const int py = (int)(r % p.py_tiles), n = (int)(r / p.py_tiles);
+        const int x0 = px * WG_PW, y0 = py * WG_PH;
+        uint8_t* st = smem + stage * stage_bytes;
         mbar_wait(&empty[stage], phase ^ 1);
-        if (p.debug & 1) { mbar_arrive(&full[stage]); }
-        else if (p.debug & 8) { mbar_arrive_expect_tx(&full[stage], A_BYTES); tma_load_4d(smem + stage * STAGE, &map_dz, xs, y, n, mt * 128, &full[stage]); }
-        else if (p.debug & 16) { mbar_arrive_expect_tx(&full[stage], B_BYTES); tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs, y + dy, n, (dx + 1) * p.cin_pad + nt * NT, &full[stage]); }
-        else {
-        mbar_arrive_expect_tx(&full[stage], STAGE);
-        tma_load_4d(smem + stage * STAGE, &map_dz, xs, y, n, mt * 128, &full[stage]);
-        tma_load_4d(smem + stage * STAGE + A_BYTES, &map_x, xs, y + dy, n, (dx + 1) * p.cin_pad + nt * NT, &full[stage]);
+        mbar_arrive_expect_tx(&full[stage], stage_bytes);
+        for (int cb = 0; cb < p.co_blocks; ++cb)
+          tma_load_4d(st + cb * WG_DZ_BLOCK, &map_dz, (mt * 2 + cb) * 64, x0, y0, n, &full[stage]);
+#pragma unroll
+        for (int jb = 0; jb < N / 64; ++jb) {
+          const int c = nt * N + jb * 64;
+          if (c < p.c0) tma_load_4d(st + a_bytes + jb * WG_X_BLOCK, &map_x0, c, x0 - 1, y0 + dy, n, &full[stage]);
+          else tma_load_4d(st + a_bytes + jb * WG_X_BLOCK, &map_x1, c - p.c0, x0 - 1, y0 + dy, n, &full[stage]);
         }
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+        if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, NT);
-      uint32_t stage = 0, phase = 0;
-      for (long long s = s0; s < s1; ++s) {
-        mbar_wait(&full[stage], phase);
-        tc_fence_after();
-        const uint64_t da = make_sw128_desc(smem_u32(smem + stage * STAGE));
-        const uint64_t db = make_sw128_desc(smem_u32(smem + stage * STAGE + A_BYTES));
+    // the whole warp walks the loop converged and one elected lane issues: descriptors stay in uniform registers
+    constexpr uint32_t idesc = make_idesc_bf16(128, N) | (1u << 15) | (1u << 16);  // A and B MN-major
+    constexpr uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);                // SBO = 1024 bytes, version 1, 128-byte swizzle
+    const uint32_t lbo_a = (p.co_blocks == 2 ? (uint32_t)WG_DZ_BLOCK >> 4 : 0u) << 16;
+    constexpr uint32_t lbo_b = ((uint32_t)WG_X_BLOCK >> 4) << 16;
+    uint32_t stage = 0, phase = 0;
+    for (long long s = s0; s < s1; ++s) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      const uint32_t a0 = smem_u32(smem + stage * stage_bytes);
+      const uint32_t a_lo = (a0 >> 4) | lbo_a, b_lo = ((a0 + a_bytes) >> 4) | lbo_b;
+      const uint32_t first = s != s0;
+      if (ntaps == 3) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (!(p.debug & 2)) mma_bf16_ss(tmem_base, da + 2 * k, db + 2 * k, idesc, (s != s0) || k != 0);
-        tc_commit(&empty[stage]);
-        if (++stage == WG_STAGES) { stage = 0; phase ^= 1; }
+        for (int r = 0; r < WG_PH; ++r) {
+          const uint64_t da = ((uint64_t)hi << 32) | (a_lo + r * (WG_PW * 128 >> 4));
+#pragma unroll
+          for (int t = 0; t < 3; ++t)
+            mma_bf16_ss_elect(tmem_base + t * N, da, ((uint64_t)hi << 32) | (b_lo + (r * WG_HALO_W + t) * 8), idesc, r != 0 ? 1u : first);
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < WG_PH; ++r)
+          mma_bf16_ss_elect(tmem_base, ((uint64_t)hi << 32) | (a_lo + r * (WG_PW * 128 >> 4)),
+                            ((uint64_t)hi << 32) | (b_lo + (r * WG_HALO_W + 1) * 8), idesc, r != 0 ? 1u : first);
       }
-      tc_commit(done);
+      tc_commit_elect(&empty[stage]);
+      if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
     }
+    tc_commit_elect(done);
   } else if (s1 > s0) {
     const int quarter = warp & 3;
-    const int co = mt * 128 + quarter * 32 + lane;
+    const int row = quarter * 32 + lane;
+    const int co = mt * 128 + row;
     mbar_wait(done, 0);
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const bool row_ok = co < p.cout && (p.co_blocks == 2 || row < 64);
+    for (int t = 0; t < ntaps; ++t) {
+      const int tap = (dy + 1) * 3 + t;
 #pragma unroll 1
-    for (int c = 0; c < NT / 32; ++c) {
-      uint32_t r[32];
-      if (p.debug & 4) {
-        for (int j = 0; j < 32; ++j) r[j] = 0;
-      } else {
-        tmem_ld_32x32(taddr + c * 32, r);
+      for (int c = 0; c < N / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + t * N + c * 32, r);
         tmem_ld_wait();
-      }
-      if (co < p.cout) {
+        if (row_ok) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int ci = nt * NT + c * 32 + j;
-          const float v = __uint_as_float(r[j]);
-          if (p.first_layer) {
-            if (ci < 9 * p.cin_real) atomicAdd(&p.dw[((size_t)co * p.cin_real + ci % p.cin_real) * 9 + ci / p.cin_real], v);
-          } else if (ci < p.cin_real) {
-            atomicAdd(&p.dw[((size_t)co * p.cin_real + ci) * 9 + tap], v);
+          for (int j = 0; j < 32; ++j) {
+            const int ci = nt * N + c * 32 + j;
+            const float v = __uint_as_float(r[j]);
+            if (p.first_layer) {
+              if (ci < 9 * p.cin_real) atomicAdd(&p.dw[((size_t)co * p.cin_real + ci % p.cin_real) * 9 + ci / p.cin_real], v);
+            } else if (ci < p.cin_real) {
+              atomicAdd(&p.dw[((size_t)co * p.cin_real + ci) * 9 + tap], v);
+            }
           }
         }
       }
@@ -650,7 +651,7 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, NT < 32 ? 32 : NT);
+    tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
@@ -667,31 +668,34 @@ static EncodeTiledFn encode_fn() {
   }
   return fn;
 }
-// map over a channel-major tensor [C][B][H][Wp]: dims (W, H, B, C), box (64 pixels of a row, 1, 1, rows channels)
-static int make_cm_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int Wp, int C, int rows) {
+// map over an NHWC bf16 tensor: dims (C, W, H, B), box (64 channels, box_w pixels, WG_PH rows, 1), 128-byte swizzle,
+// zero fill outside
+static int make_nhwc_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w) {
   EncodeTiledFn fn = encode_fn();
   RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
-  cuuint64_t dims[4] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B, (cuuint64_t)C};
-  cuuint64_t strides[3] = {(cuuint64_t)Wp * 2, (cuuint64_t)H * Wp * 2, (cuuint64_t)B * H * Wp * 2};
-  cuuint32_t box[4] = {64, 1, 1, (cuuint32_t)rows};
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)WG_PH, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(channel-major %dx%dx%dx%d) failed: %d", C, B, H, W, (int)r);
+  RDP_REQUIRE(r == CUDA_SUCCESS, RDP_ERR_CUDA, "cuTensorMapEncodeTiled(NHWC %dx%dx%dx%d) failed: %d", B, H, W, C, (int)r);
   return RDP_OK;
 }
 
-template <int NT>
-static int launch_wgrad_t(const CUtensorMap& mz, const CUtensorMap& mx, const WgradParams& p, cudaStream_t stream) {
-  constexpr int SMEM = WG_STAGES * (128 * 128 + NT * 128) + 1024 + 256;
+template <int N>
+static int launch_wgrad_t(const CUtensorMap& mz, const CUtensorMap& mx0, const CUtensorMap& mx1, WgradParams p, cudaStream_t stream) {
+  const int stage_bytes = p.co_blocks * WG_DZ_BLOCK + (N / 64) * WG_X_BLOCK;
+  p.stages = std::min(WG_MAX_STAGES, (WG_SMEM_BUDGET - 2048) / stage_bytes);
+  const int smem_bytes = p.stages * stage_bytes + 1024 + 256;
   static bool set[64] = {};
   int dev = 0;
   RDP_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 64 && !set[dev]) {
-    RDP_CUDA_TRY(cudaFuncSetAttribute(k_wgrad<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_wgrad<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BUDGET));
     set[dev] = true;
   }
-  k_wgrad<NT><<<p.m_tiles * p.n_tiles * p.taps * p.ksplit, WG_THREADS, SMEM, stream>>>(mz, mx, p);
+  k_wgrad<N><<<p.m_tiles * p.n_tiles * p.dys * p.ksplit, WG_THREADS, smem_bytes, stream>>>(mz, mx0, mx1, p);
   return RDP_OK;
 }
 
@@ -723,8 +727,6 @@ struct TrainBuffers {
   __nv_bfloat16* dz;         // gradient wrt the current layer's z (largest layer)
   __nv_bfloat16* dx;         // gradient wrt the current layer's (concatenated) input
   __nv_bfloat16* dpool;      // gradient wrt a pooled tensor (alias of dx is not possible: both live)
-  __nv_bfloat16* xt;         // transposed input of the current layer
-  __nv_bfloat16* dzt;        // transposed dz
   float *kscale, *kdb, *kdg;  // [1024] each
   size_t bytes;
 };
@@ -735,9 +737,8 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   for (int i = 1; i < 5; ++i) b.lv[i] = {b.lv[i - 1].H / 2, b.lv[i - 1].W / 2};
   Carver c(ws);
   auto px = [&](int l) { return (size_t)B * b.lv[l].H * b.lv[l].W; };
-  auto px_padded = [&](int l) { return (size_t)B * b.lv[l].H * ((b.lv[l].W + 7) / 8 * 8); };
   b.col = c.take<__nv_bfloat16>(px(0) * 64);
-  size_t max_act = 0, max_in = 0, max_act_t = 0, max_in_t = 0;
+  size_t max_act = 0, max_in = 0;
   for (int i = 0; i < 18; ++i) {
     const size_t n = px(kLevel[i]) * w->conv[i].cout;
     b.z[i] = c.take<__nv_bfloat16>(n);
@@ -746,8 +747,6 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
     max_act = std::max(max_act, n);
     const int cin_pad = i == 0 ? 64 : (w->conv[i].cin + 63) / 64 * 64;
     max_in = std::max(max_in, px(kLevel[i]) * cin_pad);
-    max_act_t = std::max(max_act_t, px_padded(kLevel[i]) * w->conv[i].cout);
-    max_in_t = std::max(max_in_t, 3 * px_padded(kLevel[i]) * cin_pad);   // three horizontally shifted copies
     b.mean[i] = c.take<float>(w->conv[i].cout);
     b.var[i] = c.take<float>(w->conv[i].cout);
     b.invstd[i] = c.take<float>(w->conv[i].cout);
@@ -761,8 +760,6 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   b.dz = c.take<__nv_bfloat16>(max_act);
   b.dx = c.take<__nv_bfloat16>(max_in);
   b.dpool = c.take<__nv_bfloat16>(max_act);
-  b.xt = c.take<__nv_bfloat16>(max_in_t);
-  b.dzt = c.take<__nv_bfloat16>(max_act_t);
   b.kscale = c.take<float>(1024);
   b.kdb = c.take<float>(1024);
   b.kdg = c.take<float>(1024);
@@ -920,49 +917,35 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
                                                            buf.kdb, buf.kdg, buf.dz);
     TRAIN_CHECKPOINT(stream, "backward batch norm %d", i);
-    // ---- weight gradient: transposed operands, tcgen05 GEMM over the pixels ----
+    // ---- weight gradient: tcgen05 GEMM over the pixels, operands read in place ----
     const __nv_bfloat16 *s0, *s1;
     int c0, c1;
     input_of(i, s0, c0, s1, c1);
     const int cin_pad = c0 + c1, cin_real = w->conv[i].cin;
-    const int Wp = (L.W + 7) / 8 * 8, trows = B * L.H, xchunks = (L.W + 63) / 64;
-    const size_t copy_stride = (size_t)cin_pad * trows * Wp;   // one horizontally shifted copy of the transposed input
-    k_transpose<1><<<dim3(trows, C / 64, xchunks), 256, 0, stream>>>(buf.dz, trows, L.W, Wp, C, buf.dzt, 0, 0);
-    if (i == 0) {   // the first layer's input is already im2col'ed: only the unshifted copy (channel block 1 of the map) is read
-      k_transpose<1><<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt + copy_stride, 0, 0);
-    } else {
-      k_transpose<3><<<dim3(trows, c0 / 64, xchunks), 256, 0, stream>>>(s0, trows, L.W, Wp, c0, buf.xt, 0, copy_stride);
-      if (c1) k_transpose<3><<<dim3(trows, c1 / 64, xchunks), 256, 0, stream>>>(s1, trows, L.W, Wp, c1, buf.xt, c0, copy_stride);
-    }
     RDP_CUDA_TRY(cudaMemsetAsync(g->dw[i], 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
-    TRAIN_CHECKPOINT(stream, "transposes %d", i);
     {
       WgradParams wp{};
       wp.B = B; wp.H = L.H; wp.W = L.W;
-      wp.cout = C; wp.cin_real = cin_real; wp.cin_pad = cin_pad;
-      wp.n_tile = cin_pad >= 256 ? 256 : cin_pad;
+      wp.cout = C; wp.cin_real = cin_real; wp.c0 = c0;
+      wp.co_blocks = C >= 128 ? 2 : 1;
+      const int n_tile = cin_pad >= 128 ? 128 : 64;
       wp.m_tiles = (C + 127) / 128;
-      wp.n_tiles = cin_pad / wp.n_tile;
-      wp.taps = i == 0 ? 1 : 9;
-      wp.wsteps = (L.W + 63) / 64;
-      const long long steps = (long long)B * L.H * wp.wsteps;
-      const int items = wp.m_tiles * wp.n_tiles * wp.taps;
-      int ks = (2 * num_sms + items - 1) / items;
-      ks = (int)std::max<long long>(1, std::min<long long>(ks, steps / 4 > 0 ? steps / 4 : 1));
-      wp.ksplit = ks;
+      wp.n_tiles = cin_pad / n_tile;
+      wp.dys = i == 0 ? 1 : 3;
+      wp.px_tiles = (L.W + WG_PW - 1) / WG_PW;
+      wp.py_tiles = (L.H + WG_PH - 1) / WG_PH;
+      const long long patches = (long long)B * wp.px_tiles * wp.py_tiles;
+      const int items = wp.m_tiles * wp.n_tiles * wp.dys;
+      wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches));   // two full waves, one CTA per SM
       wp.first_layer = i == 0;
       wp.dw = g->dw[i];
-#ifdef RDP_DEVELOPMENT
-      wp.debug = getenv("RDP_WGRAD_DEBUG") ? atoi(getenv("RDP_WGRAD_DEBUG")) : 0;
-#endif
-      CUtensorMap mz, mx;
-      RDP_TRY(make_cm_map(&mz, buf.dzt, B, L.H, L.W, Wp, C, 128));
-      RDP_TRY(make_cm_map(&mx, buf.xt, B, L.H, L.W, Wp, 3 * cin_pad, wp.n_tile));
-      switch (wp.n_tile) {
-        case 64: RDP_TRY(launch_wgrad_t<64>(mz, mx, wp, stream)); break;
-        case 128: RDP_TRY(launch_wgrad_t<128>(mz, mx, wp, stream)); break;
-        default: RDP_TRY(launch_wgrad_t<256>(mz, mx, wp, stream)); break;
-      }
+      CUtensorMap mz, mx0, mx1;
+      RDP_TRY(make_nhwc_map(&mz, buf.dz, B, L.H, L.W, C, WG_PW));
+      RDP_TRY(make_nhwc_map(&mx0, s0, B, L.H, L.W, c0, WG_HALO_W));
+      if (c1) RDP_TRY(make_nhwc_map(&mx1, s1, B, L.H, L.W, c1, WG_HALO_W));
+      else mx1 = mx0;
+      if (n_tile == 64) RDP_TRY(launch_wgrad_t<64>(mz, mx0, mx1, wp, stream));
+      else RDP_TRY(launch_wgrad_t<128>(mz, mx0, mx1, wp, stream));
     }
     TRAIN_CHECKPOINT(stream, "weight gradient %d (%dx%d, %d x %d)", i, L.H, L.W, C, cin_pad);
     if (i == 0) break;  // the image needs no gradient
