@@ -75,65 +75,109 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
 // ---------------------------------------------------------------------------------------------------------
 // BatchNorm (training mode) forward
 // ---------------------------------------------------------------------------------------------------------
-// sums[c] += sum_p z[p][c], sums[C + c] += sum_p z[p][c]^2 (fp64 atomics; z is bf16 [P][C], C a multiple of 8 and
-// a divisor of 2048).  A thread owns 8 channels and walks rows; partial sums go through shared memory once per block.
+// Per-thread partial sums of one 8-channel group -> the block's [2][C] array `s_acc` (zeroed by the caller), then the
+// block's row of the partial-sum table `part` ([gridDim.x][2C]).  No atomics anywhere: lanes of a warp that hold the same
+// group (c8 < 32: lanes cg, cg + c8, ...) are folded with shuffles, the eight warps then add their values one warp at a
+// time (within a warp the active lanes own distinct channels), and the finalize kernel adds the blocks' rows in a fixed
+// order.  The statistics are therefore bit-reproducible from run to run.  Called by every thread of the block; needs
+// c8 to be a power of two no larger than the block (threads without rows pass zeros).
 constexpr int ST_THREADS = 256;
-__global__ void __launch_bounds__(ST_THREADS) k_bn_stats(const __nv_bfloat16* __restrict__ z, size_t P, int C, double* sums) {
-  extern __shared__ double s_acc[];  // [2][C]
-  const int c8 = C / 8, tid = threadIdx.x;
-  const int lanes = ST_THREADS / c8 > 0 ? ST_THREADS / c8 : 1;  // rows handled side by side
-  for (int i = tid; i < 2 * C; i += ST_THREADS) s_acc[i] = 0.0;
-  __syncthreads();
-  if (tid < lanes * c8) {
-    const int cg = tid % c8, rl = tid / c8;
-    double a[8], q[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) a[k] = q[k] = 0.0;
-    // four rows in flight; their sum and sum of squares in fp32 (exact to ~2^-22 relative for four bf16 values), then fp64
-    const size_t rstride = (size_t)gridDim.x * lanes;
-    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
-      uint4 v[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const size_t ru = r + u * rstride;
-        v[u] = ru < P ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
-      }
-      float sa[8], sq[8];
-#pragma unroll
-      for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        float f[8];
-        unpack8(v[u], f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          sa[k] += f[k];
-          sq[k] = fmaf(f[k], f[k], sq[k]);
-        }
-      }
+__device__ __forceinline__ void block_channel_sums(double (&a)[8], double (&q)[8], double* s_acc, int C, int c8, int cg, double* part) {
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  bool active = true;
+  if (c8 < 32) {
+    for (int off = 16; off >= c8; off >>= 1) {
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        a[k] += (double)sa[k];
-        q[k] += (double)sq[k];
+        a[k] += __shfl_xor_sync(0xffffffffu, a[k], off);
+        q[k] += __shfl_xor_sync(0xffffffffu, q[k], off);
+      }
+    }
+    active = lane < c8;
+  }
+  for (int w = 0; w < ST_THREADS / 32; ++w) {
+    if (warp == w && active) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s_acc[cg * 8 + k] += a[k];
+        s_acc[C + cg * 8 + k] += q[k];
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < 2 * C; i += ST_THREADS) part[(size_t)blockIdx.x * 2 * C + i] = s_acc[i];
+}
+
+// the two sums of channel c over the blocks' rows of the table: one warp per channel, fixed order
+__device__ __forceinline__ void reduce_partials(const double* __restrict__ part, int nb, int C, int c, int lane, double& s0, double& s1) {
+  double x = 0.0, y = 0.0;
+  for (int b = lane; b < nb; b += 32) {
+    x += part[(size_t)b * 2 * C + c];
+    y += part[(size_t)b * 2 * C + C + c];
+  }
+#pragma unroll
+  for (int off = 16; off; off >>= 1) {
+    x += __shfl_xor_sync(0xffffffffu, x, off);
+    y += __shfl_xor_sync(0xffffffffu, y, off);
+  }
+  s0 = x;
+  s1 = y;
+}
+
+// part[block][c] = sum_p z[p][c], part[block][C + c] = sum_p z[p][c]^2 over the block's rows (z is bf16 [P][C], C/8 a
+// power of two <= 256).  A thread owns 8 channels and walks rows.
+__global__ void __launch_bounds__(ST_THREADS) k_bn_stats(const __nv_bfloat16* __restrict__ z, size_t P, int C, double* part) {
+  extern __shared__ double s_acc[];  // [2][C]
+  const int c8 = C / 8, tid = threadIdx.x;
+  const int lanes = ST_THREADS / c8;  // rows handled side by side
+  for (int i = tid; i < 2 * C; i += ST_THREADS) s_acc[i] = 0.0;
+  __syncthreads();
+  const int cg = tid % c8, rl = tid / c8;
+  double a[8], q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = q[k] = 0.0;
+  // four rows in flight; their sum and sum of squares in fp32 (exact to ~2^-22 relative for four bf16 values), then fp64
+  const size_t rstride = (size_t)gridDim.x * lanes;
+  for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t ru = r + u * rstride;
+      v[u] = ru < P ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
+    }
+    float sa[8], sq[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float f[8];
+      unpack8(v[u], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        sa[k] += f[k];
+        sq[k] = fmaf(f[k], f[k], sq[k]);
       }
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      atomicAdd(&s_acc[cg * 8 + k], a[k]);
-      atomicAdd(&s_acc[C + cg * 8 + k], q[k]);
+      a[k] += (double)sa[k];
+      q[k] += (double)sq[k];
     }
   }
-  __syncthreads();
-  for (int i = tid; i < 2 * C; i += ST_THREADS) atomicAdd(&sums[i], s_acc[i]);
+  block_channel_sums(a, q, s_acc, C, c8, cg, part);
 }
 
-// mean, biased variance, and the affine form of the normalisation: y = z * scale + shift
-__global__ void k_bn_finalize(const double* sums, int C, double n, const float* gamma, const float* beta, float eps, float* mean,
-                              float* var, float* invstd, float* scale, float* shift) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// mean, biased variance, and the affine form of the normalisation: y = z * scale + shift.  One warp per channel.
+__global__ void __launch_bounds__(256) k_bn_finalize(const double* __restrict__ part, int nb, int C, double n, const float* gamma,
+                                                     const float* beta, float eps, float* mean, float* var, float* invstd, float* scale,
+                                                     float* shift) {
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
-  const double m = sums[c] / n;
-  double v = sums[C + c] / n - m * m;
+  double s0, s1;
+  reduce_partials(part, nb, C, c, lane, s0, s1);
+  if (lane) return;
+  const double m = s0 / n;
+  double v = s1 / n - m * m;
   v = v > 0.0 ? v : 0.0;
   const double is = 1.0 / sqrt(v + (double)eps);
   mean[c] = (float)m;
@@ -205,6 +249,7 @@ __global__ void __launch_bounds__(256) k_outconv_fwd(const __nv_bfloat16* __rest
 // dY[p][c] = sum_cls dlogit[cls][p] w[cls][c];  dW[cls][c] += sum_p dlogit y;  db[cls] += sum_p dlogit.
 // A thread owns one 8-channel group and walks pixels (32 side by side per block); its share of dW stays in registers
 // until the end, then one shared-memory and one global atomic per value.
+template <int NC>  // classes the registers are sized for (>= ncls)
 __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ dlogits, const __nv_bfloat16* __restrict__ y, size_t P,
                                                      size_t HW, int ncls, const float* __restrict__ w, __nv_bfloat16* __restrict__ dy,
                                                      float* dw, float* db) {
@@ -212,8 +257,9 @@ __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ d
   for (int i = threadIdx.x; i < 8 * 64 + 8; i += blockDim.x) s_dw[i] = 0.f;
   __syncthreads();
   const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
-  float acc[8][8], accb[8], wv[8][8];
-  for (int cls = 0; cls < 8; ++cls) {
+  float acc[NC][8], accb[NC], wv[NC][8];
+#pragma unroll
+  for (int cls = 0; cls < NC; ++cls) {
     accb[cls] = 0.f;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -221,30 +267,53 @@ __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ d
       wv[cls][k] = cls < ncls ? w[cls * 64 + cg * 8 + k] : 0.f;
     }
   }
-  for (size_t p = (size_t)blockIdx.x * 32 + rl; p < P; p += (size_t)gridDim.x * 32) {
-    const size_t n = p / HW, off = p % HW;
-    float f[8], o[8];
-    unpack8(reinterpret_cast<const uint4*>(y + p * 64)[cg], f);
+  const size_t pstride = (size_t)gridDim.x * 32;
+  for (size_t p0 = (size_t)blockIdx.x * 32 + rl; p0 < P; p0 += 4 * pstride) {  // four pixels in flight
+    uint4 yv[4];
+    float gv[4][NC];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) o[k] = 0.f;
+    for (int u = 0; u < 4; ++u) {
+      const size_t pu = p0 + u * pstride;
+      const bool in = pu < P;
+      yv[u] = in ? reinterpret_cast<const uint4*>(y + pu * 64)[cg] : make_uint4(0, 0, 0, 0);
+      if (NC == 1) {
+        gv[u][0] = in ? dlogits[pu] : 0.f;  // one class: (n, 0, off) is pixel pu itself
+      } else {
+        const size_t n = pu / HW, off = pu % HW;
 #pragma unroll
-    for (int cls = 0; cls < 8; ++cls) {
-      if (cls < ncls) {
-        const float g = dlogits[(n * ncls + cls) * HW + off];
-        accb[cls] += g;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          o[k] = fmaf(g, wv[cls][k], o[k]);
-          acc[cls][k] = fmaf(g, f[k], acc[cls][k]);
-        }
+        for (int cls = 0; cls < NC; ++cls) gv[u][cls] = (in && cls < ncls) ? dlogits[(n * ncls + cls) * HW + off] : 0.f;
       }
     }
-    reinterpret_cast<uint4*>(dy + p * 64)[cg] = pack8(o);
-  }
-  for (int cls = 0; cls < ncls; ++cls) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) atomicAdd(&s_dw[cls * 64 + cg * 8 + k], acc[cls][k]);
-    if (cg == 0) atomicAdd(&s_dw[8 * 64 + cls], accb[cls]);
+    for (int u = 0; u < 4; ++u) {
+      const size_t pu = p0 + u * pstride;
+      if (pu >= P) break;
+      float f[8], o[8];
+      unpack8(yv[u], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+#pragma unroll
+      for (int cls = 0; cls < NC; ++cls) {
+        if (cls < ncls) {
+          const float g = gv[u][cls];
+          accb[cls] += g;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            o[k] = fmaf(g, wv[cls][k], o[k]);
+            acc[cls][k] = fmaf(g, f[k], acc[cls][k]);
+          }
+        }
+      }
+      reinterpret_cast<uint4*>(dy + pu * 64)[cg] = pack8(o);
+    }
+  }
+#pragma unroll
+  for (int cls = 0; cls < NC; ++cls) {
+    if (cls < ncls) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) atomicAdd(&s_dw[cls * 64 + cg * 8 + k], acc[cls][k]);
+      if (cg == 0) atomicAdd(&s_dw[8 * 64 + cls], accb[cls]);
+    }
   }
   __syncthreads();
   for (int i = threadIdx.x; i < ncls * 64; i += blockDim.x) atomicAdd(&dw[i], s_dw[i]);
@@ -254,81 +323,77 @@ __global__ void __launch_bounds__(256) k_outconv_bwd(const float* __restrict__ d
 // ---------------------------------------------------------------------------------------------------------
 // BatchNorm + ReLU backward
 // ---------------------------------------------------------------------------------------------------------
-// sums[c] += sum_p dY~, sums[C + c] += sum_p dY~ xhat,  dY~ = dY [Y > 0],  xhat = (Z - mean) invstd.
-// Y > 0 is re-derived from Z with the forward pass's own expression (fmaf(z, scale, shift) > 0: bf16 rounding keeps the
-// sign), which saves reading Y.
+// part[block][c] = sum_p dY~, part[block][C + c] = sum_p dY~ xhat over the block's rows,  dY~ = dY [Y > 0],
+// xhat = (Z - mean) invstd.  Y > 0 is re-derived from Z with the forward pass's own expression
+// (fmaf(z, scale, shift) > 0: bf16 rounding keeps the sign), which saves reading Y.
 __global__ void __launch_bounds__(ST_THREADS) k_bn_bwd_reduce(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ scale,
                                                               const float* __restrict__ shift,
                                                               const __nv_bfloat16* __restrict__ z, size_t P, int C,
-                                                              const float* __restrict__ mean, const float* __restrict__ invstd, double* sums) {
+                                                              const float* __restrict__ mean, const float* __restrict__ invstd, double* part) {
   extern __shared__ double s_acc[];
   const int c8 = C / 8, tid = threadIdx.x;
-  const int lanes = ST_THREADS / c8 > 0 ? ST_THREADS / c8 : 1;
+  const int lanes = ST_THREADS / c8;
   for (int i = tid; i < 2 * C; i += ST_THREADS) s_acc[i] = 0.0;
   __syncthreads();
-  if (tid < lanes * c8) {
-    const int cg = tid % c8, rl = tid / c8;
-    double a[8], q[8];
-    float mu[8], is[8], sc[8], sh[8];
+  const int cg = tid % c8, rl = tid / c8;
+  double a[8], q[8];
+  float mu[8], is[8], sc[8], sh[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      a[k] = q[k] = 0.0;
-      mu[k] = mean[cg * 8 + k];
-      is[k] = invstd[cg * 8 + k];
-      sc[k] = scale[cg * 8 + k];
-      sh[k] = shift[cg * 8 + k];
+  for (int k = 0; k < 8; ++k) {
+    a[k] = q[k] = 0.0;
+    mu[k] = mean[cg * 8 + k];
+    is[k] = invstd[cg * 8 + k];
+    sc[k] = scale[cg * 8 + k];
+    sh[k] = shift[cg * 8 + k];
+  }
+  const size_t rstride = (size_t)gridDim.x * lanes;
+  for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
+    uint4 vg[4], vz[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const size_t ru = r + u * rstride;
+      const bool in = ru < P;
+      vg[u] = in ? *reinterpret_cast<const uint4*>(dy + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
+      vz[u] = in ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
     }
-    const size_t rstride = (size_t)gridDim.x * lanes;
-    for (size_t r = (size_t)blockIdx.x * lanes + rl; r < P; r += 4 * rstride) {
-      uint4 vg[4], vz[4];
+    float sa[8], sq[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const size_t ru = r + u * rstride;
-        const bool in = ru < P;
-        vg[u] = in ? *reinterpret_cast<const uint4*>(dy + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
-        vz[u] = in ? *reinterpret_cast<const uint4*>(z + ru * C + cg * 8) : make_uint4(0, 0, 0, 0);
-      }
-      float sa[8], sq[8];
+    for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) sa[k] = sq[k] = 0.f;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        float g[8], zz[8];
-        unpack8(vg[u], g);   // rows beyond P carry dY = 0 and add nothing
-        unpack8(vz[u], zz);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
-          sa[k] += gm;
-          sq[k] = fmaf(gm, (zz[k] - mu[k]) * is[k], sq[k]);
-        }
-      }
+    for (int u = 0; u < 4; ++u) {
+      float g[8], zz[8];
+      unpack8(vg[u], g);   // rows beyond P carry dY = 0 and add nothing
+      unpack8(vz[u], zz);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        a[k] += (double)sa[k];
-        q[k] += (double)sq[k];
+        const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
+        sa[k] += gm;
+        sq[k] = fmaf(gm, (zz[k] - mu[k]) * is[k], sq[k]);
       }
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      atomicAdd(&s_acc[cg * 8 + k], a[k]);
-      atomicAdd(&s_acc[C + cg * 8 + k], q[k]);
+      a[k] += (double)sa[k];
+      q[k] += (double)sq[k];
     }
   }
-  __syncthreads();
-  for (int i = tid; i < 2 * C; i += ST_THREADS) atomicAdd(&sums[i], s_acc[i]);
+  block_channel_sums(a, q, s_acc, C, c8, cg, part);
 }
 
-// dbeta, dgamma out (fp32) and the two per-channel terms of dZ
-__global__ void k_bn_bwd_finalize(const double* sums, int C, double n, const float* gamma, const float* invstd, float* dgamma,
-                                  float* dbeta, float* k_scale, float* k_mean_db, float* k_mean_dg) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+// dbeta, dgamma out (fp32) and the two per-channel terms of dZ.  One warp per channel.
+__global__ void __launch_bounds__(256) k_bn_bwd_finalize(const double* __restrict__ part, int nb, int C, double n, const float* gamma,
+                                                         const float* invstd, float* dgamma, float* dbeta, float* k_scale,
+                                                         float* k_mean_db, float* k_mean_dg) {
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
-  dbeta[c] = (float)sums[c];
-  dgamma[c] = (float)sums[C + c];
+  double s0, s1;
+  reduce_partials(part, nb, C, c, lane, s0, s1);
+  if (lane) return;
+  dbeta[c] = (float)s0;
+  dgamma[c] = (float)s1;
   k_scale[c] = gamma[c] * invstd[c];
-  k_mean_db[c] = (float)(sums[c] / n);
-  k_mean_dg[c] = (float)(sums[C + c] / n);
+  k_mean_db[c] = (float)(s0 / n);
+  k_mean_dg[c] = (float)(s1 / n);
 }
 
 __global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ scale,
@@ -712,6 +777,8 @@ const int kLevel[18] = {0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0};
 struct Shape { int H, W; };
 
 // Everything one forward/backward pair keeps in the workspace.
+constexpr int STAT_MAX_BLOCKS = 1184;  // rows of the partial-sum table (8 CTAs on each of 148 SMs)
+
 struct TrainBuffers {
   Shape lv[5];
   __nv_bfloat16* col;        // im2col of the input (64 channels)
@@ -721,7 +788,7 @@ struct TrainBuffers {
   __nv_bfloat16* up[4];      // up-sampled + padded low branch of up1..up4
   float* zero_shift;         // 1024 zeros
   float *mean[18], *var[18], *invstd[18], *scale[18], *shift[18];
-  double* sums;              // [2 * 1024]
+  double* part;              // [STAT_MAX_BLOCKS][2 * 1024] per-block partial sums of the BatchNorm reductions
   // backward scratch
   __nv_bfloat16* dy[18];     // gradient wrt y[i]
   __nv_bfloat16* dz;         // gradient wrt the current layer's z (largest layer)
@@ -756,7 +823,7 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   for (int i = 0; i < 4; ++i) b.pool[i] = c.take<__nv_bfloat16>(px(i + 1) * w->conv[2 * i + 1].cout);
   for (int j = 0; j < 4; ++j) b.up[j] = c.take<__nv_bfloat16>(px(3 - j) * w->conv[9 + 2 * j].cout);
   b.zero_shift = c.take<float>(1024);
-  b.sums = c.take<double>(2048);
+  b.part = c.take<double>((size_t)STAT_MAX_BLOCKS * 2048);
   b.dz = c.take<__nv_bfloat16>(max_act);
   b.dx = c.take<__nv_bfloat16>(max_in);
   b.dpool = c.take<__nv_bfloat16>(max_act);
@@ -765,6 +832,13 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   b.kdg = c.take<float>(1024);
   b.bytes = c.total();
   return b;
+}
+
+// CTAs of a BatchNorm reduction: eight per SM on the large layers, never fewer than 8 rows per thread
+int stat_blocks(size_t P, int C, int num_sms) {
+  const int lanes = ST_THREADS / (C / 8);
+  const size_t by_rows = (P + (size_t)lanes * 8 - 1) / ((size_t)lanes * 8);
+  return (int)std::max<size_t>(1, std::min<size_t>(by_rows, std::min<size_t>((size_t)num_sms * 8, STAT_MAX_BLOCKS)));
 }
 
 int ew_grid(size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)148 * 16); }
@@ -826,12 +900,10 @@ extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_n
     int r = unet::raw_conv(src0, c0, src1, c1, w->conv[i].w, C, taps, B, L.H, L.W, buf.zero_shift, buf.z[i], num_sms, stream);
     if (r != RDP_OK) return r;
     TRAIN_CHECKPOINT(stream, "forward conv %d (%dx%d, %d+%d -> %d channels)", i, L.H, L.W, c0, c1, C);
-    RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
-    const int lanes = std::max(1, ST_THREADS / (C / 8));
-    const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
-    k_bn_stats<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.z[i], P, C, buf.sums);
-    k_bn_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, w->conv[i].beta, eps, buf.mean[i], buf.var[i],
-                                                       buf.invstd[i], buf.scale[i], buf.shift[i]);
+    const int blocks = stat_blocks(P, C, num_sms);
+    k_bn_stats<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.z[i], P, C, buf.part);
+    k_bn_finalize<<<(C + 7) / 8, 256, 0, stream>>>(buf.part, blocks, C, (double)P, w->conv[i].gamma, w->conv[i].beta, eps, buf.mean[i], buf.var[i],
+                                                   buf.invstd[i], buf.scale[i], buf.shift[i]);
     k_bn_relu<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.z[i], P * C / 8, C / 8, buf.scale[i], buf.shift[i], buf.y[i]);
     TRAIN_CHECKPOINT(stream, "forward batch norm %d", i);
     if (stats && stats->mean[i]) RDP_CUDA_TRY(cudaMemcpyAsync(stats->mean[i], buf.mean[i], C * sizeof(float), cudaMemcpyDeviceToDevice, stream));
@@ -886,9 +958,16 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
   const size_t P0 = (size_t)B * H * W;
   RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_weight, 0, (size_t)w->n_classes * 64 * sizeof(float), stream));
   RDP_CUDA_TRY(cudaMemsetAsync(g->d_outc_bias, 0, (size_t)w->n_classes * sizeof(float), stream));
-  k_outconv_bwd<<<(int)std::min<size_t>((P0 + 31) / 32, (size_t)num_sms * 8), 256, 0, stream>>>(dlogits, buf.y[17], P0, (size_t)H * W, w->n_classes,
-                                                                                                  w->outc_weight, buf.dy[17], g->d_outc_weight,
-                                                                                                  g->d_outc_bias);
+  {
+    const int ob_grid = (int)std::min<size_t>((P0 + 127) / 128, (size_t)num_sms * 8);
+    const size_t HW0 = (size_t)H * W;
+    if (w->n_classes == 1)
+      k_outconv_bwd<1><<<ob_grid, 256, 0, stream>>>(dlogits, buf.y[17], P0, HW0, 1, w->outc_weight, buf.dy[17], g->d_outc_weight, g->d_outc_bias);
+    else if (w->n_classes <= 4)
+      k_outconv_bwd<4><<<ob_grid, 256, 0, stream>>>(dlogits, buf.y[17], P0, HW0, w->n_classes, w->outc_weight, buf.dy[17], g->d_outc_weight, g->d_outc_bias);
+    else
+      k_outconv_bwd<8><<<ob_grid, 256, 0, stream>>>(dlogits, buf.y[17], P0, HW0, w->n_classes, w->outc_weight, buf.dy[17], g->d_outc_weight, g->d_outc_bias);
+  }
 
   // the input of stage i as (src0[c0] ++ src1[c1]); what the gradient of that input feeds
   auto input_of = [&](int i, const __nv_bfloat16*& s0, int& c0, const __nv_bfloat16*& s1, int& c1) {
@@ -908,12 +987,10 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     const int C = w->conv[i].cout;
     const size_t P = (size_t)B * L.H * L.W;
     // ---- BatchNorm + ReLU backward: dgamma, dbeta, dz ----
-    RDP_CUDA_TRY(cudaMemsetAsync(buf.sums, 0, 2 * C * sizeof(double), stream));
-    const int lanes = std::max(1, ST_THREADS / (C / 8));
-    const int blocks = (int)std::min<size_t>((P + lanes - 1) / lanes, (size_t)num_sms * 8);
-    k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.sums);
-    k_bn_bwd_finalize<<<(C + 127) / 128, 128, 0, stream>>>(buf.sums, C, (double)P, w->conv[i].gamma, buf.invstd[i], g->dgamma[i], g->dbeta[i],
-                                                           buf.kscale, buf.kdb, buf.kdg);
+    const int blocks = stat_blocks(P, C, num_sms);
+    k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.part);
+    k_bn_bwd_finalize<<<(C + 7) / 8, 256, 0, stream>>>(buf.part, blocks, C, (double)P, w->conv[i].gamma, buf.invstd[i], g->dgamma[i], g->dbeta[i],
+                                                       buf.kscale, buf.kdb, buf.kdg);
     k_bn_bwd_apply<<<ew_grid(P * C / 8), 256, 0, stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P * C / 8, C / 8, buf.mean[i], buf.invstd[i], buf.kscale,
                                                            buf.kdb, buf.kdg, buf.dz);
     TRAIN_CHECKPOINT(stream, "backward batch norm %d", i);

@@ -1226,33 +1226,42 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
 // ---------------------------------------------------------------------------------------------------------
 // First layer: gather the 3x3xC neighbourhood of every pixel into 64 bf16 (k = (3*ky+kx)*C + c, zero padded),
 // so that inc.0 runs through the same tensor-core kernel as a 1x1 convolution with K = 64.
-__global__ void __launch_bounds__(256) k_im2col_first(const void* in, int in_fmt, int B, int H, int W, int C,
-                                                      __nv_bfloat16* out) {
-  const size_t total = (size_t)B * H * W * 8;  // 8 chunks of 8 values per pixel
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int chunk = (int)(i & 7);
-    size_t px = i >> 3;
-    const int x = (int)(px % W);
-    const int y = (int)((px / W) % H);
-    const int n = (int)(px / ((size_t)W * H));
-    __align__(16) __nv_bfloat16 v[8];
+// grid = (ceil(W*8 / 256), H, B); C is a template parameter so that k / C and k % C are multiplications.
+template <int C>
+__global__ void __launch_bounds__(256) k_im2col_first(const void* __restrict__ in, int in_fmt, int H, int W, __nv_bfloat16* __restrict__ out) {
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= W * 8) return;
+  const int chunk = t & 7, x = t >> 3, y = blockIdx.y, n = blockIdx.z;
+  __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int k = chunk * 8 + j;
-      float val = 0.f;
-      if (k < 9 * C) {
-        const int tap = k / C, c = k - tap * C;
-        const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
-        if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-          if (in_fmt == RDP_IN_RGB_U8_NHWC)
-            val = (float)((const uint8_t*)in)[(((size_t)n * H + yy) * W + xx) * C + c] / 255.0f;  // ToTensor
-          else
-            val = ((const float*)in)[(((size_t)n * C + c) * H + yy) * W + xx];
-        }
+  for (int j = 0; j < 8; ++j) {
+    const int k = chunk * 8 + j;
+    float val = 0.f;
+    if (k < 9 * C) {
+      const int tap = k / C, c = k - tap * C;
+      const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+        if (in_fmt == RDP_IN_RGB_U8_NHWC)
+          val = (float)__ldg((const uint8_t*)in + (((size_t)n * H + yy) * W + xx) * C + c) / 255.0f;  // ToTensor
+        else
+          val = __ldg((const float*)in + (((size_t)n * C + c) * H + yy) * W + xx);
       }
-      v[j] = __float2bfloat16_rn(val);
     }
-    *reinterpret_cast<uint4*>(out + px * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
+    v[j] = __float2bfloat16_rn(val);
+  }
+  *reinterpret_cast<uint4*>(out + (((size_t)n * H + y) * W + x) * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
+}
+
+static void launch_im2col_first(const void* in, int in_fmt, int B, int H, int W, int C, __nv_bfloat16* out, cudaStream_t stream) {
+  const dim3 grid((W * 8 + 255) / 256, H, B);
+  switch (C) {
+    case 1: k_im2col_first<1><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    case 2: k_im2col_first<2><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    case 3: k_im2col_first<3><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    case 4: k_im2col_first<4><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    case 5: k_im2col_first<5><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    case 6: k_im2col_first<6><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
+    default: k_im2col_first<7><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
   }
 }
 
@@ -1798,9 +1807,7 @@ int rdp::unet::raw_conv(const void* src0, int c0, const void* src1, int c1, cons
 }
 
 int rdp::unet::im2col_first(const void* in, int in_fmt, int B, int H, int W, int C, void* out, void* stream_) {
-  const size_t items = (size_t)B * H * W * 8;
-  k_im2col_first<<<(int)std::min<size_t>((items + 255) / 256, 148 * 16), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      in, in_fmt, B, H, W, C, static_cast<__nv_bfloat16*>(out));
+  launch_im2col_first(in, in_fmt, B, H, W, C, static_cast<__nv_bfloat16*>(out), static_cast<cudaStream_t>(stream_));
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
 }
@@ -1937,7 +1944,6 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
   // (measured, batch 64 at 640x480, pair vs two independent CTAs: down1.3 0.94 vs 1.19 ms, up3.3 0.59 vs 0.69, up4.0 2.34
   // vs 2.80, up4.3 1.40 vs 1.49; inc.3 and down1.0, one 64-channel block per tile, lose to the per-tile hand-shake)
   const char* sel = (sel_env && strlen(sel_env) == 18) ? sel_env : "1hhphhhhhhhhhhhppp";
-  auto ew_grid = [&](size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)net->num_sms * 16); };
   int n_marks = 0;
   auto mark = [&]() {
     if (marks) cudaEventRecord(marks[n_marks++], stream);
@@ -1972,8 +1978,7 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     }
   }
   if (!first_fused) {
-    const size_t items = (size_t)B * H * W * 8;
-    k_im2col_first<<<ew_grid(items), 256, 0, stream>>>(input, in_fmt, B, H, W, net->w.n_channels, buf.col);
+    launch_im2col_first(input, in_fmt, B, H, W, net->w.n_channels, buf.col, stream);
     mark();
   }
 
