@@ -583,7 +583,7 @@ struct WgradParams {
   int m_tiles, n_tiles, dys, ksplit, stages;
   int px_tiles, py_tiles;       // patches along x / y
   int first_layer;              // the input is the im2col'ed image: column k = tap * cin_real + c  ->  dW[co][c][tap]; one "tap"
-  float* dw;                    // fp32 [cout][cin_real][3][3]
+  float* dw;                    // fp32 scratch [9 * cin_real][cout] (k = tap * cin_real + ci), see k_dw_layout
 };
 
 template <int N>
@@ -698,15 +698,14 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
         tmem_ld_32x32(taddr + t * N + c * 32, r);
         tmem_ld_wait();
         if (row_ok) {
+          // scratch layout [k][co], k = tap * cin + ci (the first layer's im2col column is that k already): the lanes of
+          // a warp are consecutive co, so one warp-level reduction is one 128-byte line
+          const int k_lim = p.first_layer ? 9 * p.cin_real : p.cin_real;
+          float* dst = p.dw + (size_t)(p.first_layer ? 0 : tap * p.cin_real) * p.cout + co;
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int ci = nt * N + c * 32 + j;
-            const float v = __uint_as_float(r[j]);
-            if (p.first_layer) {
-              if (ci < 9 * p.cin_real) atomicAdd(&p.dw[((size_t)co * p.cin_real + ci % p.cin_real) * 9 + ci / p.cin_real], v);
-            } else if (ci < p.cin_real) {
-              atomicAdd(&p.dw[((size_t)co * p.cin_real + ci) * 9 + tap], v);
-            }
+            if (ci < k_lim) atomicAdd(dst + (size_t)ci * p.cout, __uint_as_float(r[j]));
           }
         }
       }
@@ -717,6 +716,26 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// scratch [9 * cin][cout] (what the GEMM epilogue can add to with coalesced reductions) -> the parameter's layout
+// [cout][cin][3][3].  A block moves 32 output channels x 32 input channels x 9 taps through shared memory so that both
+// sides are contiguous.  grid = (ceil(cin / 32), ceil(cout / 32)).
+__global__ void __launch_bounds__(256) k_dw_layout(const float* __restrict__ src, int cin, int cout, float* __restrict__ dst) {
+  __shared__ float tile[32][9 * 32 + 1];  // [co][ci * 9 + tap]
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  for (int r = w; r < 9 * 32; r += 8) {  // r = tap * 32 + ci
+    const int tap = r >> 5, ci = ci0 + (r & 31), co = co0 + lane;
+    if (ci < cin && co < cout) tile[lane][(r & 31) * 9 + tap] = src[((size_t)tap * cin + ci) * cout + co];
+  }
+  __syncthreads();
+  const int span = min(32, cin - ci0) * 9;
+  for (int r = w; r < 32; r += 8) {
+    const int co = co0 + r;
+    if (co >= cout) break;
+    for (int e = lane; e < span; e += 32) dst[((size_t)co * cin + ci0) * 9 + e] = tile[r][e];
   }
 }
 
@@ -795,6 +814,7 @@ struct TrainBuffers {
   __nv_bfloat16* dx;         // gradient wrt the current layer's (concatenated) input
   __nv_bfloat16* dpool;      // gradient wrt a pooled tensor (alias of dx is not possible: both live)
   float *kscale, *kdb, *kdg;  // [1024] each
+  float* dws;                 // weight-gradient scratch of the current layer, [9 * cin][cout]
   size_t bytes;
 };
 
@@ -805,7 +825,7 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   Carver c(ws);
   auto px = [&](int l) { return (size_t)B * b.lv[l].H * b.lv[l].W; };
   b.col = c.take<__nv_bfloat16>(px(0) * 64);
-  size_t max_act = 0, max_in = 0;
+  size_t max_act = 0, max_in = 0, max_w = 0;
   for (int i = 0; i < 18; ++i) {
     const size_t n = px(kLevel[i]) * w->conv[i].cout;
     b.z[i] = c.take<__nv_bfloat16>(n);
@@ -814,6 +834,7 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
     max_act = std::max(max_act, n);
     const int cin_pad = i == 0 ? 64 : (w->conv[i].cin + 63) / 64 * 64;
     max_in = std::max(max_in, px(kLevel[i]) * cin_pad);
+    max_w = std::max(max_w, (size_t)9 * w->conv[i].cin * w->conv[i].cout);
     b.mean[i] = c.take<float>(w->conv[i].cout);
     b.var[i] = c.take<float>(w->conv[i].cout);
     b.invstd[i] = c.take<float>(w->conv[i].cout);
@@ -830,6 +851,7 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   b.kscale = c.take<float>(1024);
   b.kdb = c.take<float>(1024);
   b.kdg = c.take<float>(1024);
+  b.dws = c.take<float>(max_w);
   b.bytes = c.total();
   return b;
 }
@@ -999,7 +1021,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     int c0, c1;
     input_of(i, s0, c0, s1, c1);
     const int cin_pad = c0 + c1, cin_real = w->conv[i].cin;
-    RDP_CUDA_TRY(cudaMemsetAsync(g->dw[i], 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
+    RDP_CUDA_TRY(cudaMemsetAsync(buf.dws, 0, (size_t)C * cin_real * 9 * sizeof(float), stream));
     {
       WgradParams wp{};
       wp.B = B; wp.H = L.H; wp.W = L.W;
@@ -1015,7 +1037,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       const int items = wp.m_tiles * wp.n_tiles * wp.dys;
       wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches));   // two full waves, one CTA per SM
       wp.first_layer = i == 0;
-      wp.dw = g->dw[i];
+      wp.dw = buf.dws;
       CUtensorMap mz, mx0, mx1;
       RDP_TRY(make_nhwc_map(&mz, buf.dz, B, L.H, L.W, C, WG_PW));
       RDP_TRY(make_nhwc_map(&mx0, s0, B, L.H, L.W, c0, WG_HALO_W));
@@ -1023,6 +1045,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       else mx1 = mx0;
       if (n_tile == 64) RDP_TRY(launch_wgrad_t<64>(mz, mx0, mx1, wp, stream));
       else RDP_TRY(launch_wgrad_t<128>(mz, mx0, mx1, wp, stream));
+      k_dw_layout<<<dim3((cin_real + 31) / 32, (C + 31) / 32), 256, 0, stream>>>(buf.dws, cin_real, C, g->dw[i]);
     }
     TRAIN_CHECKPOINT(stream, "weight gradient %d (%dx%d, %d x %d)", i, L.H, L.W, C, cin_pad);
     if (i == 0) break;  // the image needs no gradient
