@@ -6,15 +6,15 @@
 //
 // Data: activations NHWC bf16 as in the inference path, gradients of activations bf16, parameter gradients fp32,
 // batch statistics accumulated in fp64.  Per 3x3 conv + BatchNorm + ReLU stage i, forward
-//     Z_i = conv(X_i, W_i)            k_conv3x3<BN, RAW> (tcgen05 implicit GEMM, csrc/unet.cu)
-//     mu, var = stats(Z_i)            k_bn_stats      per-channel sum and sum of squares over B*H*W
+//     Z_i = conv(X_i, W_i)            k_conv3x3_halo<.., RAW> (tcgen05 implicit GEMM, csrc/unet.cu)
+//     mu, var = stats(Z_i)            k_bn_stats + k_bn_finalize   per-channel sum and sum of squares over B*H*W
 //     Y_i = relu(g (Z_i - mu)/sqrt(var + eps) + b)     k_bn_relu
 // and backward, given dY_i,
-//     dbeta, dgamma                   k_bn_bwd_reduce (dY masked by Y > 0)
+//     dbeta, dgamma                   k_bn_bwd_reduce + k_bn_bwd_finalize (dY masked by Y > 0, re-derived from Z)
 //     dZ_i = g/sigma (dY~ - dbeta/n - xhat dgamma/n)   k_bn_bwd_apply
-//     dW_i = sum_p dZ_i[p] (x) X_i[p + tap]            k_wgrad: tcgen05 GEMM with K = the pixels (both operands transposed to
-//                                                      pixel-major by k_transpose so that K is contiguous for TMA / UMMA)
-//     dX_i = conv(dZ_i, W_i flipped and transposed)    k_conv3x3<BN, RAW> again
+//     dW_i = sum_p dZ_i[p] (x) X_i[p + tap]            k_wgrad: tcgen05 GEMM with K = the pixels, both operands read in place
+//                                                      from the NHWC tensors as MN-major operands; k_dw_layout
+//     dX_i = conv(dZ_i, W_i flipped and transposed)    k_conv3x3_halo<.., RAW> again
 // plus the adjoints of MaxPool2d(2) (first maximum wins, like ATen), of the bilinear x2 up-sampling with its pad, of the
 // channel concatenation, and the 1x1 OutConv in both directions.
 #include <cuda.h>
