@@ -152,7 +152,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if (remote_empty) mbar_arrive_cluster(remote_empty);
+        if (remote_empty) mbar_arrive_remote(remote_empty);
         else mbar_arrive(acc_empty_bar);
       }
     }
@@ -234,7 +234,7 @@ __device__ __forceinline__ void epilogue_tile(const ConvParams& p, const float* 
     tc_fence_before();
     __syncwarp();
     if (lane == 0) {
-      if (remote_empty) mbar_arrive_cluster(remote_empty);
+      if (remote_empty) mbar_arrive_remote(remote_empty);
       else mbar_arrive(acc_empty_bar);
     }
   }
@@ -892,8 +892,9 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       constexpr uint32_t hi_a = desc_hi(HW * 128), hi_b = desc_hi(1024);
       uint32_t sa = 0, pa = 0, sb = 0, pb = 0, aphase = 0;
       const uint32_t a_lo0 = desc_lo(smem_u32(smem_a)), b_lo0 = desc_lo(smem_u32(smem_b));
+      RDP_DEV(long long w_acc = 0, w_a = 0, t_begin = clock64(), t0;)
       if (RESIDENT) {
-        mbar_wait_cluster(w_full, 0);
+        mbar_wait(w_full, 0);
         tc_fence_after();
       }
       int work = pair;
@@ -901,16 +902,21 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
 #pragma unroll
         for (int as = 0; as < NACC; ++as) {
           if (work < pair_work) {
-            mbar_wait_cluster(&acc_empty[as], aphase ^ 1);
+            RDP_DEV(t0 = clock64();)
+            mbar_wait(&acc_empty[as], aphase ^ 1);   // a drained tensor-memory stage: no memory to acquire
+            RDP_DEV(w_acc += clock64() - t0;)
             tc_fence_after();
             const uint32_t tmem_acc = tmem_base + as * BN;
             for (int cb = 0; cb < ncb; ++cb) {
-              mbar_wait_cluster(&full_a[sa], pa);
+              RDP_DEV(t0 = clock64();)
+              if (INTERP) mbar_wait_cluster(&full_a[sa], pa);   // the peer's interpolation warps wrote its block with ordinary stores
+              else mbar_wait(&full_a[sa], pa);                   // TMA completions only
+              RDP_DEV(w_a += clock64() - t0;)
               tc_fence_after();
               const uint32_t a_lo = a_lo0 + sa * (HALO_STRIDE >> 4);
               uint32_t bres_lo = b_lo0 + cb * (9 * B_HALF >> 4);
               if (!RESIDENT) {
-                mbar_wait_cluster(&full_b[sb], pb);
+                mbar_wait(&full_b[sb], pb);
                 tc_fence_after();
                 bres_lo = b_lo0 + sb * (9 * B_HALF >> 4);
               }
@@ -935,6 +941,8 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
         }
         aphase ^= 1;
       }
+      RDP_DEV(if (p.debug_waits && blockIdx.x == 0 && (threadIdx.x & 31) == 0)
+        printf("  pair mma thread: total %lld cyc, waiting acc_empty %lld, full_a %lld (BN %d resident %d)\n", clock64() - t_begin, w_acc, w_a, BN, (int)RESIDENT);)
     }
   } else if (INTERP && warp >= 2 + 4 * epi_groups(BN, INTERP)) {
     // ================= interpolation producers: halo blocks of the up-sampled branch, each CTA its own tile =================
@@ -977,6 +985,7 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     int it = 0;
+    RDP_DEV(long long epi_wait = 0; const long long epi_begin = clock64();)
     for (int work = pair; work < pair_work; work += n_pairs, ++it) {
       if (EG > 1 && (it % EG) != group) continue;
       const uint32_t as = it % NACC, aphase = (it / NACC) & 1;
@@ -985,11 +994,15 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
       const bool real = n < p.B;
       const int y = real ? ty * 16 + (row >> 3) : p.H + 16, x = tx * 8 + (row & 7);
       const bool inside = y < p.H && x < p.W;
+      RDP_DEV(const long long e0 = clock64();)
       mbar_wait(&acc_full[as], aphase);
+      RDP_DEV(epi_wait += clock64() - e0;)
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(quarter * 32) << 16);
       epilogue_tile<BN, true>(p, s_aux, taddr, 0, real ? n : 0, y, x, inside, nullptr, lane, mapa_u32(smem_u32(&acc_empty[as]), 0));
     }
+    RDP_DEV(if (p.debug_waits && blockIdx.x < 2 && threadIdx.x == 64)
+      printf("  pair epilogue warp (rank %u): total %lld cyc, waiting acc_full %lld\n", rank, clock64() - epi_begin, epi_wait);)
   }
 
   tc_fence_before();
