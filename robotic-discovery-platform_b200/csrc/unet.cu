@@ -1396,6 +1396,93 @@ __global__ void __launch_bounds__(256) k_upsample2x_row(const __nv_bfloat16* __r
   }
 }
 
+// Fast path of the stand-alone interpolation for the exact doubling without pad (Hs = 2h, Ws = 2w: every level of an
+// image whose sides divide by 16).  With align_corners the output rows 2k-1 and 2k read the same two source rows k-1 and
+// k, and likewise the columns: a thread produces that 2x2 block of output pixels for one 8-channel group from FOUR
+// loads and one conversion of each (the row kernel above loads and converts four source pixels per output pixel, and
+// is bound by instruction issue).  Indices and weights still come from the same fp32 expressions per output row and
+// column, and a block whose outputs do not share their sources (the first and last row / column) falls back to
+// per-output loads, so the results are those of k_upsample2x bit for bit.
+// grid = (ceil((w+1)*C8 / 256), ceil((h+1) / UQ_ROWS), B); thread = (column pair j = 0..w, channel group).
+constexpr int UQ_ROWS = 4;
+struct UpsAxis { int i0, i1; float l0, l1; };
+__device__ __forceinline__ UpsAxis ups_axis(float r, int o, int n) {
+  UpsAxis a;
+  const float f = r * (float)o;
+  a.i0 = (int)f;
+  a.i1 = a.i0 + (a.i0 < n - 1 ? 1 : 0);
+  a.l1 = f - (float)a.i0;
+  a.l0 = 1.f - a.l1;
+  return a;
+}
+__device__ __forceinline__ void bf16x8_to_f32(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__global__ void __launch_bounds__(256) k_upsample2x_quad(const __nv_bfloat16* __restrict__ in, int h, int w, int C8, int c8_shift,
+                                                         float ry, float rx, __nv_bfloat16* __restrict__ out) {
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t >= (w + 1) * C8) return;
+  const int j = t >> c8_shift, c8 = t & (C8 - 1), n = blockIdx.z;
+  const int Ho = 2 * h, Wo = 2 * w;
+  const int xa = 2 * j - 1, xb = 2 * j;
+  const bool va = xa >= 0, vb = xb < Wo;
+  const UpsAxis ca = ups_axis(rx, va ? xa : xb, w), cb = ups_axis(rx, vb ? xb : xa, w);
+  const bool same_c = ca.i0 == cb.i0 && ca.i1 == cb.i1;
+  const uint4* src = reinterpret_cast<const uint4*>(in) + (size_t)n * h * w * C8 + c8;
+  uint4* dst = reinterpret_cast<uint4*>(out) + (size_t)n * Ho * Wo * C8 + c8;
+  auto emit = [&](const float (&top0)[8], const float (&top1)[8], const float (&bot0)[8], const float (&bot1)[8], const UpsAxis& r,
+                  const UpsAxis& c, int yo, int xo) {
+    uint4 o;
+    __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float r0 = r.l0 * (c.l0 * top0[2 * q] + c.l1 * top1[2 * q]) + r.l1 * (c.l0 * bot0[2 * q] + c.l1 * bot1[2 * q]);
+      const float r1 = r.l0 * (c.l0 * top0[2 * q + 1] + c.l1 * top1[2 * q + 1]) + r.l1 * (c.l0 * bot0[2 * q + 1] + c.l1 * bot1[2 * q + 1]);
+      po[q] = __floats2bfloat162_rn(r0, r1);
+    }
+    dst[((size_t)yo * Wo + xo) * C8] = o;
+  };
+  auto generic = [&](const UpsAxis& r, const UpsAxis& c, int yo, int xo) {
+    float a[8], b[8], cc[8], d[8];
+    bf16x8_to_f32(__ldg(src + ((size_t)r.i0 * w + c.i0) * C8), a);
+    bf16x8_to_f32(__ldg(src + ((size_t)r.i0 * w + c.i1) * C8), b);
+    bf16x8_to_f32(__ldg(src + ((size_t)r.i1 * w + c.i0) * C8), cc);
+    bf16x8_to_f32(__ldg(src + ((size_t)r.i1 * w + c.i1) * C8), d);
+    emit(a, b, cc, d, r, c, yo, xo);
+  };
+#pragma unroll 1
+  for (int k = blockIdx.y * UQ_ROWS; k < min(h + 1, (blockIdx.y + 1) * UQ_ROWS); ++k) {
+    const int ya = 2 * k - 1, yb = 2 * k;
+    const bool ua = ya >= 0, ub = yb < Ho;
+    const UpsAxis ra = ups_axis(ry, ua ? ya : yb, h), rb = ups_axis(ry, ub ? yb : ya, h);
+    const bool same_r = ra.i0 == rb.i0 && ra.i1 == rb.i1;
+    if (same_r && same_c) {
+      float v00[8], v01[8], v10[8], v11[8];
+      const uint4 q00 = __ldg(src + ((size_t)ra.i0 * w + ca.i0) * C8), q01 = __ldg(src + ((size_t)ra.i0 * w + ca.i1) * C8);
+      const uint4 q10 = __ldg(src + ((size_t)ra.i1 * w + ca.i0) * C8), q11 = __ldg(src + ((size_t)ra.i1 * w + ca.i1) * C8);
+      bf16x8_to_f32(q00, v00);
+      bf16x8_to_f32(q01, v01);
+      bf16x8_to_f32(q10, v10);
+      bf16x8_to_f32(q11, v11);
+      if (ua && va) emit(v00, v01, v10, v11, ra, ca, ya, xa);
+      if (ua && vb) emit(v00, v01, v10, v11, ra, cb, ya, xb);
+      if (ub && va) emit(v00, v01, v10, v11, rb, ca, yb, xa);
+      if (ub && vb) emit(v00, v01, v10, v11, rb, cb, yb, xb);
+    } else {
+      if (ua && va) generic(ra, ca, ya, xa);
+      if (ua && vb) generic(ra, cb, ya, xb);
+      if (ub && va) generic(rb, ca, yb, xa);
+      if (ub && vb) generic(rb, cb, yb, xb);
+    }
+  }
+}
+
 // NHWC bf16 -> NCHW fp32 (parity hook, not on the hot path)
 __global__ void k_nhwc_to_nchw_f32(const __nv_bfloat16* in, int B, int H, int W, int C, float* out) {
   const size_t total = (size_t)B * C * H * W;
@@ -1834,9 +1921,15 @@ int rdp::unet::maxpool2(const void* in, int B, int H, int W, int C, void* out, v
 }
 
 int rdp::unet::upsample2x(const void* in, int B, int h, int w, int C, int Hs, int Ws, void* out, void* stream_) {
-  const int C8 = C / 8, dy = Hs - 2 * h, dx = Ws - 2 * w;
-  k_upsample2x<<<dim3((Ws * C8 + 255) / 256, Hs, B), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      static_cast<const __nv_bfloat16*>(in), h, w, C8, log2_exact(C8), Hs, Ws, dy / 2, dx / 2, static_cast<__nv_bfloat16*>(out));
+  const int C8 = C / 8, dy = Hs - 2 * h, dx = Ws - 2 * w, sh = log2_exact(C8);
+  if (sh >= 0 && dy == 0 && dx == 0 && h > 1 && w > 1) {
+    const float ry = (float)(h - 1) / (float)(2 * h - 1), rx = (float)(w - 1) / (float)(2 * w - 1);
+    k_upsample2x_quad<<<dim3(((w + 1) * C8 + 255) / 256, (h + 1 + UQ_ROWS - 1) / UQ_ROWS, B), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        static_cast<const __nv_bfloat16*>(in), h, w, C8, sh, ry, rx, static_cast<__nv_bfloat16*>(out));
+  } else {
+    k_upsample2x<<<dim3((Ws * C8 + 255) / 256, Hs, B), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        static_cast<const __nv_bfloat16*>(in), h, w, C8, sh, Hs, Ws, dy / 2, dx / 2, static_cast<__nv_bfloat16*>(out));
+  }
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
 }
@@ -2113,7 +2206,12 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
     } else {
       static const bool ups_v1 = dev_env("RDP_UPSAMPLE_V1") != nullptr;  // the one-output-per-thread kernel (A/B, cross-check)
       const int sh = log2_exact(C8);
-      if (ups_v1 || sh < 0 || C8 > 256) {
+      static const bool ups_row = dev_env("RDP_UPSAMPLE_ROW") != nullptr;  // the kernel before the 2x2-block one (A/B, cross-check)
+      if (!ups_v1 && !ups_row && sh >= 0 && dy == 0 && dx == 0 && Ls.H == 2 * Ll.H && Ls.W == 2 * Ll.W && Ll.H > 1 && Ll.W > 1) {
+        const float ry = (float)(Ll.H - 1) / (float)(2 * Ll.H - 1), rx = (float)(Ll.W - 1) / (float)(2 * Ll.W - 1);
+        k_upsample2x_quad<<<dim3(((Ll.W + 1) * C8 + 255) / 256, (Ll.H + 1 + UQ_ROWS - 1) / UQ_ROWS, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, sh,
+                                                                                                                       ry, rx, buf.up[j]);
+      } else if (ups_v1 || sh < 0 || C8 > 256) {
         k_upsample2x<<<dim3((Ls.W * C8 + 255) / 256, Ls.H, B), 256, 0, stream>>>(buf.act[low_i], Ll.H, Ll.W, C8, sh, Ls.H, Ls.W, dy / 2, dx / 2, buf.up[j]);
       } else {
         const int Ho = 2 * Ll.H, Wo = 2 * Ll.W;
