@@ -297,6 +297,10 @@ typedef struct {  /* parameter gradients (device, fp32), each overwritten by the
   float* d_outc_bias;   /* [n_classes] */
 } RdpTrainGrads;
 
+/* Conv2d.weight as the optimiser holds it (fp32 [cout][cin][3][3], pkg/segmentation_model.py:26-33) -> the two bf16
+ * layouts above, once per step after the optimiser's update.  first_layer: w is [cout][64]; w_t may be NULL. */
+int rdp_unet_train_pack(const float* w_oihw, int cout, int cin, int first_layer, void* w, void* w_t, void* stream);
+
 /* H and W must be divisible by 16 (the reference trains at 256 x 256, train_segmenter.py:49). */
 int rdp_unet_train_workspace_bytes(const RdpTrainWeights* w, int B, int H, int W, size_t* bytes);
 

@@ -719,6 +719,26 @@ k_wgrad(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUte
   }
 }
 
+// Conv2d.weight fp32 [cout][cin][3][3] -> the two bf16 operand layouts of RdpTrainLayer: w [cout][tap][cin] (first layer:
+// [cout][64] with k = tap * cin + c, zero padded) and w_t [cin][8 - tap][cout] (the flipped, transposed kernel of the
+// input gradient).  One thread per weight; a block of the first layer also clears that layer's padding columns.
+__global__ void __launch_bounds__(256) k_pack_train_weights(const float* __restrict__ w, int cout, int cin, int first,
+                                                            __nv_bfloat16* __restrict__ fwd, __nv_bfloat16* __restrict__ wt) {
+  const int total = cout * cin * 9;
+  const int e = blockIdx.x * 256 + threadIdx.x;
+  if (e < total) {
+    const int co = e / (cin * 9), rem = e - co * cin * 9, ci = rem / 9, tap = rem - ci * 9;
+    const __nv_bfloat16 v = __float2bfloat16_rn(w[e]);
+    if (first) fwd[co * 64 + tap * cin + ci] = v;
+    else fwd[((size_t)co * 9 + tap) * cin + ci] = v;
+    if (wt) wt[((size_t)ci * 9 + (8 - tap)) * cout + co] = v;
+  }
+  if (first) {
+    const int pad = 64 - 9 * cin;
+    for (int i = e; i < cout * pad; i += gridDim.x * 256) fwd[(i / pad) * 64 + 9 * cin + i % pad] = __float2bfloat16_rn(0.f);
+  }
+}
+
 // scratch [9 * cin][cout] (what the GEMM epilogue can add to with coalesced reductions) -> the parameter's layout
 // [cout][cin][3][3].  A block moves 32 output channels x 32 input channels x 9 taps through shared memory so that both
 // sides are contiguous.  grid = (ceil(cin / 32), ceil(cout / 32)).
@@ -889,6 +909,17 @@ extern "C" int rdp_debug_timeouts(int* out8) {  // development builds only: firs
   return cudaMemcpyFromSymbol(out8, rdp::ptx::g_rdp_timeout, 8 * sizeof(int)) == cudaSuccess ? 0 : -3;
 }
 #endif
+
+extern "C" int rdp_unet_train_pack(const float* w_oihw, int cout, int cin, int first_layer, void* w, void* w_t, void* stream_) {
+  RDP_REQUIRE(w_oihw && w && cout > 0 && cin > 0, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_pack: null pointer or empty layer");
+  RDP_REQUIRE(!first_layer || 9 * cin <= 64, RDP_ERR_UNSUPPORTED, "rdp_unet_train_pack: first layer with %d channels (9*C must be <= 64)", cin);
+  RDP_REQUIRE(first_layer || w_t, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_pack: w_t is required for every layer but the first");
+  const int total = cout * cin * 9;
+  k_pack_train_weights<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      w_oihw, cout, cin, first_layer ? 1 : 0, static_cast<__nv_bfloat16*>(w), first_layer ? nullptr : static_cast<__nv_bfloat16*>(w_t));
+  RDP_CUDA_TRY(cudaGetLastError());
+  return RDP_OK;
+}
 
 extern "C" int rdp_unet_train_workspace_bytes(const RdpTrainWeights* w, int B, int H, int W, size_t* bytes) {
   RDP_REQUIRE(bytes, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_workspace_bytes: null argument");

@@ -24,7 +24,7 @@ EXPORTS = [
     "rdp_geom_deproject_static",
     "rdp_pre_resize", "rdp_post_mask_nearest", "rdp_post_mask_png_sizes", "rdp_post_mask_png",
     "rdp_pre_decode_sizes", "rdp_pre_decode_jpeg", "rdp_pre_decode_png16",
-    "rdp_unet_train_workspace_bytes", "rdp_unet_train_forward", "rdp_unet_train_backward",
+    "rdp_unet_train_pack", "rdp_unet_train_workspace_bytes", "rdp_unet_train_forward", "rdp_unet_train_backward",
 ]
 
 

@@ -43,7 +43,8 @@ def _bind(lib):
                                            C.POINTER(TrainBatchStats), C.c_void_p, C.c_size_t, C.c_void_p]
     lib.rdp_unet_train_backward.argtypes = [C.POINTER(TrainWeights), C.c_void_p, C.c_int, C.c_int, C.c_int,
                                             C.POINTER(TrainGrads), C.c_void_p, C.c_size_t, C.c_void_p]
-    for n in ("rdp_unet_train_workspace_bytes", "rdp_unet_train_forward", "rdp_unet_train_backward"):
+    lib.rdp_unet_train_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    for n in ("rdp_unet_train_pack", "rdp_unet_train_workspace_bytes", "rdp_unet_train_forward", "rdp_unet_train_backward"):
         getattr(lib, n).restype = C.c_int
     lib._rdp_train_bound = True
 
@@ -66,6 +67,23 @@ def pack_for_training(params: dict, n_channels: int):
     return ws, wts
 
 
+_LEVEL = [0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0]
+
+
+def _packed_buffers(model, dev, table):
+    """bf16 operand buffers of the 18 convolutions, allocated once per (model, device) and refilled every step by
+    `rdp_unet_train_pack` (the optimiser changes the fp32 parameters in place between steps)."""
+    cache = model.__dict__.setdefault("_rdp_train_buffers", {})
+    key = (dev.type, dev.index)
+    if key not in cache:
+        ws, wts = [], []
+        for i, (_, _, cin, cout) in enumerate(table):
+            ws.append(torch.empty((cout, 64) if i == 0 else (cout, 9, cin), dtype=torch.bfloat16, device=dev))
+            wts.append(None if i == 0 else torch.empty((cin, 9, cout), dtype=torch.bfloat16, device=dev))
+        cache[key] = (ws, wts)
+    return cache[key]
+
+
 class _TrainStep(torch.autograd.Function):
     """One autograd node for the whole network: inputs are the image batch and every parameter (in
     `unet_layer_table` order: conv weight, BN weight, BN bias per stage, then OutConv weight and bias)."""
@@ -85,7 +103,12 @@ class _TrainStep(torch.autograd.Function):
         ow, ob = params[k], params[k + 1]
         B, _, H, W = x.shape
         with torch.cuda.device(dev):
-            ws, wts = pack_for_training(named, n_channels)
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            ws, wts = _packed_buffers(model, dev, table)
+            for i, (conv, _, cin, cout) in enumerate(table):
+                w32 = named[f"{conv}.weight"].detach().float().contiguous()
+                _lib.check(lib.rdp_unet_train_pack(w32.data_ptr(), cout, cin, int(i == 0), ws[i].data_ptr(),
+                                                   wts[i].data_ptr() if wts[i] is not None else None, stream), "rdp_unet_train_pack")
             gam = [named[f"{bn}.weight"].detach().float().contiguous() for _, bn, _, _ in table]
             bet = [named[f"{bn}.bias"].detach().float().contiguous() for _, bn, _, _ in table]
             owc = ow.detach().float().reshape(n_classes, 64).contiguous()
@@ -101,24 +124,27 @@ class _TrainStep(torch.autograd.Function):
             _lib.check(lib.rdp_unet_train_workspace_bytes(C.byref(desc), B, H, W, C.byref(need)), "rdp_unet_train_workspace_bytes")
             wsp = torch.empty(need.value, dtype=torch.uint8, device=dev)
             logits = torch.empty((B, n_classes, H, W), dtype=torch.float32, device=dev)
-            means = [torch.empty(cout, dtype=torch.float32, device=dev) for _, _, _, cout in table]
-            vars_ = [torch.empty(cout, dtype=torch.float32, device=dev) for _, _, _, cout in table]
+            couts = [cout for _, _, _, cout in table]
+            stats = torch.empty(2 * sum(couts), dtype=torch.float32, device=dev)
+            means = list(stats[: sum(couts)].split(couts))
+            vars_ = list(stats[sum(couts):].split(couts))
             st = TrainBatchStats()
             for i in range(18):
                 st.mean[i], st.var_biased[i] = means[i].data_ptr(), vars_[i].data_ptr()
             xin = x.detach().float().contiguous()
-            stream = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(lib.rdp_unet_train_forward(C.byref(desc), xin.data_ptr(), B, H, W, logits.data_ptr(), C.byref(st),
                                                   wsp.data_ptr(), wsp.numel(), stream), "rdp_unet_train_forward")
             # running statistics, as nn.BatchNorm2d updates them in train mode (momentum 0.1, unbiased variance)
             n = B * H * W
             with torch.no_grad():
-                for i, (_, bn, _, _) in enumerate(table):
-                    mod = model.get_submodule(bn)
-                    ni = n >> (2 * [0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 3, 3, 2, 2, 1, 1, 0, 0][i])
-                    mod.running_mean.mul_(0.9).add_(means[i], alpha=0.1)
-                    mod.running_var.mul_(0.9).add_(vars_[i] * (ni / max(ni - 1, 1)), alpha=0.1)
-                    mod.num_batches_tracked += 1
+                mods = [model.get_submodule(bn) for _, bn, _, _ in table]
+                rm, rv = [m.running_mean for m in mods], [m.running_var for m in mods]
+                unbias = [0.1 * ni / max(ni - 1, 1) for ni in (n >> (2 * _LEVEL[i]) for i in range(18))]
+                torch._foreach_mul_(rm, 0.9)
+                torch._foreach_add_(rm, means, alpha=0.1)
+                torch._foreach_mul_(rv, 0.9)
+                torch._foreach_add_(rv, torch._foreach_mul(vars_, unbias))
+                torch._foreach_add_([m.num_batches_tracked for m in mods], 1)
         ctx.keep = (desc, ws, wts, gam, bet, owc, obc, wsp, xin)
         ctx.shape = (B, H, W, n_channels, n_classes)
         ctx.param_shapes = [p.shape for p in params]
@@ -133,11 +159,12 @@ class _TrainStep(torch.autograd.Function):
         table = unet_layer_table(n_channels)
         with torch.cuda.device(dev):
             g = TrainGrads()
-            dws, dgs, dbs = [], [], []
+            couts = [cout for _, _, _, cout in table]
+            small = torch.empty(2 * sum(couts), dtype=torch.float32, device=dev)
+            dgs, dbs = list(small[: sum(couts)].split(couts)), list(small[sum(couts):].split(couts))
+            dws = []
             for i, (_, _, cin, cout) in enumerate(table):
                 dws.append(torch.empty((cout, cin, 3, 3), dtype=torch.float32, device=dev))
-                dgs.append(torch.empty(cout, dtype=torch.float32, device=dev))
-                dbs.append(torch.empty(cout, dtype=torch.float32, device=dev))
                 g.dw[i], g.dgamma[i], g.dbeta[i] = dws[i].data_ptr(), dgs[i].data_ptr(), dbs[i].data_ptr()
             dow = torch.empty((n_classes, 64), dtype=torch.float32, device=dev)
             dob = torch.empty(n_classes, dtype=torch.float32, device=dev)
