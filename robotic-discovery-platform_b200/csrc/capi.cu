@@ -15,5 +15,5 @@ void set_error(const char* fmt, ...) {
 }
 }  // namespace rdp
 
-extern "C" int rdp_abi_version(void) { return 2; }
+extern "C" int rdp_abi_version(void) { return 3; }
 extern "C" const char* rdp_last_error(void) { return rdp::g_error; }

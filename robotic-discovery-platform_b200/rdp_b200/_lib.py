@@ -14,7 +14,7 @@ DEPTH_U16, DEPTH_F32, DEPTH_F32_WIDE, DEPTH_F64 = 0, 1, 2, 3
 IN_RGB_U8_NHWC, IN_F32_NCHW = 0, 1
 IN_FLAG_KEEP_ACTIVATIONS = 0x100
 FIT_FLAG_KNOT_TIE, FIT_FLAG_BRACKET_TIE, FIT_FLAG_NPLUS_TIE = 1, 2, 4
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 EXPORTS = [
     "rdp_abi_version", "rdp_last_error",

@@ -18,7 +18,7 @@ def test_library_exports_match_header():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in include/rdp_b200.h but not exported"
     assert declared == set(_lib.EXPORTS)
-    assert lib.rdp_abi_version() == _lib.ABI_VERSION == 2
+    assert lib.rdp_abi_version() == _lib.ABI_VERSION == 3
 
 
 def test_argument_errors_without_gpu():
