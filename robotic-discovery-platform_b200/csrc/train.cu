@@ -111,7 +111,16 @@ __device__ __forceinline__ void block_channel_sums(double (&a)[8], double (&q)[8
 // the two sums of channel c over the blocks' rows of the table: one warp per channel, fixed order
 __device__ __forceinline__ void reduce_partials(const double* __restrict__ part, int nb, int C, int c, int lane, double& s0, double& s1) {
   double x = 0.0, y = 0.0;
-  for (int b = lane; b < nb; b += 32) {
+  int b = lane;
+  for (; b + 96 < nb; b += 128) {  // four rows of the table in flight per lane, added in a fixed order
+    const double x0 = part[(size_t)b * 2 * C + c], x1 = part[(size_t)(b + 32) * 2 * C + c];
+    const double x2 = part[(size_t)(b + 64) * 2 * C + c], x3 = part[(size_t)(b + 96) * 2 * C + c];
+    const double y0 = part[(size_t)b * 2 * C + C + c], y1 = part[(size_t)(b + 32) * 2 * C + C + c];
+    const double y2 = part[(size_t)(b + 64) * 2 * C + C + c], y3 = part[(size_t)(b + 96) * 2 * C + C + c];
+    x += (x0 + x1) + (x2 + x3);
+    y += (y0 + y1) + (y2 + y3);
+  }
+  for (; b < nb; b += 32) {
     x += part[(size_t)b * 2 * C + c];
     y += part[(size_t)b * 2 * C + C + c];
   }
@@ -416,32 +425,32 @@ __global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __res
     mdb[k] = k_mean_db[c];
     mdg[k] = k_mean_dg[c];
   }
+  constexpr int U = 4;  // elements in flight per thread (two 16-byte loads each)
   const size_t stride = (size_t)gridDim.x * blockDim.x;
-  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < n8; i0 += 2 * stride) {
-    const bool two = i0 + stride < n8;
-    const size_t i1 = two ? i0 + stride : i0;
-    const uint4 g0 = reinterpret_cast<const uint4*>(dy)[i0], z0 = reinterpret_cast<const uint4*>(z)[i0];
-    const uint4 g1 = reinterpret_cast<const uint4*>(dy)[i1], z1 = reinterpret_cast<const uint4*>(z)[i1];
-    float g[8], zz[8], o[8];
-    unpack8(g0, g);
-    unpack8(z0, zz);
+  for (size_t i0 = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i0 < n8; i0 += U * stride) {
+    uint4 gv[U], zv[U];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
-      const float xh = (zz[k] - mu[k]) * is[k];
-      o[k] = ks[k] * (gm - mdb[k] - xh * mdg[k]);
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i < n8) {
+        gv[u] = reinterpret_cast<const uint4*>(dy)[i];
+        zv[u] = reinterpret_cast<const uint4*>(z)[i];
+      }
     }
-    reinterpret_cast<uint4*>(dz)[i0] = pack8(o);
-    if (two) {
-      unpack8(g1, g);
-      unpack8(z1, zz);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = i0 + u * stride;
+      if (i >= n8) break;
+      float g[8], zz[8], o[8];
+      unpack8(gv[u], g);
+      unpack8(zv[u], zz);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float gm = fmaf(zz[k], sc[k], sh[k]) > 0.f ? g[k] : 0.f;
         const float xh = (zz[k] - mu[k]) * is[k];
         o[k] = ks[k] * (gm - mdb[k] - xh * mdg[k]);
       }
-      reinterpret_cast<uint4*>(dz)[i1] = pack8(o);
+      reinterpret_cast<uint4*>(dz)[i] = pack8(o);
     }
   }
 }
@@ -876,11 +885,12 @@ TrainBuffers carve_train(const RdpTrainWeights* w, void* ws, int B, int H, int W
   return b;
 }
 
-// CTAs of a BatchNorm reduction: eight per SM on the large layers, never fewer than 8 rows per thread
-int stat_blocks(size_t P, int C, int num_sms) {
+// CTAs of a BatchNorm reduction: one resident wave (`per_sm` = what the kernel's registers allow) on the large layers,
+// never fewer than 8 rows per thread; every CTA costs the finalize kernel one row of the table
+int stat_blocks(size_t P, int C, int num_sms, int per_sm) {
   const int lanes = ST_THREADS / (C / 8);
   const size_t by_rows = (P + (size_t)lanes * 8 - 1) / ((size_t)lanes * 8);
-  return (int)std::max<size_t>(1, std::min<size_t>(by_rows, std::min<size_t>((size_t)num_sms * 8, STAT_MAX_BLOCKS)));
+  return (int)std::max<size_t>(1, std::min<size_t>(by_rows, std::min<size_t>((size_t)num_sms * per_sm, STAT_MAX_BLOCKS)));
 }
 
 int ew_grid(size_t items) { return (int)std::min<size_t>((items + 255) / 256, (size_t)148 * 16); }
@@ -953,7 +963,7 @@ extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_n
     int r = unet::raw_conv(src0, c0, src1, c1, w->conv[i].w, C, taps, B, L.H, L.W, buf.zero_shift, buf.z[i], num_sms, stream);
     if (r != RDP_OK) return r;
     TRAIN_CHECKPOINT(stream, "forward conv %d (%dx%d, %d+%d -> %d channels)", i, L.H, L.W, c0, c1, C);
-    const int blocks = stat_blocks(P, C, num_sms);
+    const int blocks = stat_blocks(P, C, num_sms, 3);
     k_bn_stats<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.z[i], P, C, buf.part);
     k_bn_finalize<<<(C + 7) / 8, 256, 0, stream>>>(buf.part, blocks, C, (double)P, w->conv[i].gamma, w->conv[i].beta, eps, buf.mean[i], buf.var[i],
                                                    buf.invstd[i], buf.scale[i], buf.shift[i]);
@@ -1040,7 +1050,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
     const int C = w->conv[i].cout;
     const size_t P = (size_t)B * L.H * L.W;
     // ---- BatchNorm + ReLU backward: dgamma, dbeta, dz ----
-    const int blocks = stat_blocks(P, C, num_sms);
+    const int blocks = stat_blocks(P, C, num_sms, 2);
     k_bn_bwd_reduce<<<blocks, ST_THREADS, 2 * C * sizeof(double), stream>>>(buf.dy[i], buf.scale[i], buf.shift[i], buf.z[i], P, C, buf.mean[i], buf.invstd[i], buf.part);
     k_bn_bwd_finalize<<<(C + 7) / 8, 256, 0, stream>>>(buf.part, blocks, C, (double)P, w->conv[i].gamma, buf.invstd[i], g->dgamma[i], g->dbeta[i],
                                                        buf.kscale, buf.kdb, buf.kdg);
