@@ -335,34 +335,79 @@ __global__ void __launch_bounds__(DP_THREADS) k_deproject(const Params p) {
 // match.any before the shared-memory atomic was measured slower than the plain atomic, which the hardware already folds
 // for lanes that hit one address.)
 // k per bin, bin offsets, edge offsets and the frame status from the 50 counts (geometry_utils.py:121-138)
-__device__ void finalize_bins(const Params& p, int b, const volatile int* counts) {
+// Executed by one whole warp: lane l owns bins l and l + 32, the running offsets are two warp scans.
+__device__ void finalize_bins(const Params& p, int b, const volatile int* counts, int lane) {
   FrameState& f = p.fs[b];
   double x_min, width;
-  int status = RDP_FRAME_OK, off = 0, eoff = 0;
+  int status = RDP_FRAME_OK;
   if (f.n_points < MIN_POINTS) {
     status = RDP_FRAME_TOO_FEW_POINTS;
   } else if (!frame_bins(f, x_min, width)) {
     status = RDP_FRAME_DEGENERATE_BINS;
   }
-  for (int i = 0; i < NUM_BINS; ++i) {
-    const int c = status == RDP_FRAME_OK ? counts[i] : 0;
-    int k = 0;
-    if (c > 0) {
-      k = (int)__dmul_rn((double)c, 0.05);  // int(cnt * top_k_percent), geometry_utils.py:138
-      k = k < 1 ? 1 : k;
+  int c[2], k[2], coff[2], koff[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int i = lane + 32 * h;
+    c[h] = (status == RDP_FRAME_OK && i < NUM_BINS) ? counts[i] : 0;
+    k[h] = 0;
+    if (c[h] > 0) {
+      k[h] = (int)__dmul_rn((double)c[h], 0.05);  // int(cnt * top_k_percent), geometry_utils.py:138
+      k[h] = k[h] < 1 ? 1 : k[h];
     }
-    f.bin_k[i] = k;
-    f.bin_off[i] = off;
-    f.edge_off[i] = eoff;
-    off += c;
-    eoff += k;
-    if (p.out.bin_counts) p.out.bin_counts[b * NUM_BINS + i] = c;
   }
-  f.bin_off[NUM_BINS] = off;
-  f.edge_off[NUM_BINS] = eoff;
-  f.n_edge = eoff;
-  if (status == RDP_FRAME_OK && eoff < MIN_EDGE) status = RDP_FRAME_TOO_FEW_EDGE;
-  f.status = status;
+  int cbase = 0, kbase = 0;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    int ci = c[h], ki = k[h];  // inclusive scans over the lanes
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int a = __shfl_up_sync(0xffffffffu, ci, o), e = __shfl_up_sync(0xffffffffu, ki, o);
+      if (lane >= o) {
+        ci += a;
+        ki += e;
+      }
+    }
+    coff[h] = cbase + ci - c[h];
+    koff[h] = kbase + ki - k[h];
+    cbase += __shfl_sync(0xffffffffu, ci, 31);
+    kbase += __shfl_sync(0xffffffffu, ki, 31);
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int i = lane + 32 * h;
+    if (i < NUM_BINS) {
+      f.bin_k[i] = k[h];
+      f.bin_off[i] = coff[h];
+      f.edge_off[i] = koff[h];
+      if (p.out.bin_counts) p.out.bin_counts[b * NUM_BINS + i] = c[h];
+    }
+  }
+  if (lane == 0) {
+    f.bin_off[NUM_BINS] = cbase;
+    f.edge_off[NUM_BINS] = kbase;
+    f.n_edge = kbase;
+    if (status == RDP_FRAME_OK && kbase < MIN_EDGE) status = RDP_FRAME_TOO_FEW_EDGE;
+    f.status = status;
+  }
+}
+
+// Points arrive in row-major pixel order, so the 32 points a warp handles at once fall into one or two bins.  The lanes of
+// a run (consecutive lanes with the same bin) are counted with one ballot and the run's first lane makes ONE atomic for
+// all of them; the others take their place behind it.  Returns the lane's offset inside its run, the run's length
+// (valid on its first lane) and the first lane's index.  bin < 0 = no point on this lane.
+struct BinRun { int head_lane, offset, length; bool is_head; };
+__device__ __forceinline__ BinRun bin_run(int bin, int lane) {
+  const int prev = __shfl_up_sync(0xffffffffu, bin, 1);
+  const bool head = lane == 0 || prev != bin;
+  const unsigned heads = __ballot_sync(0xffffffffu, head);
+  BinRun r;
+  r.head_lane = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));  // the last head at or below this lane
+  r.offset = lane - r.head_lane;
+  const unsigned above = lane == 31 ? 0u : (heads >> (lane + 1));
+  r.length = above ? __ffs(above) : 32 - lane;                      // distance to the next head (meaningful on heads)
+  r.is_head = head;
+  return r;
 }
 
 __global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
@@ -373,7 +418,7 @@ __global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
   const int n = f.n_points, i0 = blockIdx.x * PT_PER_BLOCK;
   double x_min, width;
   if (!frame_bins(f, x_min, width)) {  // too few points or zero width: nothing to count, block 0 records the status
-    if (blockIdx.x == 0 && threadIdx.x == 0) finalize_bins(p, b, f.bin_count);
+    if (blockIdx.x == 0 && threadIdx.x < 32) finalize_bins(p, b, f.bin_count, threadIdx.x);
     return;
   }
   if (i0 >= n) return;
@@ -396,9 +441,9 @@ __global__ void __launch_bounds__(PT_THREADS) k_bin_hist(const Params p) {
     s_last = atomicAdd(&f.hist_done, 1) == blocks - 1;
   }
   __syncthreads();
-  if (s_last && threadIdx.x == 0) {
+  if (s_last && threadIdx.x < 32) {
     __threadfence();
-    finalize_bins(p, b, f.bin_count);
+    finalize_bins(p, b, f.bin_count, threadIdx.x);
   }
 }
 
@@ -412,7 +457,24 @@ __global__ void __launch_bounds__(PT_THREADS) k_scatter(const Params p) {
   __syncthreads();
   const size_t fbase = (size_t)b * p.P;
   const int i1 = min(n, i0 + PT_PER_BLOCK);
-  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) atomicAdd(&s_cnt[p.bins[fbase + i]], 1);
+  constexpr int ITERS = PT_PER_BLOCK / PT_THREADS;
+  const int lane = threadIdx.x & 31;
+  int bins[ITERS];
+  uint32_t pix[ITERS];
+  unsigned long long yk[ITERS];
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) {  // all loads of the block's share in flight
+    const int i = i0 + threadIdx.x + it * PT_THREADS;
+    const bool in = i < i1;
+    bins[it] = in ? (int)p.bins[fbase + i] : -1;
+    pix[it] = in ? p.pix[fbase + i] : 0u;
+    yk[it] = in ? p.ykey_c[fbase + i] : 0ull;
+  }
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) {
+    const BinRun r = bin_run(bins[it], lane);
+    if (r.is_head && bins[it] >= 0) atomicAdd(&s_cnt[bins[it]], r.length);
+  }
   __syncthreads();
   if (threadIdx.x < NUM_BINS) {
     const int c = s_cnt[threadIdx.x];
@@ -420,11 +482,18 @@ __global__ void __launch_bounds__(PT_THREADS) k_scatter(const Params p) {
     s_cnt[threadIdx.x] = 0;
   }
   __syncthreads();
-  for (int i = i0 + threadIdx.x; i < i1; i += PT_THREADS) {
-    const int bin = p.bins[fbase + i];
-    const int pos = s_base[bin] + atomicAdd(&s_cnt[bin], 1);
-    p.binned[fbase + pos] = p.pix[fbase + i];
-    p.ykey_b[fbase + pos] = p.ykey_c[fbase + i];
+#pragma unroll
+  for (int it = 0; it < ITERS; ++it) {
+    const int bin = bins[it];
+    const BinRun r = bin_run(bin, lane);
+    int first = 0;
+    if (r.is_head && bin >= 0) first = s_base[bin] + atomicAdd(&s_cnt[bin], r.length);
+    first = __shfl_sync(0xffffffffu, first, r.head_lane);
+    if (bin >= 0) {  // the order inside a bin is free: the selection and the final sort are total orders on (y, x, pixel)
+      const int pos = first + r.offset;
+      p.binned[fbase + pos] = pix[it];
+      p.ykey_b[fbase + pos] = yk[it];
+    }
   }
 }
 
