@@ -319,8 +319,8 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ================= MMA issuer =================
+    {
+      // ================= MMA issuer: the warp walks the loop converged, one elected lane issues =================
       constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
       for (int work = blockIdx.x; work < p.total_work; work += gridDim.x) {
@@ -335,12 +335,12 @@ k_conv3x3(const __grid_constant__ CUtensorMap map_src0, const __grid_constant__ 
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             // advancing 16 bf16 = 32 bytes inside the 128-byte swizzle row: +2 in 16-byte descriptor units
-            mma_bf16_ss(tmem_acc, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+            mma_bf16_ss_elect(tmem_acc, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
           }
-          tc_commit(&empty[stage]);  // frees the smem stage once these MMAs have read it
+          tc_commit_elect(&empty[stage]);  // frees the smem stage once these MMAs have read it
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
-        tc_commit(&acc_full[as]);    // accumulator complete
+        tc_commit_elect(&acc_full[as]);    // accumulator complete
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
     }
@@ -1141,10 +1141,14 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
       mbar_arrive(&a_full[stage]);
     }
   } else if (warp == FIRST_MMA_WARP) {
-    if (lane == 0) {
-      // ================= weights + MMA issuer =================
-      mbar_arrive_expect_tx(w_full, BN * BLOCK_K * 2);
-      tma_load_2d(smem_b, &map_w, 0, 0, w_full);
+    {
+      // ================= weights + MMA issuer: the warp walks the loop converged, one elected lane issues =================
+      // (a single-lane loop makes ptxas wrap every tcgen05.mma in a vector-to-uniform loop: ~180 cycles per 48-cycle MMA)
+      if (lane == 0) {
+        mbar_arrive_expect_tx(w_full, BN * BLOCK_K * 2);
+        tma_load_2d(smem_b, &map_w, 0, 0, w_full);
+      }
+      __syncwarp();
       mbar_wait(w_full, 0);
       tc_fence_after();
       constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BN);
@@ -1163,12 +1167,12 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
         tc_fence_after();
         const uint64_t da = make_sw128_desc(smem_u32(smem_a + stage * A_STAGE_BYTES));
 #pragma unroll
-        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) mma_bf16_ss(tmem_base + as * BN, da + 2 * k, db + 2 * k, idesc, k != 0);
-        tc_commit(&a_empty[stage]);
-        tc_commit(&acc_full[as]);
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) mma_bf16_ss_elect(tmem_base + as * BN, da + 2 * k, db + 2 * k, idesc, k != 0);
+        tc_commit_elect(&a_empty[stage]);
+        tc_commit_elect(&acc_full[as]);
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
-      RDP_DEV(if (p.debug_waits && blockIdx.x == 0)
+      RDP_DEV(if (p.debug_waits && blockIdx.x == 0 && lane == 0)
         printf("first layer mma thread: total %lld cyc, waiting acc_empty (epilogue) %lld, a_full (producers) %lld\n",
                clock64() - t_begin, w_acc, w_a);)
     }
