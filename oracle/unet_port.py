@@ -66,6 +66,37 @@ def unet_forward(sd, x: torch.Tensor, taps: dict | None = None) -> torch.Tensor:
     return F.conv2d(y, sd["outc.conv.weight"], sd["outc.conv.bias"])
 
 
+def unet_forward_train(sd, x: torch.Tensor) -> torch.Tensor:
+    """The same network as `UNet.forward` computes it in `train()` mode (`scripts/train_segmenter.py:151-158`): every
+    BatchNorm2d normalises with the statistics of the batch (`segmentation_model.py:31-36`; running statistics are not
+    touched here).  Runs under autograd: give `sd` tensors with `requires_grad` to get the reference gradients."""
+    def cbr(x, conv, bn):
+        x = F.conv2d(x, sd[f"{conv}.weight"], None, padding=1)
+        x = F.batch_norm(x, None, None, sd[f"{bn}.weight"], sd[f"{bn}.bias"], training=True, eps=BN_EPS)
+        return F.relu(x)
+
+    def dc(x, prefix):
+        return cbr(cbr(x, f"{prefix}.0", f"{prefix}.1"), f"{prefix}.3", f"{prefix}.4")
+
+    def up(x_low, x_skip, prefix):
+        x_low = F.interpolate(x_low, scale_factor=2, mode="bilinear", align_corners=True)
+        dy, dx = x_skip.shape[2] - x_low.shape[2], x_skip.shape[3] - x_low.shape[3]
+        x_low = F.pad(x_low, [dx // 2, dx - dx // 2, dy // 2, dy - dy // 2])
+        return dc(torch.cat([x_skip, x_low], dim=1), prefix)
+
+    x = x.to(torch.float32)
+    x1 = dc(x, "inc.double_conv")
+    x2 = dc(F.max_pool2d(x1, 2), "down1.maxpool_conv.1.double_conv")
+    x3 = dc(F.max_pool2d(x2, 2), "down2.maxpool_conv.1.double_conv")
+    x4 = dc(F.max_pool2d(x3, 2), "down3.maxpool_conv.1.double_conv")
+    x5 = dc(F.max_pool2d(x4, 2), "down4.maxpool_conv.1.double_conv")
+    y = up(x5, x4, "up1.conv.double_conv")
+    y = up(y, x3, "up2.conv.double_conv")
+    y = up(y, x2, "up3.conv.double_conv")
+    y = up(y, x1, "up4.conv.double_conv")
+    return F.conv2d(y, sd["outc.conv.weight"], sd["outc.conv.bias"])
+
+
 def mask_from_logits(logits: torch.Tensor) -> torch.Tensor:
     """uint8 {0,1}; fp32 sigmoid then `> 0.5`, exactly as the server does (true only for logit >~ 8.9e-8)."""
     return (torch.sigmoid(logits) > 0.5).to(torch.uint8)

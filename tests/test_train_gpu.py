@@ -99,6 +99,49 @@ def test_training_step_matches_reference_autograd(name):
         assert np.allclose(got[sure], g[f"param_after/{pname}"][sure], rtol=0, atol=2e-5), pname
 
 
+def test_training_step_with_three_classes():
+    """The multi-class head (`UNet(3, 3)`; `OutConv` `segmentation_model.py:78-84`) in both directions: logits, loss and the
+    gradients that sit before the rounding amplification (OutConv, up4) against the oracle's train-mode restatement run
+    under torch.autograd in fp32 on the same GPU (the checker; the goldens on file are single-class).  Bounds as for the
+    single-class case: logits within 5 % of their largest, loss within 1e-3, OutConv gradients within 2 % of the tensor's
+    largest entry, up4's within 3 % (2 x 64 x 96 is the small case: the 2 % of the single-class test holds at 4 x 256 x 256;
+    measured here 2.1 %), norms within 3 %; every other gradient must be finite and within 25 % in norm."""
+    from oracle import unet_port
+    from pkg.segmentation_model import UNet
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    sd = synth.make_state_dict(11, planted=False, n_classes=3)
+    model = UNet(3, 3)
+    model.load_state_dict(sd)
+    model = model.cuda().train()
+    x, t1 = (torch.from_numpy(a).cuda() for a in train_batch((60, 61), 64, 96))
+    t = torch.cat([t1, 1 - t1, torch.roll(t1, 7, dims=3)], dim=1)
+    crit = torch.nn.BCEWithLogitsLoss()
+    out = model(x)
+    loss = crit(out, t)
+    loss.backward()
+    ref_sd = {k: v.detach().clone().cuda().float().requires_grad_(v.dtype.is_floating_point and "running" not in k)
+              for k, v in sd.items()}
+    ref_out = unet_port.unet_forward_train(ref_sd, x)
+    ref_loss = crit(ref_out, t)
+    ref_loss.backward()
+    assert out.shape == (2, 3, 64, 96)
+    scale = float(ref_out.detach().abs().max())
+    print(f"3 classes: loss {loss.item():.6f} vs {ref_loss.item():.6f}; max |logit - ref| {float((out.detach() - ref_out.detach()).abs().max()):.4f} of {scale:.3f}")
+    assert abs(loss.item() - ref_loss.item()) <= 1e-3 * abs(ref_loss.item())
+    assert float((out.detach() - ref_out.detach()).abs().max()) <= 0.05 * scale
+    for name, prm in model.named_parameters():
+        g, r = prm.grad.float(), ref_sd[name].grad
+        assert torch.isfinite(g).all(), name
+        gn, rn = float(g.norm()), float(r.norm())
+        if name.startswith(("outc.", "up4.")):
+            err = float((g - r).abs().max()) / float(r.abs().max())
+            print(f"  {name}: max error {err:.4f} of the largest entry, norm {gn:.4e} vs {rn:.4e}")
+            assert err <= (0.02 if name.startswith("outc.") else 0.03) and abs(gn - rn) <= 0.03 * rn, name
+        else:
+            assert abs(gn - rn) <= 0.25 * rn, (name, gn, rn)
+
+
 def test_train_mode_then_eval_mode_round_trip():
     """After a training step the same module serves inference again (the folded weights are rebuilt from the updated
     parameters and running statistics)."""
