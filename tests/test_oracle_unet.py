@@ -56,3 +56,27 @@ def test_planted_weights_give_bimodal_logits(manifest, golden):
     lg = g["logits"]
     assert (np.abs(lg) < 0.05).mean() < 1e-3
     assert 0.1 < manifest["cases"][name]["coverage"] < 0.4
+
+
+def test_train_mode_port_matches_reference_autograd():
+    """`unet_port.unet_forward_train` (batch-statistics BatchNorm, under autograd) against what the unmodified reference
+    module computed in `train()` mode: loss and sampled gradients of tests/golden/train_step_2x64x96.npz
+    (`oracle/make_golden_train.py`).  Pins the checker of the multi-class training test."""
+    import json
+    import os
+    from oracle.make_golden_train import train_batch
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    with open(os.path.join(gdir, "train_manifest.json")) as fh:
+        meta = json.load(fh)["cases"]["train_step_2x64x96"]
+    with np.load(os.path.join(gdir, "train_step_2x64x96.npz")) as z:
+        g = {k: z[k] for k in z.files}
+    sd = {k: (v.clone().requires_grad_(True) if v.dtype.is_floating_point and "running" not in k else v)
+          for k, v in synth.make_state_dict(meta["weight_seed"], planted=False).items()}
+    x, t = (torch.from_numpy(a) for a in train_batch(meta["frame_seeds"], meta["H"], meta["W"]))
+    loss = torch.nn.BCEWithLogitsLoss()(unet_port.unet_forward_train(sd, x), t)
+    loss.backward()
+    assert abs(loss.item() - float(g["loss"])) <= 1e-5 * float(g["loss"])
+    for name in ("inc.double_conv.0.weight", "down4.maxpool_conv.1.double_conv.3.weight", "up1.conv.double_conv.1.bias",
+                 "up4.conv.double_conv.3.weight", "outc.conv.weight", "outc.conv.bias"):
+        got = sd[name].grad.reshape(-1)[torch.from_numpy(g[f"grad_idx/{name}"])].numpy()
+        np.testing.assert_allclose(got, g[f"grad_val/{name}"], rtol=2e-3, atol=2e-4 * float(g[f"grad_absmax/{name}"]), err_msg=name)
