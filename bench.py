@@ -15,6 +15,8 @@ One JSON line on stdout (rank 0).  Besides the contract keys it carries
   cudnn_reference  (c2, measurement only) the reference U-Net's own PyTorch ops on the same GPU through cuDNN: fp32 as
                 shipped and bf16 autocast + channels_last - the kernels the hand-written convolutions have to beat
   latency_b1    (c2) ms per frame of the server's unchanged call pattern at batch 1 (`server.py:121-130`)
+  training_step (c2, with the cuDNN leg) one optimisation step of the reference's training loop at 256x256 through the
+                drop-in module, and through the reference module + cuDNN autograd on the same GPU (measurement only)
 `--impl reference` times the reference's own modules (oracle/_ref, else the oracle port) on the host cores, on a
 bounded sample per step.
 
@@ -338,8 +340,9 @@ def run_reference(args):
 def time_cudnn_reference(sd, rgb_u8, flops_per_frame, reps=3):
     """"the reference's Blackwell kernel" is whatever PyTorch/cuDNN runs for the unmodified `UNet` on
     this GPU.  Measurement only - nothing of it is on the product path: the reference module itself (oracle/_ref, else the
-    oracle's functional restatement of the same torch ops) on CUDA, same batch, same event timing, fp32 as shipped
-    (`server.py:57,121-123`) and bf16 autocast + channels_last (the strongest stock variant)."""
+    oracle's functional restatement of the same torch ops) on CUDA, same batch, same event timing: fp32 as shipped
+    (`server.py:57,121-123`; PyTorch's defaults allow TF32 inside cuDNN convolutions), strict fp32, and bf16 autocast +
+    channels_last (the strongest stock variant)."""
     import torch
     from oracle import unet_port
     dev = rgb_u8.device
@@ -372,9 +375,9 @@ def time_cudnn_reference(sd, rgb_u8, flops_per_frame, reps=3):
         torch.backends.cudnn.allow_tf32 = False
         torch.backends.cuda.matmul.allow_tf32 = False
         with torch.no_grad():
-            variants["fp32_as_shipped"] = timed(lambda: fwd(x))
+            variants["fp32_strict"] = timed(lambda: fwd(x))              # no TF32 anywhere
             torch.backends.cudnn.allow_tf32 = True
-            variants["fp32_tf32_allowed"] = timed(lambda: fwd(x))
+            variants["fp32_as_shipped"] = timed(lambda: fwd(x))          # PyTorch's defaults, which the reference keeps: TF32 convolutions
             torch.backends.cudnn.allow_tf32 = False
             if model is not None:
                 model_cl = model.to(memory_format=torch.channels_last)
@@ -390,6 +393,64 @@ def time_cudnn_reference(sd, rgb_u8, flops_per_frame, reps=3):
         out[k] = {"ms_per_batch": ms, "frames_per_s": B / ms * 1e3, "tflops": B * flops_per_frame / (ms * 1e-3) / 1e12}
     del model, x
     torch.cuda.empty_cache()
+    return out
+
+
+def time_training_step(device, batches=(4, 32), steps=6):
+    """one optimisation step of the reference's loop (`scripts/train_segmenter.py:151-165`: forward in
+    train mode, BCEWithLogitsLoss, backward, Adam) at 256x256 through the drop-in `UNet` - the reference's batch of 4 and
+    a batch of 32 - and, measurement only, the reference module itself through PyTorch/cuDNN autograd on the same GPU."""
+    import torch
+    from pkg.segmentation_model import UNet
+    from rdp_b200 import synth
+    out = {"what": "full step (zero_grad, forward, loss, backward, Adam) at 256x256, CUDA events, mean of %d steps after 3" % steps,
+           "flops_per_image": "3 x 79.96 GFLOP (forward, input gradient, weight gradient)"}
+    sd = synth.make_state_dict(7, planted=False)
+    g = torch.Generator(device="cpu").manual_seed(5)
+
+    def timed(model, x, t):
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4)
+        crit = torch.nn.BCEWithLogitsLoss()
+
+        def step():
+            opt.zero_grad()
+            loss = crit(model(x), t)
+            loss.backward()
+            opt.step()
+            return loss
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize(device)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize(device)
+        return e0.elapsed_time(e1) / steps, float(loss.detach())
+
+    try:
+        for B in batches:
+            x = torch.rand((B, 3, 256, 256), generator=g).to(device)
+            t = (torch.rand((B, 1, 256, 256), generator=g) > 0.7).float().to(device)
+            ours = UNet(3, 1)
+            ours.load_state_dict(sd)
+            ms, loss = timed(ours.to(device).train(), x, t)
+            row = {"ms_per_step": ms, "images_per_s": B / ms * 1e3, "tflops_equiv": 3 * 79.960e9 * B / (ms * 1e-3) / 1e12, "loss": loss}
+            del ours
+            ref = reference_unet(sd, device)
+            if ref is not None:
+                torch.backends.cudnn.benchmark = True
+                torch.backends.cudnn.allow_tf32 = True     # PyTorch's default, which train_segmenter.py keeps
+                rms, rloss = timed(ref.train(), x, t)
+                row["reference_cudnn_as_shipped"] = {"ms_per_step": rms, "images_per_s": B / rms * 1e3, "loss": rloss,
+                                                     "precision": "fp32 tensors, TF32 allowed inside cuDNN convolutions (PyTorch default)"}
+                row["ours_over_reference"] = rms / ms
+                del ref
+            out["batch%d" % B] = row
+            torch.cuda.empty_cache()
+    except Exception as e:  # keep the line
+        out["error"] = repr(e)
     return out
 
 
@@ -610,6 +671,7 @@ def run_b200(args):
             if best:
                 line["cudnn_reference"]["our_unet_frames_per_s"] = B / (float(unet_ms.sum()) * 1e-3)
                 line["cudnn_reference"]["ours_over_best_cudnn"] = B / (float(unet_ms.sum()) * 1e-3) / best
+            line["training_step"] = time_training_step(dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = time_cpu_reference(H, W, budget_s=args.cpu_budget, all_cores=(args.config == "c2"))
     elif rank == 0:
