@@ -1076,7 +1076,9 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       wp.py_tiles = (L.H + WG_PH - 1) / WG_PH;
       const long long patches = (long long)B * wp.px_tiles * wp.py_tiles;
       const int items = wp.m_tiles * wp.n_tiles * wp.dys;
-      wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches));   // two full waves, one CTA per SM
+      // two full waves of one CTA per SM on the large layers; never fewer than four patches per CTA (every CTA pays a
+      // 128 x N x 3 epilogue of reductions, which is all there is to a small layer at a small batch)
+      wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches / 4));
       wp.first_layer = i == 0;
       wp.dw = buf.dws;
       CUtensorMap mz, mx0, mx1;
