@@ -80,6 +80,7 @@ struct ConvParams {
   int low_h, low_w;
   int pad_y, pad_x;          // offset of the interpolated image inside the skip-sized frame (Up.forward's F.pad)
   float ry, rx;              // align_corners=True scales (h-1)/(2h-1), (w-1)/(2w-1)
+  int interp_fast;           // exact doubling without pad (H = 2 low_h, W = 2 low_w): the producers work on 2x2 blocks
   int debug_waits;           // development aid: CTA 0 prints where its MMA and epilogue threads waited
   // fused MaxPool2d(2): second, pooled output of the layers that feed a Down block (8-wide tiles only)
   __nv_bfloat16* pool_out;   // (B, H/2, W/2, cout) NHWC or null
@@ -542,6 +543,98 @@ __device__ __forceinline__ uint4 interp_chunk(const ConvParams& p, const uint8_t
   return o;
 }
 
+// The same interpolation for the exact doubling without pad, a 2x2 block of halo pixels at a time.  The halo of a tile
+// starts at an odd output row and column (16 ty - 1, 8 tx TILES - 1), so it splits into blocks of rows (2k-1, 2k) x
+// columns (2j-1, 2j), and under align_corners those four pixels read the SAME four source pixels: four shared-memory
+// loads and one conversion of each per block instead of per pixel.  Indices and weights come from the expressions of
+// interp_chunk per row and column, a block whose pixels do not share their sources (first / last row or column of
+// the image) is done pixel by pixel, and pixels outside the image are the zero padding: no bit changes.
+struct InterpAxis { int i0, i1; float l0, l1; };
+__device__ __forceinline__ InterpAxis interp_axis(float r, int o, int n) {
+  InterpAxis a;
+  const float f = r * (float)o;
+  a.i0 = (int)f;
+  a.i1 = a.i0 + (a.i0 < n - 1 ? 1 : 0);
+  a.l1 = f - (float)a.i0;
+  a.l0 = 1.f - a.l1;
+  return a;
+}
+__device__ __forceinline__ void interp_unpack(const uint4& v, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(h[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+__device__ __forceinline__ uint4 interp_emit(const float (&a)[8], const float (&b)[8], const float (&c)[8], const float (&d)[8],
+                                             const InterpAxis& r, const InterpAxis& cx) {
+  uint4 o;
+  __nv_bfloat162* po = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float e0 = r.l0 * (cx.l0 * a[2 * q] + cx.l1 * b[2 * q]) + r.l1 * (cx.l0 * c[2 * q] + cx.l1 * d[2 * q]);
+    const float e1 = r.l0 * (cx.l0 * a[2 * q + 1] + cx.l1 * b[2 * q + 1]) + r.l1 * (cx.l0 * c[2 * q + 1] + cx.l1 * d[2 * q + 1]);
+    po[q] = __floats2bfloat162_rn(e0, e1);
+  }
+  return o;
+}
+// One 64-channel halo block of HW x HALO_H pixels, written with TMA's 128-byte swizzle; IT producer threads, thread t.
+template <int HW, int PW, int IT>
+__device__ __forceinline__ void interp_halo_fast(const ConvParams& p, const uint8_t* patch, uint8_t* stage, int sy0, int sx0, int y0,
+                                                 int x0, int t) {
+  constexpr int BX = HW / 2, BY = HALO_H / 2;
+  const int j = t & 7;
+  const uint4* src = reinterpret_cast<const uint4*>(patch) + j;
+  auto put = [&](int hy, int hx, const uint4& v) {
+    const int px = hy * HW + hx;
+    *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;
+  };
+  auto at = [&](int yy, int xx) { return src[((yy - sy0) * PW + (xx - sx0)) * 8]; };
+  auto single = [&](const InterpAxis& r, const InterpAxis& c) {
+    float a[8], b[8], cc[8], d[8];
+    interp_unpack(at(r.i0, c.i0), a);
+    interp_unpack(at(r.i0, c.i1), b);
+    interp_unpack(at(r.i1, c.i0), cc);
+    interp_unpack(at(r.i1, c.i1), d);
+    return interp_emit(a, b, cc, d, r, c);
+  };
+  const uint4 zero = make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+  for (int b = t >> 3; b < BX * BY; b += IT / 8) {
+    const int by = b / BX, bx = b - by * BX;
+    const int hy = 2 * by, hx = 2 * bx;
+    const int ya = y0 + hy, yb = ya + 1, xa = x0 + hx, xb = xa + 1;
+    const bool ua = ya >= 0 && ya < p.H, ub = yb >= 0 && yb < p.H, va = xa >= 0 && xa < p.W, vb = xb >= 0 && xb < p.W;
+    if (!(ua || ub) || !(va || vb)) {  // the whole block lies in the padding
+      put(hy, hx, zero);
+      put(hy, hx + 1, zero);
+      put(hy + 1, hx, zero);
+      put(hy + 1, hx + 1, zero);
+      continue;
+    }
+    const InterpAxis ra = interp_axis(p.ry, ua ? ya : yb, p.low_h), rb = interp_axis(p.ry, ub ? yb : ya, p.low_h);
+    const InterpAxis ca = interp_axis(p.rx, va ? xa : xb, p.low_w), cb = interp_axis(p.rx, vb ? xb : xa, p.low_w);
+    if (ra.i0 == rb.i0 && ra.i1 == rb.i1 && ca.i0 == cb.i0 && ca.i1 == cb.i1) {
+      float v00[8], v01[8], v10[8], v11[8];
+      interp_unpack(at(ra.i0, ca.i0), v00);
+      interp_unpack(at(ra.i0, ca.i1), v01);
+      interp_unpack(at(ra.i1, ca.i0), v10);
+      interp_unpack(at(ra.i1, ca.i1), v11);
+      put(hy, hx, (ua && va) ? interp_emit(v00, v01, v10, v11, ra, ca) : zero);
+      put(hy, hx + 1, (ua && vb) ? interp_emit(v00, v01, v10, v11, ra, cb) : zero);
+      put(hy + 1, hx, (ub && va) ? interp_emit(v00, v01, v10, v11, rb, ca) : zero);
+      put(hy + 1, hx + 1, (ub && vb) ? interp_emit(v00, v01, v10, v11, rb, cb) : zero);
+    } else {
+      put(hy, hx, (ua && va) ? single(ra, ca) : zero);
+      put(hy, hx + 1, (ua && vb) ? single(ra, cb) : zero);
+      put(hy + 1, hx, (ub && va) ? single(rb, ca) : zero);
+      put(hy + 1, hx + 1, (ub && vb) ? single(rb, cb) : zero);
+    }
+  }
+}
+
 // first source row / column a tile's halo needs (monotone in the output coordinate, so it matches interp_chunk)
 __device__ __forceinline__ int patch_origin(float r, int first_out, int pad) {
   const int o = first_out - pad;
@@ -686,11 +779,15 @@ k_conv3x3_halo(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
           mbar_wait(&full_l[sl], pl);
           uint8_t* stage = smem_a + sa * HALO_STRIDE;
           const uint8_t* patch = smem_l + sl * PATCH_STRIDE;
+          if (p.interp_fast) {
+            interp_halo_fast<HW, PATCH_W, IT>(p, patch, stage, sy0, sx0, y0, x0, t);
+          } else {
 #pragma unroll 4
-          for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
-            const int hy = px / HW, hx = px - hy * HW;
-            const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
-            *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;  // TMA's 128-byte swizzle
+            for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
+              const int hy = px / HW, hx = px - hy * HW;
+              const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
+              *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;  // TMA's 128-byte swizzle
+            }
           }
           fence_proxy_async();
           asm volatile("bar.sync 1, %0;" ::"n"(IT) : "memory");
@@ -961,11 +1058,15 @@ k_conv3x3_pair(const __grid_constant__ CUtensorMap map_src0, const __grid_consta
           mbar_wait(&full_l[sl], pl);
           uint8_t* stage = smem_a + sa * HALO_STRIDE;
           const uint8_t* patch = smem_l + sl * PATCH_STRIDE;
+          if (p.interp_fast) {
+            interp_halo_fast<HW, PATCH_W, IT>(p, patch, stage, sy0, sx0, y0, x0, t);
+          } else {
 #pragma unroll 4
-          for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
-            const int hy = px / HW, hx = px - hy * HW;
-            const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
-            *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;
+            for (int px = t >> 3; px < HW * HALO_H; px += IT / 8) {
+              const int hy = px / HW, hx = px - hy * HW;
+              const uint4 v = interp_chunk(p, patch, PATCH_W, sy0, sx0, y0 + hy, x0 + hx, j);
+              *reinterpret_cast<uint4*>(stage + px * 128 + ((j ^ (px & 7)) << 4)) = v;
+            }
           }
           fence_proxy_async();  // generic-proxy writes -> visible to the tensor core (the leader's MMA reads both CTAs)
           asm volatile("bar.sync 1, %0;" ::"n"(IT) : "memory");
@@ -2134,6 +2235,8 @@ static int forward_impl(const RdpUnet* net, const void* input, int in_fmt, int B
       p.pad_y = low->pad_y; p.pad_x = low->pad_x;
       p.ry = 2 * low->h > 1 ? (float)(low->h - 1) / (float)(2 * low->h - 1) : 0.f;
       p.rx = 2 * low->w > 1 ? (float)(low->w - 1) / (float)(2 * low->w - 1) : 0.f;
+      static const bool interp_generic = dev_env("RDP_INTERP_GENERIC") != nullptr;  // development switch: per-pixel producer everywhere
+      p.interp_fast = !interp_generic && low->pad_y == 0 && low->pad_x == 0 && L.H == 2 * low->h && L.W == 2 * low->w && low->h > 1 && low->w > 1;
     }
     const CUtensorMap *pm0 = nullptr, *pm1 = nullptr;
     const int box_w = halo ? halo_w(tiles) : p.tile_w, box_h = halo ? HALO_H : p.tile_h;

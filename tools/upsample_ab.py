@@ -1,10 +1,12 @@
 """Development build only: the stand-alone up4 interpolation, 2x2-block kernel against the row kernel (RDP_UPSAMPLE_ROW):
 logits of one forward must agree bit for bit, and the launch time of 'upsample up4' is printed for both.
-Run each mode in its own process:  python tools/upsample_ab.py quad|row  (writes gpurun_out/ups_<mode>.npy)"""
+Run each mode in its own process:  python tools/upsample_ab.py quad|row|generic  (writes gpurun_out/ups_<mode>.npy)"""
 import os, sys
 mode = sys.argv[1]
 if mode == "row":
     os.environ["RDP_UPSAMPLE_ROW"] = "1"
+if mode == "generic":       # fused interpolation producers of up1..up3: per-pixel path instead of the 2x2-block one
+    os.environ["RDP_INTERP_GENERIC"] = "1"
 import numpy as np, torch
 sys.path[:0] = ['/root/repo', '/root/repo/robotic-discovery-platform_b200']
 from pkg.segmentation_model import UNet
