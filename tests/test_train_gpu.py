@@ -142,6 +142,67 @@ def test_training_step_with_three_classes():
             assert abs(gn - rn) <= 0.25 * rn, (name, gn, rn)
 
 
+@pytest.mark.parametrize("shape", [(2, 32, 32), (1, 48, 80), (3, 16, 64)])
+def test_training_step_small_and_odd_shapes(shape):
+    """Shapes whose deepest levels are smaller than one tile of the kernels (2x2, 3x5, 1x4 pixels at level 4): the TMA boxes of
+    the convolutions and of the weight gradient hang over the tensors on every side.  With so few samples per BatchNorm
+    channel the gradients themselves are rounding-chaotic, so what is asserted is the forward (logits, loss against the
+    oracle's train-mode restatement in fp32) and that every gradient is finite and of the right order of magnitude."""
+    from oracle import unet_port
+    from pkg.segmentation_model import UNet
+    B, H, W = shape
+    sd = synth.make_state_dict(21, planted=False)
+    model = UNet(3, 1)
+    model.load_state_dict(sd)
+    model = model.cuda().train()
+    g = torch.Generator().manual_seed(B * 1000 + H + W)
+    x = torch.rand((B, 3, H, W), generator=g).cuda()
+    t = (torch.rand((B, 1, H, W), generator=g) > 0.6).float().cuda()
+    crit = torch.nn.BCEWithLogitsLoss()
+    out = model(x)
+    loss = crit(out, t)
+    loss.backward()
+    ref_sd = {k: v.detach().clone().cuda().float().requires_grad_(v.dtype.is_floating_point and "running" not in k)
+              for k, v in sd.items()}
+    ref_out = unet_port.unet_forward_train(ref_sd, x)
+    ref_loss = crit(ref_out, t)
+    ref_loss.backward()
+    scale = float(ref_out.detach().abs().max())
+    err = float((out.detach() - ref_out.detach()).abs().max())
+    print(f"{shape}: loss {loss.item():.5f} vs {ref_loss.item():.5f}, max |logit - ref| {err:.4f} of {scale:.3f}")
+    assert abs(loss.item() - ref_loss.item()) <= 1e-2 * abs(ref_loss.item())
+    assert err <= 0.1 * scale
+    for name, prm in model.named_parameters():
+        gn, rn = float(prm.grad.float().norm()), float(ref_sd[name].grad.norm())
+        assert torch.isfinite(prm.grad).all() and 0.2 * rn <= gn <= 5.0 * rn + 1e-6, (name, gn, rn)
+
+
+def test_weight_packing_kernel_matches_torch_layouts():
+    """`rdp_unet_train_pack` (one kernel per layer, every step) against the same two layouts built with torch ops
+    (`rdp_b200.train.pack_for_training`): bf16 [cout][tap][cin] and the flipped, transposed [cin][tap][cout], bit for bit."""
+    import ctypes as C
+    from rdp_b200 import _lib, train
+    from rdp_b200.synth import unet_layer_table
+    lib = _lib.load()
+    train._bind(lib)
+    sd = {k: v.cuda() for k, v in synth.make_state_dict(5, planted=False).items()}
+    ws, wts = train.pack_for_training(sd, 3)
+    stream = torch.cuda.current_stream().cuda_stream
+    for i, (conv, _, cin, cout) in enumerate(unet_layer_table(3)):
+        w32 = sd[f"{conv}.weight"].float().contiguous()
+        got_w = torch.full_like(ws[i], float("nan"))
+        got_t = torch.full_like(wts[i], float("nan")) if wts[i] is not None else None
+        _lib.check(lib.rdp_unet_train_pack(w32.data_ptr(), cout, cin, int(i == 0), got_w.data_ptr(),
+                                           got_t.data_ptr() if got_t is not None else None, stream), "rdp_unet_train_pack")
+        torch.cuda.synchronize()
+        assert torch.equal(got_w.view(torch.int16), ws[i].view(torch.int16)), conv
+        if got_t is not None:
+            assert torch.equal(got_t.view(torch.int16), wts[i].view(torch.int16)), conv
+    assert lib.rdp_unet_train_pack(None, 64, 64, 0, None, None, stream) != 0       # null pointers are refused
+    w32 = sd["inc.double_conv.3.weight"].float().contiguous()
+    assert lib.rdp_unet_train_pack(w32.data_ptr(), 64, 64, 0, ws[1].data_ptr(), None, stream) != 0   # w_t is required
+
+
 def test_train_mode_then_eval_mode_round_trip():
     """After a training step the same module serves inference again (the folded weights are rebuilt from the updated
     parameters and running statistics)."""
