@@ -106,7 +106,7 @@ class UNet(nn.Module):
 
     def __getstate__(self):
         state = dict(self.__dict__)
-        for k in ("_rdp_engine", "_rdp_fingerprint", "_rdp_lock"):
+        for k in ("_rdp_engine", "_rdp_fingerprint", "_rdp_lock", "_rdp_train_buffers"):
             state.pop(k, None)
         return state
 

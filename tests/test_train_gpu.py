@@ -219,3 +219,16 @@ def test_train_mode_then_eval_mode_round_trip():
     sd = {k: v.detach().cpu() for k, v in model.state_dict().items()}
     ref = unet_port.unet_forward(sd, x.cpu())
     assert float((out.cpu() - ref).abs().max()) <= 0.05 * float(ref.abs().max())
+    # the trained module pickles as a whole (`mlflow.pytorch.log_model`, train_segmenter.py:199-204) without the engine, the
+    # lock or the bf16 operand buffers of the training step, and the copy serves inference
+    import io
+    import pickle
+    state = model.__getstate__()
+    assert not any(k.startswith("_rdp_") for k in state)
+    buf = io.BytesIO()
+    torch.save(model, buf)
+    assert buf.tell() < 80e6                                   # 17.3 M fp32 parameters + buffers, nothing else
+    buf.seek(0)
+    copy = torch.load(buf, weights_only=False).cuda().eval()
+    with torch.no_grad():
+        assert torch.equal(copy(x), out)
