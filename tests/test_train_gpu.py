@@ -232,3 +232,23 @@ def test_train_mode_then_eval_mode_round_trip():
     copy = torch.load(buf, weights_only=False).cuda().eval()
     with torch.no_grad():
         assert torch.equal(copy(x), out)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_training_step_on_a_second_device_of_the_process():
+    """One process, two GPUs (SURVEY 8e allows threads instead of torchrun): kernel attributes, the packed operand buffers and
+    the workspace belong to the device the batch lives on."""
+    from pkg.segmentation_model import UNet
+    x, t = (torch.from_numpy(a) for a in train_batch((44, 45), 64, 96))
+    losses, norms = [], []
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        model = UNet(3, 1)
+        model.load_state_dict(synth.make_state_dict(8, planted=False))
+        model = model.to(dev).train()
+        loss = torch.nn.BCEWithLogitsLoss()(model(x.to(dev)), t.to(dev))
+        loss.backward()
+        torch.cuda.synchronize(dev)
+        losses.append(loss.item())
+        norms.append(float(model.outc.conv.weight.grad.norm()))
+    assert abs(losses[0] - losses[1]) <= 1e-5 * abs(losses[0]) and abs(norms[0] - norms[1]) <= 1e-3 * norms[0], (losses, norms)
