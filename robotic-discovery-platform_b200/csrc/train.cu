@@ -768,6 +768,150 @@ __global__ void __launch_bounds__(256) k_dw_layout(const float* __restrict__ src
   }
 }
 
+// The same GEMM for the layers with 64 output channels (the four full-resolution layers: their pixel count makes them the
+// long ones, and in k_wgrad they fill only half of the M = 128 rows), with the operands' roles exchanged and ALL NINE taps
+// in one CTA:
+//   * M = input channels, N = the 64 output channels; one 64-channel block of X per CTA (a 128-channel input is two
+//     independent problems, blockIdx selects the block);
+//   * M = 128 holds TWO TAPS of that block: the MN-major descriptor's block stride (LBO) is free, so the second 64 rows
+//     are the same halo entered one tap further (128 bytes for the next column, 16 pixels = 2048 bytes from the last
+//     column of a halo row to the first of the next).  Taps (0,1) (2,3) (4,5) (6,7) share an MMA each, tap 8 takes a
+//     fifth whose upper rows repeat the lower and are dropped: five MMAs per patch row for nine taps;
+//   * one stage = dZ of a 16x8 patch (16 KB) + the 18x10 halo of X (22.5 KB): 39 KB from L2 for nine taps, where three
+//     CTAs with one tap row each moved 102 KB - these layers were bound by L2 throughput, not by the tensor pipe.
+// D rows are (tap, input channel), columns the output channels: a thread adds its 64 contiguous floats of the [k][co]
+// scratch with 16-byte vector reductions.  The im2col'ed first layer is the one-tap case (halo row 1, column 1).
+constexpr int WG9_HALO_H = WG_PH + 2;
+constexpr int WG9_X_BYTES = WG_HALO_W * WG9_HALO_H * 128;                 // 23,040
+constexpr int WG9_X_STRIDE = (WG9_X_BYTES + 1023) / 1024 * 1024;          // 23,552: the next stage starts 1024-byte aligned
+constexpr int WG9_STAGE = WG_DZ_BLOCK + WG9_X_STRIDE;
+__global__ void __launch_bounds__(WG_THREADS, 1)
+k_wgrad_co64(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUtensorMap map_x0, const __grid_constant__ CUtensorMap map_x1,
+             const WgradParams p) {
+  constexpr uint32_t TMEM_COLS = 512;  // five accumulators of 64 columns
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + p.stages * WG9_STAGE);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + WG_MAX_STAGES;
+  uint64_t* done = bars + 2 * WG_MAX_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  const int nt = blockIdx.x % p.n_tiles;   // 64-channel block of the input
+  const int ks = blockIdx.x / p.n_tiles;
+  const bool one_tap = p.first_layer != 0;   // a 1x1 convolution over the im2col'ed image
+  const long long total = (long long)p.B * p.py_tiles * p.px_tiles;
+  const long long s0 = total * ks / p.ksplit, s1 = total * (ks + 1) / p.ksplit;
+
+  if (threadIdx.x == 0) {
+    prefetch_tensormap(&map_dz);
+    prefetch_tensormap(&map_x0);
+    prefetch_tensormap(&map_x1);
+    for (int s = 0; s < WG_MAX_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      const int c = nt * 64;
+      for (long long s = s0; s < s1; ++s) {
+        const int px = (int)(s % p.px_tiles);
+        long long r = s / p.px_tiles;
+        const int py = (int)(r % p.py_tiles), n = (int)(r / p.py_tiles);
+        const int x0 = px * WG_PW, y0 = py * WG_PH;
+        uint8_t* st = smem + stage * WG9_STAGE;
+        mbar_wait(&empty[stage], phase ^ 1);
+        mbar_arrive_expect_tx(&full[stage], WG_DZ_BLOCK + WG9_X_BYTES);
+        tma_load_4d(st, &map_dz, 0, x0, y0, n, &full[stage]);
+        if (c < p.c0) tma_load_4d(st + WG_DZ_BLOCK, &map_x0, c, x0 - 1, y0 - 1, n, &full[stage]);
+        else tma_load_4d(st + WG_DZ_BLOCK, &map_x1, c - p.c0, x0 - 1, y0 - 1, n, &full[stage]);
+        if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc_bf16(128, 64) | (1u << 15) | (1u << 16);  // A and B MN-major
+    constexpr uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);                 // SBO = 1024 bytes, version 1, 128-byte swizzle
+    constexpr uint32_t lbo_next_col = (128u >> 4) << 16;                            // second tap = one pixel on
+    constexpr uint32_t lbo_next_row = ((uint32_t)(WG_HALO_W - 2) * 128u >> 4) << 16;  // from column 2 of a halo row to column 0 of the next
+    uint32_t stage = 0, phase = 0;
+    for (long long s = s0; s < s1; ++s) {
+      mbar_wait(&full[stage], phase);
+      tc_fence_after();
+      const uint32_t z0 = smem_u32(smem + stage * WG9_STAGE);
+      const uint32_t z_lo = z0 >> 4, x_lo = (z0 + WG_DZ_BLOCK) >> 4;
+      const uint32_t first = s != s0;
+#pragma unroll
+      for (int r = 0; r < WG_PH; ++r) {
+        const uint64_t db = ((uint64_t)hi << 32) | (z_lo + r * (WG_PW * 128 >> 4));   // dZ: N = 64 output channels
+        const uint32_t acc = r != 0 ? 1u : first;
+        // halo pixel (row, col) in 16-byte units: ((r + dy + 1) * 18 + dx + 1) * 8
+        auto view = [&](int tap) { return x_lo + ((r + tap / 3) * WG_HALO_W + tap % 3) * 8; };
+        if (one_tap) {
+          mma_bf16_ss_elect(tmem_base, ((uint64_t)hi << 32) | view(4), db, idesc, acc);   // the centre tap only; upper rows repeat
+        } else {
+          mma_bf16_ss_elect(tmem_base + 0 * 64, ((uint64_t)hi << 32) | (view(0) | lbo_next_col), db, idesc, acc);  // taps 0, 1
+          mma_bf16_ss_elect(tmem_base + 1 * 64, ((uint64_t)hi << 32) | (view(2) | lbo_next_row), db, idesc, acc);  // taps 2, 3
+          mma_bf16_ss_elect(tmem_base + 2 * 64, ((uint64_t)hi << 32) | (view(4) | lbo_next_col), db, idesc, acc);  // taps 4, 5
+          mma_bf16_ss_elect(tmem_base + 3 * 64, ((uint64_t)hi << 32) | (view(6) | lbo_next_col), db, idesc, acc);  // taps 6, 7
+          mma_bf16_ss_elect(tmem_base + 4 * 64, ((uint64_t)hi << 32) | view(8), db, idesc, acc);                   // tap 8; upper rows repeat
+        }
+      }
+      tc_commit_elect(&empty[stage]);
+      if (++stage == (uint32_t)p.stages) { stage = 0; phase ^= 1; }
+    }
+    tc_commit_elect(done);
+  } else if (s1 > s0) {
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int ci = nt * 64 + (row & 63);
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    const int naccs = one_tap ? 1 : 5;
+#pragma unroll 1
+    for (int a = 0; a < naccs; ++a) {
+      // which row k = tap * cin + ci of the scratch this row of accumulator `a` is; k < 0: the row carries nothing
+      int k = -1;
+      if (one_tap) {
+        if (row < 64 && row < 9 * p.cin_real) k = row;            // the im2col column is k = tap * cin + c already
+      } else if (ci < p.cin_real) {
+        const int tap = 2 * a + (row >> 6);
+        if (tap < 9 && (a < 4 || row < 64)) k = tap * p.cin_real + ci;
+      }
+#pragma unroll 1
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + a * 64 + c * 32, r);
+        tmem_ld_wait();
+        if (k >= 0) {
+          float4* dst = reinterpret_cast<float4*>(p.dw + (size_t)k * p.cout + c * 32);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            atomicAdd(dst + j, make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                                           __uint_as_float(r[4 * j + 3])));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -781,14 +925,14 @@ static EncodeTiledFn encode_fn() {
   }
   return fn;
 }
-// map over an NHWC bf16 tensor: dims (C, W, H, B), box (64 channels, box_w pixels, WG_PH rows, 1), 128-byte swizzle,
+// map over an NHWC bf16 tensor: dims (C, W, H, B), box (64 channels, box_w pixels, box_h rows, 1), 128-byte swizzle,
 // zero fill outside
-static int make_nhwc_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w) {
+static int make_nhwc_map(CUtensorMap* m, const void* ptr, int B, int H, int W, int C, int box_w, int box_h = WG_PH) {
   EncodeTiledFn fn = encode_fn();
   RDP_REQUIRE(fn, RDP_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)WG_PH, 1};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_w, (cuuint32_t)box_h, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -809,6 +953,20 @@ static int launch_wgrad_t(const CUtensorMap& mz, const CUtensorMap& mx0, const C
     set[dev] = true;
   }
   k_wgrad<N><<<p.m_tiles * p.n_tiles * p.dys * p.ksplit, WG_THREADS, smem_bytes, stream>>>(mz, mx0, mx1, p);
+  return RDP_OK;
+}
+
+static int launch_wgrad_co64(const CUtensorMap& mz, const CUtensorMap& mx0, const CUtensorMap& mx1, WgradParams p, cudaStream_t stream) {
+  p.stages = std::min(WG_MAX_STAGES, (WG_SMEM_BUDGET - 2048) / WG9_STAGE);
+  const int smem_bytes = p.stages * WG9_STAGE + 1024 + 256;
+  static bool set[64] = {};
+  int dev = 0;
+  RDP_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 64 && !set[dev]) {
+    RDP_CUDA_TRY(cudaFuncSetAttribute(k_wgrad_co64, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM_BUDGET));
+    set[dev] = true;
+  }
+  k_wgrad_co64<<<p.n_tiles * p.ksplit, WG_THREADS, smem_bytes, stream>>>(mz, mx0, mx1, p);
   return RDP_OK;
 }
 
@@ -1081,12 +1239,22 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches / 4));
       wp.first_layer = i == 0;
       wp.dw = buf.dws;
+#ifdef RDP_DEVELOPMENT
+      static const bool no_co64 = getenv("RDP_WGRAD_NO_CO64") != nullptr;  // A/B: the general kernel for these layers too
+#else
+      const bool no_co64 = false;
+#endif
+      const bool co64 = C == 64 && !no_co64;   // operands exchanged, nine taps per CTA (k_wgrad_co64)
       CUtensorMap mz, mx0, mx1;
       RDP_TRY(make_nhwc_map(&mz, buf.dz, B, L.H, L.W, C, WG_PW));
-      RDP_TRY(make_nhwc_map(&mx0, s0, B, L.H, L.W, c0, WG_HALO_W));
-      if (c1) RDP_TRY(make_nhwc_map(&mx1, s1, B, L.H, L.W, c1, WG_HALO_W));
+      RDP_TRY(make_nhwc_map(&mx0, s0, B, L.H, L.W, c0, WG_HALO_W, co64 ? WG9_HALO_H : WG_PH));
+      if (c1) RDP_TRY(make_nhwc_map(&mx1, s1, B, L.H, L.W, c1, WG_HALO_W, co64 ? WG9_HALO_H : WG_PH));
       else mx1 = mx0;
-      if (n_tile == 64) RDP_TRY(launch_wgrad_t<64>(mz, mx0, mx1, wp, stream));
+      if (co64) {
+        wp.n_tiles = cin_pad / 64;
+        wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / wp.n_tiles, patches / 4));
+        RDP_TRY(launch_wgrad_co64(mz, mx0, mx1, wp, stream));
+      } else if (n_tile == 64) RDP_TRY(launch_wgrad_t<64>(mz, mx0, mx1, wp, stream));
       else RDP_TRY(launch_wgrad_t<128>(mz, mx0, mx1, wp, stream));
       k_dw_layout<<<dim3((cin_real + 31) / 32, (C + 31) / 32), 256, 0, stream>>>(buf.dws, cin_real, C, g->dw[i]);
     }
