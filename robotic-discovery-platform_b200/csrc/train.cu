@@ -1234,9 +1234,24 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       wp.py_tiles = (L.H + WG_PH - 1) / WG_PH;
       const long long patches = (long long)B * wp.px_tiles * wp.py_tiles;
       const int items = wp.m_tiles * wp.n_tiles * wp.dys;
-      // two full waves of one CTA per SM on the large layers; never fewer than four patches per CTA (every CTA pays a
-      // 128 x N x 3 epilogue of reductions, which is all there is to a small layer at a small batch)
-      wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches / 4));
+      // Split-K factor: every CTA ends with 128 x N x 3 fp32 reductions into the scratch, and L2 retires about one of
+      // them per slice and clock (14 M of them = 40 us on the 512 x 512 layers with six CTAs per work item), so more
+      // CTAs per work item buy tensor time only while the layer has it to give.  Pick the factor that minimises
+      // waves x patches-per-CTA x (cycles per patch) + reductions / (L2 slices), both in cycles; never fewer than
+      // four patches per CTA.
+      {
+        const double patch_cycles = 24.0 * (n_tile == 128 ? 100.0 : 77.0), reds_per_cta = 128.0 * n_tile * 3.0, l2_slices = 184.0;
+        const int ks_max = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / items, patches / 4));
+        double best = 1e300;
+        for (int ks = 1; ks <= ks_max; ++ks) {
+          const double waves = (double)((items * ks + num_sms - 1) / num_sms);
+          const double cost = waves * (double)((patches + ks - 1) / ks) * patch_cycles + (double)items * ks * reds_per_cta / l2_slices;
+          if (cost < best) {
+            best = cost;
+            wp.ksplit = ks;
+          }
+        }
+      }
       wp.first_layer = i == 0;
       wp.dw = buf.dws;
 #ifdef RDP_DEVELOPMENT
@@ -1252,7 +1267,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       else mx1 = mx0;
       if (co64) {
         wp.n_tiles = cin_pad / 64;
-        wp.ksplit = (int)std::max<long long>(1, std::min<long long>(2 * num_sms / wp.n_tiles, patches / 4));
+        wp.ksplit = (int)std::max<long long>(1, std::min<long long>(num_sms / wp.n_tiles, patches / 4));
         RDP_TRY(launch_wgrad_co64(mz, mx0, mx1, wp, stream));
       } else if (n_tile == 64) RDP_TRY(launch_wgrad_t<64>(mz, mx0, mx1, wp, stream));
       else RDP_TRY(launch_wgrad_t<128>(mz, mx0, mx1, wp, stream));
