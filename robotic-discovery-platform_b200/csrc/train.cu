@@ -76,7 +76,7 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
 // BatchNorm (training mode) forward
 // ---------------------------------------------------------------------------------------------------------
 // Per-thread partial sums of one 8-channel group -> the block's [2][C] array `s_acc` (zeroed by the caller), then the
-// block's row of the partial-sum table `part` ([gridDim.x][2C]).  No atomics anywhere: lanes of a warp that hold the same
+// block's column of the partial-sum table `part` ([2C][gridDim.x]).  No atomics anywhere: lanes of a warp that hold the same
 // group (c8 < 32: lanes cg, cg + c8, ...) are folded with shuffles, the eight warps then add their values one warp at a
 // time (within a warp the active lanes own distinct channels), and the finalize kernel adds the blocks' rows in a fixed
 // order.  The statistics are therefore bit-reproducible from run to run.  Called by every thread of the block; needs
@@ -105,24 +105,25 @@ __device__ __forceinline__ void block_channel_sums(double (&a)[8], double (&q)[8
     }
     __syncthreads();
   }
-  for (int i = tid; i < 2 * C; i += ST_THREADS) part[(size_t)blockIdx.x * 2 * C + i] = s_acc[i];
+  // table layout [2C][gridDim.x]: the finalize kernel's warp reads one row of consecutive blocks per channel
+  for (int i = tid; i < 2 * C; i += ST_THREADS) part[(size_t)i * gridDim.x + blockIdx.x] = s_acc[i];
 }
 
 // the two sums of channel c over the blocks' rows of the table: one warp per channel, fixed order
 __device__ __forceinline__ void reduce_partials(const double* __restrict__ part, int nb, int C, int c, int lane, double& s0, double& s1) {
+  const double* px = part + (size_t)c * nb;
+  const double* py = part + (size_t)(C + c) * nb;
   double x = 0.0, y = 0.0;
   int b = lane;
-  for (; b + 96 < nb; b += 128) {  // four rows of the table in flight per lane, added in a fixed order
-    const double x0 = part[(size_t)b * 2 * C + c], x1 = part[(size_t)(b + 32) * 2 * C + c];
-    const double x2 = part[(size_t)(b + 64) * 2 * C + c], x3 = part[(size_t)(b + 96) * 2 * C + c];
-    const double y0 = part[(size_t)b * 2 * C + C + c], y1 = part[(size_t)(b + 32) * 2 * C + C + c];
-    const double y2 = part[(size_t)(b + 64) * 2 * C + C + c], y3 = part[(size_t)(b + 96) * 2 * C + C + c];
+  for (; b + 96 < nb; b += 128) {  // four coalesced loads per sum in flight per lane, added in a fixed order
+    const double x0 = px[b], x1 = px[b + 32], x2 = px[b + 64], x3 = px[b + 96];
+    const double y0 = py[b], y1 = py[b + 32], y2 = py[b + 64], y3 = py[b + 96];
     x += (x0 + x1) + (x2 + x3);
     y += (y0 + y1) + (y2 + y3);
   }
   for (; b < nb; b += 32) {
-    x += part[(size_t)b * 2 * C + c];
-    y += part[(size_t)b * 2 * C + C + c];
+    x += px[b];
+    y += py[b];
   }
 #pragma unroll
   for (int off = 16; off; off >>= 1) {
@@ -994,7 +995,7 @@ struct TrainBuffers {
   __nv_bfloat16* up[4];      // up-sampled + padded low branch of up1..up4
   float* zero_shift;         // 1024 zeros
   float *mean[18], *var[18], *invstd[18], *scale[18], *shift[18];
-  double* part;              // [STAT_MAX_BLOCKS][2 * 1024] per-block partial sums of the BatchNorm reductions
+  double* part;              // [2 * C][blocks] per-block partial sums of the BatchNorm reductions (room for STAT_MAX_BLOCKS x 2048)
   // backward scratch
   __nv_bfloat16* dy[18];     // gradient wrt y[i]
   __nv_bfloat16* dz;         // gradient wrt the current layer's z (largest layer)
