@@ -749,6 +749,32 @@ __global__ void __launch_bounds__(256) k_pack_train_weights(const float* __restr
   }
 }
 
+// The same two layouts for every layer but the first, through shared memory so that both sides are contiguous: a block
+// moves 32 output channels x 32 input channels x 9 taps (the source rows [co][ci0 .. ci0+31][9] are 288 consecutive floats).
+// grid = (cin / 32, cout / 32); cin and cout are multiples of 64 here.
+__global__ void __launch_bounds__(256) k_pack_train_weights_tiled(const float* __restrict__ w, int cout, int cin, __nv_bfloat16* __restrict__ fwd,
+                                                                  __nv_bfloat16* __restrict__ wt) {
+  __shared__ __nv_bfloat16 tile[32][9 * 32 + 2];  // [co][ci * 9 + tap]
+  const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+  for (int r = wp; r < 32; r += 8) {
+    const float* src = w + ((size_t)(co0 + r) * cin + ci0) * 9;
+#pragma unroll
+    for (int e = lane; e < 288; e += 32) tile[r][e] = __float2bfloat16_rn(src[e]);
+  }
+  __syncthreads();
+  // fwd[co][tap][ci]: 32 consecutive input channels per (co, tap)
+  for (int r = wp; r < 32 * 9; r += 8) {
+    const int co = r / 9, tap = r - co * 9;
+    fwd[((size_t)(co0 + co) * 9 + tap) * cin + ci0 + lane] = tile[co][lane * 9 + tap];
+  }
+  // wt[ci][8 - tap][co]: 32 consecutive output channels per (ci, tap)
+  for (int r = wp; r < 32 * 9; r += 8) {
+    const int ci = r / 9, tap = r - ci * 9;
+    wt[((size_t)(ci0 + ci) * 9 + (8 - tap)) * cout + co0 + lane] = tile[lane][ci * 9 + tap];
+  }
+}
+
 // scratch [9 * cin][cout] (what the GEMM epilogue can add to with coalesced reductions) -> the parameter's layout
 // [cout][cin][3][3].  A block moves 32 output channels x 32 input channels x 9 taps through shared memory so that both
 // sides are contiguous.  grid = (ceil(cin / 32), ceil(cout / 32)).
@@ -1084,8 +1110,12 @@ extern "C" int rdp_unet_train_pack(const float* w_oihw, int cout, int cin, int f
   RDP_REQUIRE(!first_layer || 9 * cin <= 64, RDP_ERR_UNSUPPORTED, "rdp_unet_train_pack: first layer with %d channels (9*C must be <= 64)", cin);
   RDP_REQUIRE(first_layer || w_t, RDP_ERR_BAD_ARGUMENT, "rdp_unet_train_pack: w_t is required for every layer but the first");
   const int total = cout * cin * 9;
-  k_pack_train_weights<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      w_oihw, cout, cin, first_layer ? 1 : 0, static_cast<__nv_bfloat16*>(w), first_layer ? nullptr : static_cast<__nv_bfloat16*>(w_t));
+  if (!first_layer && cin % 32 == 0 && cout % 32 == 0)
+    k_pack_train_weights_tiled<<<dim3(cin / 32, cout / 32), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        w_oihw, cout, cin, static_cast<__nv_bfloat16*>(w), static_cast<__nv_bfloat16*>(w_t));
+  else
+    k_pack_train_weights<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        w_oihw, cout, cin, first_layer ? 1 : 0, static_cast<__nv_bfloat16*>(w), first_layer ? nullptr : static_cast<__nv_bfloat16*>(w_t));
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
 }
