@@ -235,24 +235,37 @@ __global__ void __launch_bounds__(256) k_bn_relu(const __nv_bfloat16* __restrict
 // ---------------------------------------------------------------------------------------------------------
 // OutConv (1x1, 64 -> n_classes, bias), both directions
 // ---------------------------------------------------------------------------------------------------------
+// Eight lanes share a pixel (one 8-channel group each, so a warp reads 512 contiguous bytes per load), partial dot
+// products are folded with three shuffles, lane 0 of the eight writes.  Four pixels in flight per lane group.
 __global__ void __launch_bounds__(256) k_outconv_fwd(const __nv_bfloat16* __restrict__ y, size_t P, size_t HW, int ncls,
                                                      const float* __restrict__ w, const float* __restrict__ bias, float* __restrict__ logits) {
-  const size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (p >= P) return;
-  float x[64];
+  const int cg = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const size_t pstride = (size_t)gridDim.x * 32;
+  for (size_t p0 = (size_t)blockIdx.x * 32 + rl; p0 < P; p0 += 4 * pstride) {
+    uint4 v[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    float f[8];
-    unpack8(reinterpret_cast<const uint4*>(y + p * 64)[j], f);
+    for (int u = 0; u < 4; ++u) {
+      const size_t pu = p0 + u * pstride;
+      v[u] = pu < P ? reinterpret_cast<const uint4*>(y + pu * 64)[cg] : make_uint4(0, 0, 0, 0);
+    }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) x[8 * j + k] = f[k];
-  }
-  const size_t n = p / HW, off = p % HW;
-  for (int cls = 0; cls < ncls; ++cls) {
-    float a = 0.f;
+    for (int u = 0; u < 4; ++u) {
+      const size_t pu = p0 + u * pstride;   // uniform across the eight lanes of a pixel; the shuffles below need every lane
+      float f[8];
+      unpack8(v[u], f);
+      for (int cls = 0; cls < ncls; ++cls) {
+        float a = 0.f;
 #pragma unroll
-    for (int c = 0; c < 64; ++c) a = fmaf(x[c], w[cls * 64 + c], a);
-    logits[(n * ncls + cls) * HW + off] = a + bias[cls];
+        for (int k = 0; k < 8; ++k) a = fmaf(f[k], w[cls * 64 + cg * 8 + k], a);
+        a += __shfl_xor_sync(0xffffffffu, a, 1);
+        a += __shfl_xor_sync(0xffffffffu, a, 2);
+        a += __shfl_xor_sync(0xffffffffu, a, 4);
+        if (cg == 0 && pu < P) {
+          const size_t n = pu / HW, off = pu % HW;
+          logits[(n * ncls + cls) * HW + off] = a + bias[cls];
+        }
+      }
+    }
   }
 }
 
@@ -1186,7 +1199,8 @@ extern "C" int rdp_unet_train_forward(const RdpTrainWeights* w, const float* x_n
     RDP_TRY(stage(11 + 2 * j, buf.y[10 + 2 * j], w->conv[10 + 2 * j].cout, nullptr, 0, 9));
   }
   const size_t P0 = (size_t)B * H * W;
-  k_outconv_fwd<<<(int)((P0 + 255) / 256), 256, 0, stream>>>(buf.y[17], P0, (size_t)H * W, w->n_classes, w->outc_weight, w->outc_bias, logits);
+  k_outconv_fwd<<<(int)std::min<size_t>((P0 + 127) / 128, (size_t)num_sms * 8), 256, 0, stream>>>(buf.y[17], P0, (size_t)H * W, w->n_classes, w->outc_weight,
+                                                                                                   w->outc_bias, logits);
   RDP_CUDA_TRY(cudaGetLastError());
   return RDP_OK;
 }

@@ -1344,12 +1344,37 @@ k_conv_first(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ 
 // ---------------------------------------------------------------------------------------------------------
 // First layer: gather the 3x3xC neighbourhood of every pixel into 64 bf16 (k = (3*ky+kx)*C + c, zero padded),
 // so that inc.0 runs through the same tensor-core kernel as a 1x1 convolution with K = 64.
-// grid = (ceil(W*8 / 256), H, B); C is a template parameter so that k / C and k % C are multiplications.
+// grid = (ceil(W / 32), H, B): a CTA makes 32 pixels of one image row.  The three input rows it needs (34 pixels x C
+// channels each, zero outside the image) are staged in shared memory with coalesced loads; a thread then assembles one
+// 16-byte chunk (8 of the 64 values) of one pixel.  C is a template parameter so that k / C and k % C are constants.
 template <int C>
 __global__ void __launch_bounds__(256) k_im2col_first(const void* __restrict__ in, int in_fmt, int H, int W, __nv_bfloat16* __restrict__ out) {
-  const int t = blockIdx.x * 256 + threadIdx.x;
-  if (t >= W * 8) return;
-  const int chunk = t & 7, x = t >> 3, y = blockIdx.y, n = blockIdx.z;
+  __shared__ float s_in[3][34][C];
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, n = blockIdx.z;
+  for (int i = threadIdx.x; i < 3 * 34 * C; i += 256) {
+    int r, xx, c;
+    if (in_fmt == RDP_IN_RGB_U8_NHWC) {   // (row, pixel, channel): channels contiguous in memory
+      c = i % C;
+      xx = (i / C) % 34;
+      r = i / (C * 34);
+    } else {                              // NCHW: pixels contiguous
+      xx = i % 34;
+      c = (i / 34) % C;
+      r = i / (34 * C);
+    }
+    const int yy = y + r - 1, gx = x0 + xx - 1;
+    float v = 0.f;
+    if (yy >= 0 && yy < H && gx >= 0 && gx < W) {
+      if (in_fmt == RDP_IN_RGB_U8_NHWC)
+        v = (float)__ldg((const uint8_t*)in + (((size_t)n * H + yy) * W + gx) * C + c) / 255.0f;  // ToTensor
+      else
+        v = __ldg((const float*)in + (((size_t)n * C + c) * H + yy) * W + gx);
+    }
+    s_in[r][xx][c] = v;
+  }
+  __syncthreads();
+  const int chunk = threadIdx.x & 7, px = threadIdx.x >> 3;
+  if (x0 + px >= W) return;
   __align__(16) __nv_bfloat16 v[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -1357,21 +1382,15 @@ __global__ void __launch_bounds__(256) k_im2col_first(const void* __restrict__ i
     float val = 0.f;
     if (k < 9 * C) {
       const int tap = k / C, c = k - tap * C;
-      const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
-      if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-        if (in_fmt == RDP_IN_RGB_U8_NHWC)
-          val = (float)__ldg((const uint8_t*)in + (((size_t)n * H + yy) * W + xx) * C + c) / 255.0f;  // ToTensor
-        else
-          val = __ldg((const float*)in + (((size_t)n * C + c) * H + yy) * W + xx);
-      }
+      val = s_in[tap / 3][px + tap % 3][c];
     }
     v[j] = __float2bfloat16_rn(val);
   }
-  *reinterpret_cast<uint4*>(out + (((size_t)n * H + y) * W + x) * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
+  *reinterpret_cast<uint4*>(out + (((size_t)n * H + y) * W + x0 + px) * 64 + chunk * 8) = *reinterpret_cast<const uint4*>(v);
 }
 
 static void launch_im2col_first(const void* in, int in_fmt, int B, int H, int W, int C, __nv_bfloat16* out, cudaStream_t stream) {
-  const dim3 grid((W * 8 + 255) / 256, H, B);
+  const dim3 grid((W + 31) / 32, H, B);
   switch (C) {
     case 1: k_im2col_first<1><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
     case 2: k_im2col_first<2><<<grid, 256, 0, stream>>>(in, in_fmt, H, W, out); break;
