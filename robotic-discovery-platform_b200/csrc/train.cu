@@ -477,42 +477,57 @@ __global__ void __launch_bounds__(256) k_bn_bwd_apply(const __nv_bfloat16* __res
 // `accumulate`: add to what dst already holds (the skip connection's other consumer wrote it before).
 __global__ void __launch_bounds__(256) k_maxpool_bwd(const __nv_bfloat16* __restrict__ src_y, const __nv_bfloat16* __restrict__ dpool, int B,
                                                      int H, int W, int C8, int accumulate, __nv_bfloat16* __restrict__ dst) {
-  const size_t total = (size_t)B * H * W * C8;
+  // A thread owns one 2x2 window (8 channels): the four inputs, the pooled gradient and the four destinations are each
+  // read once.  Rows / columns beyond the last full window (odd H or W) get no gradient: handled by the tail loop below.
   const int Ho = H / 2, Wo = W / 2;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+  const size_t windows = (size_t)B * Ho * Wo * C8;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < windows; i += (size_t)gridDim.x * blockDim.x) {
     const int cg = (int)(i % C8);
     size_t r = i / C8;
-    const int x = (int)(r % W);
-    r /= W;
-    const int y = (int)(r % H), n = (int)(r / H);
-    float o[8];
-    if (accumulate) unpack8(reinterpret_cast<const uint4*>(dst)[i], o);
-    else {
+    const int xo = (int)(r % Wo);
+    r /= Wo;
+    const int yo = (int)(r % Ho), n = (int)(r / Ho);
+    size_t at[4];
+    uint4 yv[4], dv[4];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) o[k] = 0.f;
+    for (int q = 0; q < 4; ++q) {
+      at[q] = (((size_t)n * H + 2 * yo + (q >> 1)) * W + 2 * xo + (q & 1)) * C8 + cg;
+      yv[q] = reinterpret_cast<const uint4*>(src_y)[at[q]];
+      dv[q] = accumulate ? reinterpret_cast<const uint4*>(dst)[at[q]] : make_uint4(0, 0, 0, 0);
     }
-    const int yo = y >> 1, xo = x >> 1;
-    if (yo < Ho && xo < Wo) {
-      float w4[4][8], g[8];
+    float w4[4][8], o[4][8], g[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      unpack8(yv[q], w4[q]);
+      unpack8(dv[q], o[q]);
+    }
+    unpack8(reinterpret_cast<const uint4*>(dpool)[i], g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      int best = 0;
+      float m = w4[0][k];
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (w4[q][k] > m) {
+          m = w4[q][k];
+          best = q;
+        }
 #pragma unroll
       for (int q = 0; q < 4; ++q)
-        unpack8(reinterpret_cast<const uint4*>(src_y)[(((size_t)n * H + 2 * yo + (q >> 1)) * W + 2 * xo + (q & 1)) * C8 + cg], w4[q]);
-      unpack8(reinterpret_cast<const uint4*>(dpool)[(((size_t)n * Ho + yo) * Wo + xo) * C8 + cg], g);
-      const int me = ((y & 1) << 1) | (x & 1);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        int best = 0;
-        float m = w4[0][k];
-#pragma unroll
-        for (int q = 1; q < 4; ++q)
-          if (w4[q][k] > m) {
-            m = w4[q][k];
-            best = q;
-          }
-        if (best == me) o[k] += g[k];
-      }
+        if (best == q) o[q][k] += g[k];
     }
-    reinterpret_cast<uint4*>(dst)[i] = pack8(o);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) reinterpret_cast<uint4*>(dst)[at[q]] = pack8(o[q]);
+  }
+  if (!accumulate && ((H | W) & 1)) {  // the uncovered last row / column of an odd-sized tensor: zero gradient
+    const size_t total = (size_t)B * H * W * C8;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+      size_t r = i / C8;
+      const int x = (int)(r % W);
+      r /= W;
+      const int y = (int)(r % H);
+      if ((y >> 1) >= Ho || (x >> 1) >= Wo) reinterpret_cast<uint4*>(dst)[i] = make_uint4(0, 0, 0, 0);
+    }
   }
 }
 
@@ -533,28 +548,39 @@ __global__ void __launch_bounds__(256) k_upsample_bwd(const __nv_bfloat16* __res
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
-    // output rows whose source interval touches yl: fy = ry * yo in (yl - 1, yl + 1); scan a safe window and test exactly
-    const int y_lo = max(0, 2 * yl - 3), y_hi = min(Ho - 1, 2 * yl + 4);
-    const int x_lo = max(0, 2 * xl - 3), x_hi = min(Wo - 1, 2 * xl + 4);
-    for (int yo = y_lo; yo <= y_hi; ++yo) {
-      const float fy = ry * (float)yo;
-      const int y0 = (int)fy, y1 = y0 + (y0 < h - 1 ? 1 : 0);
-      const float ly1 = fy - (float)y0, ly0 = 1.f - ly1;
-      const float wy = (y0 == yl ? ly0 : 0.f) + (y1 == yl ? ly1 : 0.f);
-      if (wy == 0.f) continue;
-      const int ys = yo + py;
-      if (ys < 0 || ys >= Hs) continue;
-      for (int xo = x_lo; xo <= x_hi; ++xo) {
+    // output rows whose source interval touches yl: fy = ry * yo in (yl - 1, yl + 1); scan a safe window of eight rows
+    // and eight columns, test each exactly with the forward pass's own expressions, ONCE per row and per column
+    const int y_lo = 2 * yl - 3, x_lo = 2 * xl - 3;
+    float wy[8], wx[8];
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+      const int yo = y_lo + a, xo = x_lo + a;
+      wy[a] = 0.f;
+      wx[a] = 0.f;
+      if (yo >= 0 && yo < Ho && yo + py >= 0 && yo + py < Hs) {
+        const float fy = ry * (float)yo;
+        const int y0 = (int)fy, y1 = y0 + (y0 < h - 1 ? 1 : 0);
+        const float ly1 = fy - (float)y0, ly0 = 1.f - ly1;
+        wy[a] = (y0 == yl ? ly0 : 0.f) + (y1 == yl ? ly1 : 0.f);
+      }
+      if (xo >= 0 && xo < Wo && xo + px >= 0 && xo + px < Ws) {
         const float fx = rx * (float)xo;
         const int x0 = (int)fx, x1 = x0 + (x0 < w - 1 ? 1 : 0);
         const float lx1 = fx - (float)x0, lx0 = 1.f - lx1;
-        const float wx = (x0 == xl ? lx0 : 0.f) + (x1 == xl ? lx1 : 0.f);
-        if (wx == 0.f) continue;
-        const int xs = xo + px;
-        if (xs < 0 || xs >= Ws) continue;
+        wx[a] = (x0 == xl ? lx0 : 0.f) + (x1 == xl ? lx1 : 0.f);
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 8; ++a) {
+      if (wy[a] == 0.f) continue;
+      const int ys = y_lo + a + py;
+#pragma unroll
+      for (int b = 0; b < 8; ++b) {
+        if (wx[b] == 0.f) continue;
+        const int xs = x_lo + b + px;
         float g[8];
         unpack8(*reinterpret_cast<const uint4*>(src + (((size_t)n * Hs + ys) * Ws + xs) * src_c + c_off + cg * 8), g);
-        const float wgt = wy * wx;
+        const float wgt = wy[a] * wx[b];
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, g[k], acc[k]);
       }
@@ -1338,7 +1364,7 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       const Shape Lp = buf.lv[kLevel[i] - 1];
       const size_t Pp = (size_t)B * Lp.H * Lp.W;
       // the skip consumer (an Up block) ran earlier in this loop and wrote dy[i-1]: accumulate
-      k_maxpool_bwd<<<ew_grid(Pp * c0 / 8), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1, buf.dy[i - 1]);
+      k_maxpool_bwd<<<ew_grid(Pp * c0 / 32), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1, buf.dy[i - 1]);
     }
     TRAIN_CHECKPOINT(stream, "routing %d", i);
   }
