@@ -479,14 +479,13 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const __nv_bfloat16* __rest
                                                      int H, int W, int C8, int accumulate, __nv_bfloat16* __restrict__ dst) {
   // A thread owns one 2x2 window (8 channels): the four inputs, the pooled gradient and the four destinations are each
   // read once.  Rows / columns beyond the last full window (odd H or W) get no gradient: handled by the tail loop below.
+  // grid = (ceil(Wo * C8 / 256), Ho, B)
   const int Ho = H / 2, Wo = W / 2;
-  const size_t windows = (size_t)B * Ho * Wo * C8;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < windows; i += (size_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % C8);
-    size_t r = i / C8;
-    const int xo = (int)(r % Wo);
-    r /= Wo;
-    const int yo = (int)(r % Ho), n = (int)(r / Ho);
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t < Wo * C8 && (int)blockIdx.y < Ho) {
+    const int xo = t / C8, cg = t - xo * C8;
+    const int yo = blockIdx.y, n = blockIdx.z;
+    const size_t i = (((size_t)n * Ho + yo) * Wo + xo) * C8 + cg;
     size_t at[4];
     uint4 yv[4], dv[4];
 #pragma unroll
@@ -521,7 +520,8 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const __nv_bfloat16* __rest
   }
   if (!accumulate && ((H | W) & 1)) {  // the uncovered last row / column of an odd-sized tensor: zero gradient
     const size_t total = (size_t)B * H * W * C8;
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const size_t nthreads = (size_t)gridDim.x * gridDim.y * gridDim.z * 256;
+    for (size_t i = (((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 256 + threadIdx.x; i < total; i += nthreads) {
       size_t r = i / C8;
       const int x = (int)(r % W);
       r /= W;
@@ -536,15 +536,14 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd(const __nv_bfloat16* __rest
 // read it.  src = gradient of the padded, up-sampled tensor: channels [c_off, c_off + 8*C8) of rows of `src_c` channels.
 __global__ void __launch_bounds__(256) k_upsample_bwd(const __nv_bfloat16* __restrict__ src, int src_c, int c_off, int B, int h, int w,
                                                       int C8, int Hs, int Ws, int py, int px, __nv_bfloat16* __restrict__ dst) {
-  const size_t total = (size_t)B * h * w * C8;
+  // grid = (ceil(w * C8 / 256), h, B): no 64-bit divisions on the streaming path
   const int Ho = 2 * h, Wo = 2 * w;
   const float ry = Ho > 1 ? (float)(h - 1) / (float)(Ho - 1) : 0.f, rx = Wo > 1 ? (float)(w - 1) / (float)(Wo - 1) : 0.f;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % C8);
-    size_t r = i / C8;
-    const int xl = (int)(r % w);
-    r /= w;
-    const int yl = (int)(r % h), n = (int)(r / h);
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t < w * C8) {
+    const int xl = t / C8, cg = t - xl * C8;
+    const int yl = blockIdx.y, n = blockIdx.z;
+    const size_t i = (((size_t)n * h + yl) * w + xl) * C8 + cg;
     float acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = 0.f;
@@ -574,12 +573,16 @@ __global__ void __launch_bounds__(256) k_upsample_bwd(const __nv_bfloat16* __res
     for (int a = 0; a < 8; ++a) {
       if (wy[a] == 0.f) continue;
       const int ys = y_lo + a + py;
+      const __nv_bfloat16* rowp = src + ((size_t)n * Hs + ys) * Ws * src_c + c_off + cg * 8;
+      uint4 v[8];
+#pragma unroll
+      for (int b = 0; b < 8; ++b)   // the row's loads first (up to four of them), then the arithmetic: loads in flight together
+        if (wx[b] != 0.f) v[b] = *reinterpret_cast<const uint4*>(rowp + (size_t)(x_lo + b + px) * src_c);
 #pragma unroll
       for (int b = 0; b < 8; ++b) {
         if (wx[b] == 0.f) continue;
-        const int xs = x_lo + b + px;
         float g[8];
-        unpack8(*reinterpret_cast<const uint4*>(src + (((size_t)n * Hs + ys) * Ws + xs) * src_c + c_off + cg * 8), g);
+        unpack8(v[b], g);
         const float wgt = wy[a] * wx[b];
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[k] = fmaf(wgt, g[k], acc[k]);
@@ -593,9 +596,11 @@ __global__ void __launch_bounds__(256) k_upsample_bwd(const __nv_bfloat16* __res
 __global__ void __launch_bounds__(256) k_slice_channels(const __nv_bfloat16* __restrict__ src, int src_c8, int off8, size_t P, int C8,
                                                         __nv_bfloat16* __restrict__ dst) {
   const size_t total = P * C8;
+  const bool pow2 = (C8 & (C8 - 1)) == 0;
+  const int sh = __ffs(C8) - 1;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-    const size_t p = i / C8;
-    const int cg = (int)(i % C8);
+    const size_t p = pow2 ? i >> sh : i / C8;   // (a 64-bit division costs more than the copy itself)
+    const int cg = (int)(i - p * C8);
     reinterpret_cast<uint4*>(dst)[i] = reinterpret_cast<const uint4*>(src)[p * src_c8 + off8 + cg];
   }
 }
@@ -1359,12 +1364,13 @@ extern "C" int rdp_unet_train_backward(const RdpTrainWeights* w, const float* dl
       k_slice_channels<<<ew_grid(P * c0 / 8), 256, 0, stream>>>(buf.dx, cin_pad / 8, 0, P, c0 / 8, buf.dy[skip_i]);
       const int dyp = L.H - 2 * Ll.H, dxp = L.W - 2 * Ll.W;
       const size_t Pl = (size_t)B * Ll.H * Ll.W;
-      k_upsample_bwd<<<ew_grid(Pl * c1 / 8), 256, 0, stream>>>(buf.dx, cin_pad, c0, B, Ll.H, Ll.W, c1 / 8, L.H, L.W, dyp / 2, dxp / 2, buf.dy[low_i]);
+      k_upsample_bwd<<<dim3((Ll.W * (c1 / 8) + 255) / 256, Ll.H, B), 256, 0, stream>>>(buf.dx, cin_pad, c0, B, Ll.H, Ll.W, c1 / 8, L.H, L.W, dyp / 2, dxp / 2, buf.dy[low_i]);
     } else if (down_first) {                           // Down block: the input was pooled from y[i-1], which also feeds a skip
       const Shape Lp = buf.lv[kLevel[i] - 1];
       const size_t Pp = (size_t)B * Lp.H * Lp.W;
       // the skip consumer (an Up block) ran earlier in this loop and wrote dy[i-1]: accumulate
-      k_maxpool_bwd<<<ew_grid(Pp * c0 / 32), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1, buf.dy[i - 1]);
+      k_maxpool_bwd<<<dim3(((Lp.W / 2) * (c0 / 8) + 255) / 256, std::max(1, Lp.H / 2), B), 256, 0, stream>>>(buf.y[i - 1], buf.dx, B, Lp.H, Lp.W, c0 / 8, 1,
+                                                                                                        buf.dy[i - 1]);
     }
     TRAIN_CHECKPOINT(stream, "routing %d", i);
   }
