@@ -826,9 +826,20 @@ __global__ void __launch_bounds__(256) k_dw_layout(const float* __restrict__ src
   __shared__ float tile[32][9 * 32 + 1];  // [co][ci * 9 + tap]
   const int ci0 = blockIdx.x * 32, co0 = blockIdx.y * 32;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  for (int r = w; r < 9 * 32; r += 8) {  // r = tap * 32 + ci
-    const int tap = r >> 5, ci = ci0 + (r & 31), co = co0 + lane;
-    if (ci < cin && co < cout) tile[lane][(r & 31) * 9 + tap] = src[((size_t)tap * cin + ci) * cout + co];
+  const int co_l = co0 + lane;
+#pragma unroll 1
+  for (int r0 = w; r0 < 9 * 32; r0 += 8 * 6) {  // r = tap * 32 + ci; six rows of the scratch in flight per warp
+    float v[6];
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int r = r0 + 8 * u, tap = r >> 5, ci = ci0 + (r & 31);
+      v[u] = (r < 9 * 32 && ci < cin && co_l < cout) ? src[((size_t)tap * cin + ci) * cout + co_l] : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 6; ++u) {
+      const int r = r0 + 8 * u;
+      if (r < 9 * 32) tile[lane][(r & 31) * 9 + (r >> 5)] = v[u];
+    }
   }
   __syncthreads();
   const int span = min(32, cin - ci0) * 9;
