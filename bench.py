@@ -74,10 +74,11 @@ def geometry_bytes_per_frame(P: int, n_points: float) -> float:
 
 def load_traffic():
     """DRAM bytes from the committed ncu --set full capture (profiles/), or None."""
-    path = os.path.join(ROOT, "profiles", "r01_traffic.json")
-    if os.path.exists(path):
-        with open(path) as fh:
-            return json.load(fh)
+    for name in ("r02_traffic.json", "r01_traffic.json"):
+        path = os.path.join(ROOT, "profiles", name)
+        if os.path.exists(path):
+            with open(path) as fh:
+                return json.load(fh)
     return None
 
 
